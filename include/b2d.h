@@ -1,0 +1,95 @@
+/* b2d.h — C ABI of libb2d.so, the B200-native block-parallel DEFLATE / checksum
+ * library.  Plain pointers and sizes only; no Python, torch or CUDA types.
+ *
+ * Each entry point names the reference interface it stands in for (paths under
+ * /root/reference/src/zlib_ng/).  The reference is a CPython extension, so the
+ * "binding a maintainer would add" is the ctypes stub in
+ * python-zlib-ng_b200/zlib_ng_b200/_native.py.
+ *
+ * Return value: 0 = ok, negative = error; codes reuse zlib's numbering
+ * (zlib-ng.h Z_STREAM_ERROR / Z_MEM_ERROR / Z_BUF_ERROR) so the Python layer can
+ * raise exactly what zlib_ngmodule.c raises (zlib_ngmodule.c:68-95,224-225,
+ * 1749-1755).  There is no CPU fallback anywhere behind this ABI: if no CUDA
+ * device is usable, b2d_ctx_create fails with B2D_CUDA_ERROR.
+ */
+#ifndef B2D_H
+#define B2D_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2D_OK 0
+#define B2D_STREAM_ERROR (-2) /* bad level / bad argument            (Z_STREAM_ERROR) */
+#define B2D_MEM_ERROR (-4)    /* host or device allocation failed     (Z_MEM_ERROR)    */
+#define B2D_BUF_ERROR (-5)    /* output capacity too small            (Z_BUF_ERROR)    */
+#define B2D_CUDA_ERROR (-100) /* CUDA runtime error; see b2d_last_error()              */
+
+#define B2D_DEVICE_PAD 64u    /* bytes that must be readable after device-resident input */
+
+typedef struct b2d_ctx b2d_ctx;
+
+/* One context = one GPU + its work buffers (sized for `max_batch` input bytes per
+ * launch sequence; 0 selects 256 MiB; rounded up to 128 KiB).  Calls on one
+ * context are serialised internally; use one context per GPU.
+ * Stands in for ParallelCompress__new__ / zng_deflateInit2 (zlib_ngmodule.c:1617-1674). */
+int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out);
+void b2d_ctx_destroy(b2d_ctx *ctx);
+/* text of the last error raised on the calling thread */
+const char *b2d_last_error(void);
+int b2d_device_count(void);
+
+/* Worst-case raw-deflate bytes for n input bytes (stored fallback per 32 KiB
+ * sub-block + a sync marker per 128 KiB block + optional final block).
+ * Stands in for zng_deflateBound (zlib-ng/deflate.c:661-667). */
+uint64_t b2d_deflate_bound(uint64_t n);
+
+/* _ParallelCompress.compress_and_crc(data, zdict) (zlib_ngmodule.c:1696-1782):
+ * raw DEFLATE of `data` primed with the last 32 KiB of `dict`, never BFINAL,
+ * ends byte-aligned with the sync-flush marker 00 00 ff ff; *crc = crc32(data).
+ * B2D_BUF_ERROR if the result does not fit out_cap (-> OverflowError). */
+int b2d_compress_and_crc(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                         uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc);
+
+/* General host-buffer form used for zlib_ng.compress / compressobj
+ * (zlib_compress_impl, zlib_ngmodule.c:199-273; Compress.compress/flush :530-784):
+ * same stream as above; `final` != 0 appends the BFINAL empty fixed block 03 00
+ * (what gzip_ng_threaded.py:333 appends).  crc / adler may be NULL; adler is the
+ * Adler-32 of `data` continued from *adler's incoming value, crc likewise. */
+int b2d_deflate_host(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t n, const uint8_t *dict, uint64_t dict_n,
+                     int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler);
+
+/* zlib_ng.crc32 / adler32 (zlib_ngmodule.c:1517-1562, 1455-1500) on host bytes */
+int b2d_crc32(b2d_ctx *ctx, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out);
+int b2d_adler32(b2d_ctx *ctx, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out);
+/* zlib_ng.crc32_combine (zlib_ngmodule.c:1585-1596 -> crc32_braid_comb.c:17-19); pure host */
+uint32_t b2d_crc32_combine(uint32_t crc1, uint32_t crc2, int64_t len2);
+/* zng_adler32_combine (zlib-ng/adler32.c:78-100); pure host */
+uint32_t b2d_adler32_combine(uint32_t adler1, uint32_t adler2, int64_t len2);
+
+/* ---- device-resident variants (inputs and outputs stay in HBM) --------------
+ * d_buf = [dict (dict_n <= 32768 bytes) | data (n bytes)], 16-byte aligned, with
+ * B2D_DEVICE_PAD readable bytes after the data.  d_out is 4-byte aligned and
+ * out_cap >= b2d_deflate_bound(n).  *kernel_ms (may be NULL) receives the
+ * CUDA-event time of the whole launch sequence. */
+int b2d_deflate_device(b2d_ctx *ctx, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
+                       uint64_t out_cap, uint64_t *out_n, uint32_t *crc, float *kernel_ms);
+int b2d_crc32_device(b2d_ctx *ctx, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out, float *kernel_ms);
+int b2d_adler32_device(b2d_ctx *ctx, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out, float *kernel_ms);
+
+/* ---- memory helpers for callers without their own CUDA binding --------------- */
+int b2d_device_alloc(b2d_ctx *ctx, uint64_t bytes, void **ptr);
+int b2d_device_free(b2d_ctx *ctx, void *ptr);
+int b2d_host_alloc(b2d_ctx *ctx, uint64_t bytes, void **ptr);      /* pinned */
+int b2d_host_free(b2d_ctx *ctx, void *ptr);
+int b2d_copy_h2d(b2d_ctx *ctx, void *d_dst, const void *h_src, uint64_t bytes);
+int b2d_copy_d2h(b2d_ctx *ctx, void *h_dst, const void *d_src, uint64_t bytes);
+int b2d_device_sync(b2d_ctx *ctx);
+/* number of this library's kernel launches since the context was created */
+uint64_t b2d_launch_count(b2d_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2D_H */

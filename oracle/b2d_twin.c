@@ -9,7 +9,7 @@
  *
  *   stage 1  chains    prev-distance per position (hash of 5 bytes, 2^14 heads)
  *   stage 2  matches   best (len, dist) per position, chain depth by level
- *   stage 3  parse     local lazy parse -> tokens + per-sub-block histograms
+ *   stage 3  parse     lazy parse per 1 KiB unit -> tokens + per-sub-block histograms
  *   stage 4  plan      Huffman lengths / header / stored-fixed-dynamic choice
  *   stage 5  scan      bit offsets of sub-blocks, byte offsets of blocks
  *   stage 6  emit      bit packing, sync-flush marker per device block
@@ -51,7 +51,9 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
     size_t start = D + b * (size_t)B2D_BLOCK;
     size_t end = start + B2D_BLOCK < job_end ? start + B2D_BLOCK : job_end;
     for (size_t p = start; p < end; p++) {
-        uint32_t maxl = end - p < B2D_MAX_MATCH ? (uint32_t)(end - p) : B2D_MAX_MATCH;
+        size_t uend = ((p - D) / B2D_UNIT + 1) * (size_t)B2D_UNIT + D;   /* no match crosses a parse unit */
+        size_t lim = uend < end ? uend : end;
+        uint32_t maxl = lim - p < B2D_MAX_MATCH ? (uint32_t)(lim - p) : B2D_MAX_MATCH;
         uint32_t best = 0, bd = 0;
         if (maxl >= B2D_MIN_MATCH) {
             size_t cand = p;
@@ -70,22 +72,22 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
     }
 }
 
-/* stage 3: tokens go to tok[b*BLOCK ...], sub-block summaries to info[b*NSUB ...],
- * histograms to hist[(b*NSUB+s)*316 ...] (286 lit/len then 30 dist) */
-static void twin_parse(const uint8_t *buf, size_t D, size_t n, size_t b, const uint32_t *match,
+/* stage 3: sub-block k of the job is parsed on its own (every sub-block is a
+ * whole number of parse units): tokens go to tok[k*SUB ...], the summary to
+ * info[k], histograms to hist[k*316 ...] (286 lit/len then 30 dist) */
+static void twin_parse(const uint8_t *buf, size_t D, size_t n, size_t k, const uint32_t *match,
                        uint32_t *tok, b2d_subinfo *info, uint32_t *hist, b2d_policy pol) {
-    size_t start = b * (size_t)B2D_BLOCK;               /* relative to D */
-    uint32_t len = (uint32_t)(n - start < B2D_BLOCK ? n - start : B2D_BLOCK);
+    size_t start = k * (size_t)B2D_SUB;               /* relative to D */
+    uint32_t len = (uint32_t)(n - start < B2D_SUB ? n - start : B2D_SUB);
     const uint32_t *m = match + start;
     uint32_t *t = tok + start;
-    uint32_t nt = 0, i = 0;
-    for (uint32_t s = 0; s < B2D_NSUB; s++) {
-        b2d_subinfo *I = &info[b * B2D_NSUB + s];
-        uint32_t *H = hist + (b * B2D_NSUB + s) * (size_t)(B2D_LL_CODES + B2D_D_CODES);
-        memset(H, 0, sizeof(uint32_t) * (B2D_LL_CODES + B2D_D_CODES));
-        uint32_t limit = (s + 1) * B2D_SUB < len ? (s + 1) * B2D_SUB : len;
-        I->in_start = i; I->tok_start = nt;
-        while (i < limit) {
+    uint32_t *H = hist + k * (size_t)B2D_HIST;
+    uint32_t nt = 0;
+    memset(H, 0, sizeof(uint32_t) * B2D_HIST);
+    for (uint32_t u = 0; u < len; u += B2D_UNIT) {
+        uint32_t uend = u + B2D_UNIT < len ? u + B2D_UNIT : len;
+        uint32_t i = u;
+        while (i < uend) {
             uint32_t l0 = b2d_match_len(m[i]);
             uint32_t l1 = i + 1 < len ? b2d_match_len(m[i + 1]) : 0;
             uint32_t l2 = i + 2 < len ? b2d_match_len(m[i + 2]) : 0;
@@ -104,10 +106,9 @@ static void twin_parse(const uint8_t *buf, size_t D, size_t n, size_t b, const u
             }
             i += step;
         }
-        I->tok_count = nt - I->tok_start;
-        I->in_len = i - I->in_start;
-        if (I->tok_count) H[256] = 1;
     }
+    info[k].in_len = len; info[k].tok_count = nt; info[k].bit_off = 0; info[k].pad = 0;
+    if (nt) H[256] = 1;
 }
 
 /* ---- stage 6 helpers: LSB-first bit writer into a zeroed byte buffer ---- */
@@ -122,10 +123,10 @@ static void put(bitw *w, uint64_t value, uint32_t count) {
 typedef struct {
     uint16_t *prevd;      /* [D + n]            */
     uint32_t *match;      /* [n]                */
-    uint32_t *tok;        /* [nblocks * BLOCK]  */
-    b2d_subinfo *info;    /* [nblocks * NSUB]   */
-    uint32_t *hist;       /* [nblocks * NSUB * 316] */
-    b2d_plan *plan;       /* [nblocks * NSUB]   */
+    uint32_t *tok;        /* [nsub * SUB]       */
+    b2d_subinfo *info;    /* [nsub]             */
+    uint32_t *hist;       /* [nsub * 316]       */
+    b2d_plan *plan;       /* [nsub]             */
     uint64_t *block_off;  /* [nblocks + 1] byte offsets */
     size_t nblocks;
 } twin_state;
@@ -137,6 +138,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
                            twin_state **st_out) {
     b2d_policy pol = b2d_level_policy(level);
     size_t nb = (n + B2D_BLOCK - 1) / B2D_BLOCK;
+    size_t nsub = (n + B2D_SUB - 1) / B2D_SUB;
     twin_state *S = (twin_state *)calloc(1, sizeof *S);
     S->nblocks = nb;
     S->prevd = (uint16_t *)calloc(D + n + 8, sizeof(uint16_t));
@@ -148,13 +150,15 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     S->block_off = (uint64_t *)calloc(nb + 1, sizeof(uint64_t));
     uint16_t *head = (uint16_t *)malloc(sizeof(uint16_t) * B2D_HASH_SIZE);
     b2d_huff_scratch *scr = (b2d_huff_scratch *)malloc(sizeof *scr);
-    for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head);
-    for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol);
-    for (size_t b = 0; b < nb; b++) twin_parse(buf, D, n, b, S->match, S->tok, S->info, S->hist, pol);
-    for (size_t k = 0; k < nb * B2D_NSUB; k++) {
+    if (level > 0) {
+        for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head);
+        for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol);
+    }
+    for (size_t k = 0; k < nsub; k++) twin_parse(buf, D, n, k, S->match, S->tok, S->info, S->hist, pol);
+    for (size_t k = 0; k < nsub; k++) {
         if (!S->info[k].tok_count) continue;
-        const uint32_t *H = S->hist + k * (size_t)(B2D_LL_CODES + B2D_D_CODES);
-        b2d_plan_subblock(H, H + B2D_LL_CODES, S->info[k].in_len, &S->plan[k], scr);
+        const uint32_t *H = S->hist + k * (size_t)B2D_HIST;
+        b2d_plan_subblock(H, H + B2D_LL_CODES, S->info[k].in_len, &S->plan[k], scr, level == 0);
     }
     /* stage 5: sizes */
     uint64_t off = 0;
@@ -163,7 +167,8 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
         uint64_t bits = 0;
         for (uint32_t s = 0; s < B2D_NSUB; s++) {
             size_t k = b * B2D_NSUB + s;
-            if (!S->info[k].tok_count) continue;
+            if (k >= nsub || !S->info[k].tok_count) continue;
+            S->info[k].bit_off = (uint32_t)bits;
             bits += S->plan[k].hdr_bits;
             if (S->plan[k].type == 0) bits = ((bits + 7) & ~7ull) + 32 + 8ull * S->info[k].in_len;
             else bits += S->plan[k].body_bits;
@@ -180,6 +185,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
             bitw w = { out, S->block_off[b] * 8 };
             for (uint32_t s = 0; s < B2D_NSUB; s++) {
                 size_t k = b * B2D_NSUB + s;
+                if (k >= nsub) continue;
                 const b2d_subinfo *I = &S->info[k];
                 const b2d_plan *P = &S->plan[k];
                 if (!I->tok_count) continue;
@@ -187,11 +193,11 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
                 if (P->type == 0) {
                     w.bitpos = (w.bitpos + 7) & ~7ull;
                     put(&w, I->in_len, 16); put(&w, (~I->in_len) & 0xffffu, 16);
-                    memcpy(out + (w.bitpos >> 3), buf + D + b * (size_t)B2D_BLOCK + I->in_start, I->in_len);
+                    memcpy(out + (w.bitpos >> 3), buf + D + k * (size_t)B2D_SUB, I->in_len);
                     w.bitpos += 8ull * I->in_len;
                     continue;
                 }
-                const uint32_t *t = S->tok + b * (size_t)B2D_BLOCK + I->tok_start;
+                const uint32_t *t = S->tok + k * (size_t)B2D_SUB;
                 for (uint32_t i = 0; i < I->tok_count; i++) {
                     uint32_t x = t[i];
                     if (!b2d_tok_is_match(x)) { uint32_t c = P->ll_code[x]; put(&w, c & 0xffffu, c >> 16); continue; }

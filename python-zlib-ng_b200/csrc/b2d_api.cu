@@ -1,0 +1,345 @@
+/* b2d_api.cu — host side of libb2d.so: the C ABI declared in include/b2d.h.
+ *
+ * A context owns one CUDA stream, the per-batch work buffers of the pipeline
+ * (b2d_kernels.cu), a pinned staging pair for host-buffer calls and the
+ * checksum workspace (b2d_checksum.cu).  Big inputs are cut into batches of
+ * `max_batch` bytes; batch j > 0 is primed with the 32 KiB of input before it,
+ * so the result does not depend on the batch size (blocks are
+ * independent given the raw input).
+ */
+#include <cuda_runtime.h>
+#include <mutex>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/b2d.h"
+#include "b2d_kernels.h"
+
+static thread_local char g_err[512];
+static int fail_cuda(cudaError_t e, const char *where) {
+    snprintf(g_err, sizeof g_err, "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), where);
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? B2D_MEM_ERROR : B2D_CUDA_ERROR;
+}
+static int fail(int code, const char *msg) { snprintf(g_err, sizeof g_err, "%s", msg); return code; }
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail_cuda(e_, #x); } while (0)
+
+extern "C" const char *b2d_last_error(void) { return g_err; }
+extern "C" int b2d_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+
+static inline uint64_t align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
+
+extern "C" uint64_t b2d_deflate_bound(uint64_t n) {
+    const uint64_t nsub = (n + B2D_SUB - 1) / B2D_SUB, nblk = (n + B2D_BLOCK - 1) / B2D_BLOCK;
+    /* stored sub-block: <= 1 byte of header+pad, 4 bytes LEN/NLEN; block marker: <= 5 bytes; final 03 00 */
+    return n + 5 * nsub + 5 * (nblk ? nblk : 1) + 2 + 8;
+}
+
+struct b2d_ctx {
+    int device;
+    uint64_t max_batch;
+    cudaStream_t st;
+    cudaEvent_t ev0, ev1;
+    std::mutex mu;
+    /* work buffers for one batch */
+    uint8_t *d_in;  uint64_t d_in_cap;      /* WINDOW + max_batch + pad (host-buffer calls)   */
+    uint8_t *d_out; uint64_t d_out_cap;     /* bound(max_batch) rounded (host-buffer calls)   */
+    uint16_t *prevd; uint32_t *match, *tok, *hist;
+    b2d_subinfo *info; b2d_plan *plan; b2d_huff_scratch *scratch;
+    uint64_t *block_off;
+    uint64_t *d_total;                      /* running output byte offset of a call           */
+    uint64_t *h_total;                      /* pinned                                         */
+    uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
+    b2d_cksum_ws *ck;
+    uint64_t launches;
+};
+
+static void ctx_free(b2d_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_in); cudaFree(c->d_out); cudaFree(c->prevd); cudaFree(c->match); cudaFree(c->tok);
+    cudaFree(c->hist); cudaFree(c->info); cudaFree(c->plan); cudaFree(c->scratch); cudaFree(c->block_off);
+    cudaFree(c->d_total);
+    if (c->h_total) cudaFreeHost(c->h_total);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    b2d_cksum_ws_destroy(c->ck);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->st) cudaStreamDestroy(c->st);
+    delete c;
+}
+
+extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
+    if (!out) return fail(B2D_STREAM_ERROR, "null out pointer");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail_cuda(e == cudaSuccess ? cudaErrorNoDevice : e, "b2d_ctx_create: no usable CUDA device (there is no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(B2D_STREAM_ERROR, "bad device index");
+    if (max_batch == 0) max_batch = 256ull << 20;
+    max_batch = align_up(max_batch, B2D_BLOCK);
+    if (max_batch > (2048ull << 20)) return fail(B2D_STREAM_ERROR, "max_batch above 2 GiB");
+    b2d_ctx *c = new b2d_ctx();
+    c->device = device; c->max_batch = max_batch; c->st = nullptr; c->ev0 = c->ev1 = nullptr;
+    const uint64_t nsub = max_batch / B2D_SUB, nblk = max_batch / B2D_BLOCK;
+#define CC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { int rc_ = fail_cuda(e_, #x); ctx_free(c); return rc_; } } while (0)
+    CC(cudaSetDevice(device));
+    CC(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    CC(cudaEventCreate(&c->ev0)); CC(cudaEventCreate(&c->ev1));
+    CC(b2d_kernels_init());
+    c->d_in_cap = B2D_WINDOW + max_batch + 1024;
+    c->d_out_cap = align_up(b2d_deflate_bound(max_batch), 256);
+    CC(cudaMalloc(&c->d_in, c->d_in_cap));
+    CC(cudaMalloc(&c->d_out, c->d_out_cap));
+    CC(cudaMalloc(&c->prevd, (B2D_WINDOW + max_batch + 64) * sizeof(uint16_t)));
+    CC(cudaMalloc(&c->match, max_batch * sizeof(uint32_t)));
+    CC(cudaMalloc(&c->tok, max_batch * sizeof(uint32_t)));
+    CC(cudaMalloc(&c->hist, nsub * B2D_HIST * sizeof(uint32_t)));
+    CC(cudaMalloc(&c->info, nsub * sizeof(b2d_subinfo)));
+    CC(cudaMalloc(&c->plan, nsub * sizeof(b2d_plan)));
+    CC(cudaMalloc(&c->scratch, nsub * sizeof(b2d_huff_scratch)));
+    CC(cudaMalloc(&c->block_off, (nblk + 1) * sizeof(uint64_t)));
+    CC(cudaMalloc(&c->d_total, sizeof(uint64_t)));
+    CC(cudaMallocHost(&c->h_total, sizeof(uint64_t)));
+    c->h_stage_cap = (B2D_WINDOW + max_batch) > c->d_out_cap ? (B2D_WINDOW + max_batch) : c->d_out_cap;
+    if (c->h_stage_cap > (64ull << 20)) c->h_stage_cap = 64ull << 20;   /* staged in pieces */
+    CC(cudaMallocHost(&c->h_stage, c->h_stage_cap));
+    CC(b2d_cksum_ws_create(&c->ck));
+#undef CC
+    *out = c;
+    return B2D_OK;
+}
+
+extern "C" void b2d_ctx_destroy(b2d_ctx *c) { ctx_free(c); }
+extern "C" uint64_t b2d_launch_count(b2d_ctx *c) { return c ? c->launches : 0; }
+
+/* ---- memory helpers -------------------------------------------------------- */
+extern "C" int b2d_device_alloc(b2d_ctx *c, uint64_t bytes, void **p) { CU(cudaSetDevice(c->device)); CU(cudaMalloc(p, bytes)); return B2D_OK; }
+extern "C" int b2d_device_free(b2d_ctx *c, void *p) { CU(cudaSetDevice(c->device)); CU(cudaFree(p)); return B2D_OK; }
+extern "C" int b2d_host_alloc(b2d_ctx *c, uint64_t bytes, void **p) { CU(cudaSetDevice(c->device)); CU(cudaMallocHost(p, bytes)); return B2D_OK; }
+extern "C" int b2d_host_free(b2d_ctx *c, void *p) { CU(cudaSetDevice(c->device)); CU(cudaFreeHost(p)); return B2D_OK; }
+extern "C" int b2d_copy_h2d(b2d_ctx *c, void *d, const void *h, uint64_t n) {
+    CU(cudaSetDevice(c->device)); CU(cudaMemcpyAsync(d, h, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return B2D_OK;
+}
+extern "C" int b2d_copy_d2h(b2d_ctx *c, void *h, const void *d, uint64_t n) {
+    CU(cudaSetDevice(c->device)); CU(cudaMemcpyAsync(h, d, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return B2D_OK;
+}
+extern "C" int b2d_device_sync(b2d_ctx *c) { CU(cudaSetDevice(c->device)); CU(cudaDeviceSynchronize()); return B2D_OK; }
+
+/* ---- checksums -------------------------------------------------------------- */
+extern "C" uint32_t b2d_crc32_combine(uint32_t crc1, uint32_t crc2, int64_t len2) {
+    return b2d_host_crc32_combine(crc1, crc2, (uint64_t)len2);
+}
+extern "C" uint32_t b2d_adler32_combine(uint32_t a1, uint32_t a2, int64_t len2) {
+    if (len2 < 0) return 0xffffffffu;
+    return b2d_host_adler32_combine(a1, a2, (uint64_t)len2);
+}
+
+static uint32_t crc_launches(const uint8_t *d, uint64_t n) {
+    uint64_t head = (16 - ((uintptr_t)d & 15)) & 15; if (head > n) head = n;
+    return (n - head) / 16384 ? 2u : 1u;
+}
+
+extern "C" int b2d_crc32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, uint64_t n, uint32_t *out, float *ms) {
+    if (!c || !out) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (ms) CU(cudaEventRecord(c->ev0, c->st));
+    CU(b2d_crc32_dev(c->ck, d, n, start, out, c->st));
+    if (n) c->launches += crc_launches(d, n);
+    if (ms) { CU(cudaEventRecord(c->ev1, c->st)); CU(cudaEventSynchronize(c->ev1)); CU(cudaEventElapsedTime(ms, c->ev0, c->ev1)); }
+    return B2D_OK;
+}
+extern "C" int b2d_adler32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, uint64_t n, uint32_t *out, float *ms) {
+    if (!c || !out) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (ms) CU(cudaEventRecord(c->ev0, c->st));
+    CU(b2d_adler32_dev(c->ck, d, n, start, out, c->st));
+    if (n) c->launches += 2;
+    if (ms) { CU(cudaEventRecord(c->ev1, c->st)); CU(cudaEventSynchronize(c->ev1)); CU(cudaEventElapsedTime(ms, c->ev0, c->ev1)); }
+    return B2D_OK;
+}
+
+/* host bytes -> device in pieces through the pinned stage (or directly when the
+ * caller's buffer is itself pinned), calling `fn` on each resident piece */
+template <typename F>
+static int for_each_staged(b2d_ctx *c, const uint8_t *data, uint64_t n, F fn) {
+    cudaPointerAttributes at;
+    bool pinned = cudaPointerGetAttributes(&at, data) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    const uint64_t piece_cap = c->max_batch;
+    for (uint64_t off = 0; off < n;) {
+        const uint64_t m = n - off < piece_cap ? n - off : piece_cap;
+        if (pinned) { CU(cudaMemcpyAsync(c->d_in, data + off, m, cudaMemcpyHostToDevice, c->st)); }
+        else {
+            for (uint64_t o = 0; o < m; o += c->h_stage_cap) {
+                const uint64_t k = m - o < c->h_stage_cap ? m - o : c->h_stage_cap;
+                memcpy(c->h_stage, data + off + o, k);
+                CU(cudaMemcpyAsync(c->d_in + o, c->h_stage, k, cudaMemcpyHostToDevice, c->st));
+                CU(cudaStreamSynchronize(c->st));
+            }
+        }
+        int rc = fn(c->d_in, m);
+        if (rc) return rc;
+        off += m;
+    }
+    return B2D_OK;
+}
+
+extern "C" int b2d_crc32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out) {
+    if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    uint32_t crc = start;
+    int rc = for_each_staged(c, data, n, [&](const uint8_t *d, uint64_t m) -> int {
+        CU(b2d_crc32_dev(c->ck, d, m, crc, &crc, c->st));
+        c->launches += crc_launches(d, m);
+        return B2D_OK;
+    });
+    if (rc) return rc;
+    *out = crc;
+    return B2D_OK;
+}
+extern "C" int b2d_adler32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out) {
+    if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    uint32_t a = start;
+    int rc = for_each_staged(c, data, n, [&](const uint8_t *d, uint64_t m) -> int {
+        CU(b2d_adler32_dev(c->ck, d, m, a, &a, c->st));
+        c->launches += 2;
+        return B2D_OK;
+    });
+    if (rc) return rc;
+    *out = a;
+    return B2D_OK;
+}
+
+/* ---- deflate ---------------------------------------------------------------- */
+static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uint64_t n, uint64_t readable, int level, uint8_t *out) {
+    J->buf = buf; J->D = D; J->n = n; J->buf_readable = readable; J->level = level;
+    J->prevd = c->prevd; J->match = c->match; J->tok = c->tok; J->info = c->info; J->hist = c->hist;
+    J->plan = c->plan; J->scratch = c->scratch; J->block_off = c->block_off; J->total = c->d_total; J->out = out;
+}
+
+extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
+                                  uint64_t out_cap, uint64_t *out_n, uint32_t *crc, float *ms) {
+    if (!c || !out_n || (!d_buf && n) || !d_out) return fail(B2D_STREAM_ERROR, "null argument");
+    if (level < 0 || level > 9) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    if (dict_n > B2D_WINDOW) return fail(B2D_STREAM_ERROR, "device dictionary longer than 32768 bytes");
+    if (((uintptr_t)d_buf & 15) || ((uintptr_t)d_out & 3)) return fail(B2D_STREAM_ERROR, "misaligned device pointer");
+    if (out_cap < b2d_deflate_bound(n)) return fail(B2D_BUF_ERROR, "out_cap below b2d_deflate_bound(n)");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (ms) CU(cudaEventRecord(c->ev0, c->st));
+    CU(cudaMemsetAsync(d_out, 0, align_up(b2d_deflate_bound(n), 4) <= out_cap ? align_up(b2d_deflate_bound(n), 4) : out_cap, c->st));
+    CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
+    const uint64_t readable = dict_n + n + B2D_DEVICE_PAD;
+    for (uint64_t off = 0; off < n; off += c->max_batch) {
+        const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
+        /* re-base so the work buffers are indexed from (at most) 32 KiB + 15 bytes before the batch */
+        const uint64_t abs0 = dict_n + off;
+        const uint64_t base = abs0 > B2D_WINDOW ? (abs0 - B2D_WINDOW) & ~(uint64_t)15 : 0;
+        b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out);
+        CU(b2d_launch_pipeline(&J, c->st));
+        c->launches += level > 0 ? 6 : 4;
+    }
+    if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
+    CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+    if (ms) CU(cudaEventRecord(c->ev1, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    if (crc) *crc = n ? b2d_crc32_dev_finish(c->ck, n, 0) : 0;
+    *out_n = *c->h_total;
+    if (n == 0) {   /* the empty job is just the sync marker: 00 00 00 ff ff */
+        static const uint8_t marker[5] = {0, 0, 0, 0xff, 0xff};
+        CU(cudaMemcpyAsync(d_out, marker, 5, cudaMemcpyHostToDevice, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        *out_n = 5;
+    }
+    return B2D_OK;
+}
+
+extern "C" int b2d_deflate_host(b2d_ctx *c, int level, const uint8_t *data, uint64_t n, const uint8_t *dict, uint64_t dict_n,
+                                int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler) {
+    if (!c || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (level < 0 || level > 9) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
+    uint64_t produced = 0;
+    uint32_t crc_acc = crc ? *crc : 0, adler_acc = adler ? *adler : 1;
+    cudaPointerAttributes at;
+    const bool pinned = n && cudaPointerGetAttributes(&at, data) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    auto h2d = [&](uint8_t *dst, const uint8_t *src, uint64_t bytes, bool src_pinned) -> int {
+        if (src_pinned) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st)); return B2D_OK; }
+        for (uint64_t o = 0; o < bytes; o += c->h_stage_cap) {
+            const uint64_t k = bytes - o < c->h_stage_cap ? bytes - o : c->h_stage_cap;
+            CU(cudaStreamSynchronize(c->st));            /* the stage may still be in flight */
+            memcpy(c->h_stage, src + o, k);
+            CU(cudaMemcpyAsync(dst + o, c->h_stage, k, cudaMemcpyHostToDevice, c->st));
+        }
+        CU(cudaStreamSynchronize(c->st));
+        return B2D_OK;
+    };
+    for (uint64_t off = 0; off < n; off += c->max_batch) {
+        const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
+        uint64_t D;
+        int rc;
+        if (off == 0) {
+            D = dict_n;
+            if (D && (rc = h2d(c->d_in, dict, D, false))) return rc;
+            if ((rc = h2d(c->d_in + D, data, m, pinned))) return rc;
+        } else {
+            D = B2D_WINDOW;
+            if ((rc = h2d(c->d_in, data + off - B2D_WINDOW, B2D_WINDOW + m, pinned))) return rc;
+        }
+        const uint64_t bound = align_up(b2d_deflate_bound(m), 4);
+        CU(cudaMemsetAsync(c->d_out, 0, bound, c->st));
+        CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
+        b2d_job J; fill_job(c, &J, c->d_in, D, m, c->d_in_cap, level, c->d_out);
+        CU(b2d_launch_pipeline(&J, c->st));
+        c->launches += level > 0 ? 6 : 4;
+        CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+        if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_in + D, m, c->st)); c->launches += crc_launches(c->d_in + D, m); }
+        CU(cudaStreamSynchronize(c->st));
+        if (crc) crc_acc = b2d_crc32_dev_finish(c->ck, m, crc_acc);
+        if (adler) { CU(b2d_adler32_dev(c->ck, c->d_in + D, m, adler_acc, &adler_acc, c->st)); c->launches += 2; }
+        const uint64_t got = *c->h_total;
+        if (produced + got + (final ? 2 : 0) > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+        /* device -> caller: direct when pinned, else through the stage */
+        cudaPointerAttributes ot;
+        const bool opinned = cudaPointerGetAttributes(&ot, out) == cudaSuccess && ot.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (opinned) { CU(cudaMemcpyAsync(out + produced, c->d_out, got, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); }
+        else for (uint64_t o = 0; o < got; o += c->h_stage_cap) {
+            const uint64_t k = got - o < c->h_stage_cap ? got - o : c->h_stage_cap;
+            CU(cudaMemcpyAsync(c->h_stage, c->d_out + o, k, cudaMemcpyDeviceToHost, c->st));
+            CU(cudaStreamSynchronize(c->st));
+            memcpy(out + produced + o, c->h_stage, k);
+        }
+        produced += got;
+    }
+    if (n == 0) {
+        if (5 + (final ? 2u : 0u) > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+        static const uint8_t marker[5] = {0, 0, 0, 0xff, 0xff};
+        memcpy(out, marker, 5); produced = 5;
+    }
+    if (final) { out[produced++] = 0x03; out[produced++] = 0x00; }
+    *out_n = produced;
+    if (crc) *crc = crc_acc;
+    if (adler) *adler = adler_acc;
+    return B2D_OK;
+}
+
+extern "C" int b2d_compress_and_crc(b2d_ctx *c, int level, const uint8_t *data, uint64_t n, const uint8_t *dict, uint64_t dict_n,
+                                    uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc) {
+    if (!crc) return fail(B2D_STREAM_ERROR, "null argument");
+    *crc = 0;
+    return b2d_deflate_host(c, level, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr);
+}

@@ -18,7 +18,7 @@
 
 #if defined(__CUDACC__)
 #define B2D_HD __host__ __device__ __forceinline__
-#define B2D_HDN __host__ __device__
+#define B2D_HDN static __host__ __device__
 #else
 #define B2D_HD static inline
 #define B2D_HDN static
@@ -29,6 +29,8 @@
 #define B2D_WINDOW      32768u    /* dictionary halo = DEFLATE window                     */
 #define B2D_SUB         32768u    /* one DEFLATE block per sub-block of input             */
 #define B2D_NSUB        (B2D_BLOCK / B2D_SUB)
+#define B2D_UNIT        1024u     /* parse unit: no token crosses a multiple of this (so   */
+                                  /* every unit is parsed by its own thread); costs <0.2 % */
 #define B2D_MIN_MATCH   4u        /* shortest match ever emitted (hash covers 5 bytes)    */
 #define B2D_MAX_MATCH   258u
 #define B2D_HASH_BITS   14
@@ -42,6 +44,7 @@
 /* worst-case compressed bytes of one device block (stored fallback per
  * sub-block: 3 header bits + pad + LEN/NLEN, + sync marker) */
 #define B2D_BLOCK_BOUND(len) ((len) + 5u * B2D_NSUB + 8u)
+#define B2D_HIST        (B2D_LL_CODES + B2D_D_CODES)   /* 316 counters per sub-block */
 
 /* ---- per-level policy --------------------------------------------------- */
 typedef struct {
@@ -151,12 +154,14 @@ typedef struct {
     uint32_t pad;
 } b2d_plan;
 
-/* per-sub-block parse summary written by the parse stage */
+/* per-sub-block parse summary written by the parse stage.  Sub-block k of a
+ * job covers input bytes [k*B2D_SUB, k*B2D_SUB + in_len) and owns the token
+ * slots tok[k*B2D_SUB ...] (a sub-block never has more tokens than bytes). */
 typedef struct {
-    uint32_t in_start;    /* offset from the device block's start of the first token */
     uint32_t in_len;      /* input bytes covered by this sub-block's tokens      */
-    uint32_t tok_start;   /* index of first token inside the block's token area  */
     uint32_t tok_count;
+    uint32_t bit_off;     /* bit offset of the sub-block inside its device block (scan stage) */
+    uint32_t pad;
 } b2d_subinfo;
 
 #endif /* B2D_COMMON_H */

@@ -125,9 +125,10 @@ B2D_HD uint32_t b2d_fixed_ll_len(uint32_t sym) { return sym < 144u ? 8u : sym < 
 
 /* Build the plan of one sub-block from its histograms.
  * ll_freq must already count the end-of-block symbol (ll_freq[256] == 1).
- * in_len = input bytes the sub-block covers (for the stored alternative). */
+ * in_len = input bytes the sub-block covers (for the stored alternative).
+ * force_stored = level 0 (deflate_stored.c in the reference). */
 B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
-                               b2d_plan *P, b2d_huff_scratch *S) {
+                               b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
     const uint8_t bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
     /* ---- dynamic alternative ---- */
     b2d_huff_lengths(ll_freq, B2D_LL_CODES, 15, S->ll_len, S);
@@ -179,7 +180,7 @@ B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, 
 
     for (int i = 0; i < B2D_HDR_WORDS; i++) P->hdr[i] = 0;
     P->hdr_bits = 0; P->pad = 0;
-    if (sto_cost <= dyn_cost && sto_cost <= fix_cost && in_len <= 65535u) {
+    if ((force_stored || (sto_cost <= dyn_cost && sto_cost <= fix_cost)) && in_len <= 65535u) {
         P->type = 0; P->body_bits = 0;
         b2d_put_bits(P->hdr, &P->hdr_bits, 0u, 3);          /* BFINAL=0, BTYPE=00 */
         for (int i = 0; i < B2D_LL_CODES; i++) P->ll_code[i] = 0;

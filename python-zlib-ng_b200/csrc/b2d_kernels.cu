@@ -1,0 +1,528 @@
+/* b2d_kernels.cu — the sm_100a kernels of the block-parallel DEFLATE pipeline.
+ *
+ * One job = a contiguous device buffer [dict (D bytes) | data (n bytes)].  It is
+ * cut into device blocks of B2D_BLOCK input bytes (each ends byte-aligned with a
+ * sync-flush marker, so blocks concatenate with plain byte copies, exactly like
+ * the outputs of the reference's compress_and_crc, zlib_ngmodule.c:1696-1782)
+ * and each block into B2D_NSUB DEFLATE blocks ("sub-blocks") of B2D_SUB bytes.
+ *
+ * Stages (each a kernel; DESIGN.md §3 has the per-stage byte/roofline figures):
+ *   K1 k_chains  one warp per device block (+32 KiB halo): 5-byte hash, 2^14-entry
+ *                head table in shared memory, warp match.any to order the 32
+ *                positions of a step; writes prevd[p] = distance to the previous
+ *                position with the same hash.        (replaces insert_string /
+ *                deflateSetDictionary priming, insert_string_tpl.h:50-107)
+ *   K2 k_match   one CTA per sub-block: the 32 KiB window + 32 KiB tile and their
+ *                chain links staged in shared memory (192 KiB), one thread per
+ *                position walks `depth` links, 4-byte compares with funnel shifts.
+ *                                                   (replaces longest_match,
+ *                match_tpl.h:31-285, compare256.c)
+ *   K3 k_parse   one CTA per sub-block: one lane per 1 KiB parse unit chases the
+ *                lazy parse through match lengths in shared memory, then all
+ *                threads compact the reached positions into tokens and
+ *                histograms.                        (replaces deflate_quick /
+ *                deflate_medium's decision loop and zng_tr_tally, deflate_p.h:61-86)
+ *   K4 k_plan    one thread per sub-block: length-limited Huffman, header,
+ *                stored/fixed/dynamic choice.       (trees.c:186-552,633-711)
+ *   K5 k_scan    bit offsets of sub-blocks, byte offsets of device blocks.
+ *   K6 k_emit    one CTA per sub-block: per-thread token runs, block scan of bit
+ *                lengths, 64-bit accumulators -> global words; sync marker.
+ *                                                   (compress_block, send_bits,
+ *                zng_tr_stored_block: trees.c:593-740, trees_emit.h:42-225)
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b2d_common.h"
+#include "b2d_huff.h"
+#include "b2d_kernels.h"
+
+#define FULL 0xffffffffu
+
+/* ------------------------------------------------------------------------- */
+/* K1: hash chains                                                            */
+/* ------------------------------------------------------------------------- */
+#define K1_BATCH 512u   /* bytes staged per step group (16 steps of 32 positions) */
+
+__global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n,
+                                               uint64_t buf_readable, uint16_t *__restrict__ prevd) {
+    extern __shared__ __align__(16) uint8_t smem1[];
+    uint16_t *head = reinterpret_cast<uint16_t *>(smem1);                         /* 32 KiB */
+    uint32_t *stage = reinterpret_cast<uint32_t *>(smem1 + 2u * B2D_HASH_SIZE);     /* 2 x 512 B ring */
+    const uint32_t lane = threadIdx.x;
+    const uint64_t b = blockIdx.x;
+    const uint64_t job_end = D + n;
+    const uint64_t start = D + b * (uint64_t)B2D_BLOCK;
+    const uint64_t end = start + B2D_BLOCK < job_end ? start + B2D_BLOCK : job_end;
+    const uint64_t halo = start < B2D_WINDOW ? start : B2D_WINDOW;
+    const uint64_t span_start = start - halo;
+
+    {   /* head[] = 0xffff */
+        uint4 ff = make_uint4(FULL, FULL, FULL, FULL);
+        uint4 *h4 = reinterpret_cast<uint4 *>(head);
+        for (uint32_t i = lane; i < 2u * B2D_HASH_SIZE / 16u; i += 32) h4[i] = ff;
+    }
+    const uint64_t c0 = span_start & ~(uint64_t)(K1_BATCH - 1);
+    const uint64_t rd_lim = buf_readable & ~(uint64_t)15;
+    auto load16 = [&](uint64_t c) -> uint4 {
+        uint64_t off = c + 16u * lane;
+        if (off + 16 <= rd_lim) return __ldg(reinterpret_cast<const uint4 *>(buf + off));
+        return make_uint4(0, 0, 0, 0);
+    };
+    uint4 *stage4 = reinterpret_cast<uint4 *>(stage);
+    /* the batch at byte offset c lives in ring slot (c / 512) & 1 */
+    stage4[(uint32_t)((c0 >> 9) & 1) * 32 + lane] = load16(c0);
+    uint4 nxt = load16(c0 + K1_BATCH);
+    __syncwarp();
+    for (uint64_t c = c0; c < end; c += K1_BATCH) {
+        stage4[(uint32_t)(((c >> 9) + 1) & 1) * 32 + lane] = nxt;
+        nxt = load16(c + 2 * K1_BATCH);
+        __syncwarp();
+#pragma unroll 4
+        for (uint32_t k = 0; k < K1_BATCH / 32; ++k) {
+            const uint64_t q = c + 32u * k + lane;
+            const uint32_t qo = (uint32_t)(q & (2 * K1_BATCH - 1));   /* byte offset in the ring */
+            const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
+            const uint32_t sh = (qo & 3u) << 3;
+            const uint32_t w = __funnelshift_r(w0, w1, sh);
+            const uint32_t b4 = (w1 >> sh) & 0xffu;
+            const uint32_t h = b2d_hash5(w, b4);
+            const bool inspan = q >= span_start && q < end;
+            const bool active = inspan && q + 5 <= job_end;
+            const uint32_t r = (uint32_t)(q - span_start);
+            const uint32_t m = __match_any_sync(FULL, active ? h : (0x10000u | lane));
+            const uint32_t lower = m & ((1u << lane) - 1u);
+            uint32_t d = 0;
+            if (active) {
+                if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
+                else {
+                    uint32_t dd = (r - head[h]) & 0xffffu;
+                    if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
+                }
+            }
+            __syncwarp();
+            if (active && (m >> lane) == 1u) head[h] = (uint16_t)(r & 0xffffu);
+            __syncwarp();
+            if (inspan && (q >= start || b == 0)) prevd[q] = (uint16_t)d;
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* K2: all-position match search                                              */
+/* ------------------------------------------------------------------------- */
+#define K2_THREADS 1024
+#define K2_IN_BYTES (B2D_WINDOW + B2D_SUB + 16u + 288u)   /* +16 align slack, +258+pad look-ahead */
+
+__device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off) {
+    const uint32_t wi = byte_off >> 2;
+    return __funnelshift_r(s32[wi], s32[wi + 1], (byte_off & 3u) << 3);
+}
+
+__global__ void __launch_bounds__(K2_THREADS, 1)
+k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
+        const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice) {
+    extern __shared__ __align__(16) uint8_t smem2[];
+    uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
+    uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES);       /* 2*(W+SUB)+16 */
+    const uint32_t tid = threadIdx.x;
+    const uint64_t k = blockIdx.x;
+    const uint64_t job_end = D + n;
+    const uint64_t tile_start = D + k * (uint64_t)B2D_SUB;
+    const uint64_t tile_end = tile_start + B2D_SUB < job_end ? tile_start + B2D_SUB : job_end;
+    const uint64_t ws = tile_start >= B2D_WINDOW ? tile_start - B2D_WINDOW : 0;
+    const uint64_t ws_al = ws & ~(uint64_t)15;           /* smem byte 0 of s_in   */
+    const uint64_t wp_al = ws & ~(uint64_t)7;            /* element 0 of s_prev   */
+    const uint64_t rd_lim = buf_readable & ~(uint64_t)15;
+    const uint32_t poff = (uint32_t)(wp_al - ws_al);     /* 0 or 8 */
+    {
+        uint4 *d4 = reinterpret_cast<uint4 *>(s_in);
+        const uint32_t n16 = (uint32_t)((tile_end + 272 - ws_al + 15) >> 4);   /* <= K2_IN_BYTES/16 */
+        for (uint32_t i = tid; i < n16; i += K2_THREADS) {
+            uint64_t off = ws_al + 16ull * i;
+            d4[i] = (off + 16 <= rd_lim) ? __ldg(reinterpret_cast<const uint4 *>(buf + off)) : make_uint4(0, 0, 0, 0);
+        }
+        uint4 *p4 = reinterpret_cast<uint4 *>(s_prev);
+        const uint32_t np = (uint32_t)((tile_end - wp_al + 7) >> 3);
+        const uint64_t pd_lim = (job_end + 7) & ~(uint64_t)7;   /* prevd allocation is padded to 8 */
+        for (uint32_t i = tid; i < np; i += K2_THREADS) {
+            uint64_t e = wp_al + 8ull * i;
+            p4[i] = (e + 8 <= pd_lim) ? __ldg(reinterpret_cast<const uint4 *>(prevd + e)) : make_uint4(0, 0, 0, 0);
+        }
+    }
+    __syncthreads();
+    for (uint64_t p = tile_start + tid; p < tile_end; p += K2_THREADS) {
+        const uint64_t rel = p - D;
+        const uint64_t uend = (rel / B2D_UNIT + 1) * B2D_UNIT + D;
+        const uint64_t lim = uend < tile_end ? uend : tile_end;
+        const uint32_t maxl = lim - p < B2D_MAX_MATCH ? (uint32_t)(lim - p) : B2D_MAX_MATCH;
+        uint32_t best = 3, bd = 0;
+        if (maxl >= B2D_MIN_MATCH) {
+            const uint32_t pr = (uint32_t)(p - ws_al);
+            const uint32_t own0 = ldu32(s_in, pr);
+            uint32_t own_end = own0;
+            uint32_t d = s_prev[p - wp_al];
+            uint32_t cand = pr;                            /* smem byte index of the candidate */
+            for (int step = 0; step < depth && d != 0; ++step) {
+                if (d > cand) break;                       /* (cannot happen: links stay inside the window) */
+                cand -= d;
+                const uint32_t dist = pr - cand;
+                if (dist > B2D_WINDOW) break;
+                if (ldu32(s_in, cand + best - 3) == own_end && ldu32(s_in, cand) == own0) {
+                    uint32_t l = 4;
+                    while (l < maxl) {
+                        const uint32_t x = ldu32(s_in, cand + l) ^ ldu32(s_in, pr + l);
+                        if (x) { l += (uint32_t)(__ffs((int)x) - 1) >> 3; break; }
+                        l += 4;
+                    }
+                    if (l > maxl) l = maxl;
+                    if (l > best) {
+                        best = l; bd = dist;
+                        if (l >= nice || l == maxl) break;
+                        own_end = ldu32(s_in, pr + best - 3);
+                    }
+                }
+                d = s_prev[cand - poff];
+            }
+        }
+        match[rel] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* K3: parse + token compaction + histograms                                  */
+/* ------------------------------------------------------------------------- */
+#define K3_THREADS 256
+#define K3_WORDS (B2D_SUB / 32u)      /* bitmap words per sub-block = 1024 */
+
+__global__ void __launch_bounds__(K3_THREADS)
+k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict__ match,
+        uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy) {
+    __shared__ __align__(16) uint8_t s_len[B2D_SUB + 16];
+    __shared__ uint32_t s_reach[K3_WORDS], s_take[K3_WORDS], s_base[K3_WORDS];
+    __shared__ uint32_t s_hist[B2D_HIST];
+    __shared__ uint32_t s_wsum[K3_THREADS / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint64_t k = blockIdx.x;
+    const uint64_t sub_start = k * (uint64_t)B2D_SUB;
+    const uint32_t len = (uint32_t)(n - sub_start < B2D_SUB ? n - sub_start : B2D_SUB);
+    const uint32_t *m = match + sub_start;
+    /* match lengths -> one byte each (len-3, 0 = no match) */
+    for (uint32_t i = tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
+        uint32_t pk = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+            const uint32_t pos = 4 * i + j;
+            const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
+            pk |= (l ? l - 3u : 0u) << (8 * j);
+        }
+        reinterpret_cast<uint32_t *>(s_len)[i] = pk;
+    }
+    for (uint32_t i = tid; i < B2D_HIST; i += K3_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    /* chase: lane u of warp 0 parses unit u */
+    if (warp == 0) {
+        const uint32_t ustart = lane * B2D_UNIT;
+        const uint32_t uend = ustart + B2D_UNIT < len ? ustart + B2D_UNIT : len;
+        uint32_t i = ustart, cw = ustart >> 5, rw = 0, tw = 0;
+        while (i < uend) {
+            const uint32_t l0 = s_len[i], l1 = s_len[i + 1], l2 = s_len[i + 2];
+            uint32_t step = 1;
+            bool take = l0 != 0;
+            if (take && lazy >= 1 && l1 > l0) take = false;
+            if (take && lazy >= 2 && l2 > l0 + 1u) take = false;
+            if (take) step = l0 + 3u;
+            const uint32_t w = i >> 5;
+            if (w != cw) { s_reach[cw] = rw; s_take[cw] = tw; for (uint32_t z = cw + 1; z < w; ++z) { s_reach[z] = 0; s_take[z] = 0; } cw = w; rw = 0; tw = 0; }
+            rw |= 1u << (i & 31u);
+            if (take) tw |= 1u << (i & 31u);
+            i += step;
+        }
+        /* flush and clear the rest of the unit's words */
+        const uint32_t wend = (ustart + B2D_UNIT) >> 5;
+        if (ustart < len) { s_reach[cw] = rw; s_take[cw] = tw; cw++; }
+        for (uint32_t z = cw; z < wend; ++z) { s_reach[z] = 0; s_take[z] = 0; }
+    }
+    __syncthreads();
+    /* exclusive scan of per-word token counts: thread t owns words 4t..4t+3 */
+    uint32_t c[4], tsum = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) { c[j] = __popc(s_reach[4 * tid + j]); tsum += c[j]; }
+    uint32_t incl = tsum;
+#pragma unroll
+    for (uint32_t o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    uint32_t wbase = 0, total = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < K3_THREADS / 32; ++w) { uint32_t v = s_wsum[w]; if (w < warp) wbase += v; total += v; }
+    uint32_t run = wbase + incl - tsum;
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) { s_base[4 * tid + j] = run; run += c[j]; }
+    __syncthreads();
+    /* compaction: warp handles bitmap words warp, warp+8, ... ; lane = bit */
+    uint32_t *t = tok + sub_start;
+    const uint8_t *src = data + sub_start;
+    for (uint32_t w = warp; w < K3_WORDS; w += K3_THREADS / 32) {
+        const uint32_t rw = s_reach[w];
+        if (!rw) continue;
+        const uint32_t pos = 32u * w + lane;
+        if ((rw >> lane) & 1u) {
+            const uint32_t idx = s_base[w] + __popc(rw & ((1u << lane) - 1u));
+            if ((s_take[w] >> lane) & 1u) {
+                const uint32_t mm = __ldg(m + pos);
+                const uint32_t ml = b2d_match_len(mm), md = b2d_match_dist(mm);
+                uint32_t ls, le, lv, ds, de, dv;
+                b2d_len_sym(ml - 3u, &ls, &le, &lv);
+                b2d_dist_sym(md - 1u, &ds, &de, &dv);
+                atomicAdd(&s_hist[257u + ls], 1u);
+                atomicAdd(&s_hist[B2D_LL_CODES + ds], 1u);
+                t[idx] = b2d_tok_match(ml, md);
+            } else {
+                const uint32_t ch = src[pos];
+                atomicAdd(&s_hist[ch], 1u);
+                t[idx] = ch;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (total) s_hist[256] = 1;
+        info[k].in_len = len; info[k].tok_count = total; info[k].bit_off = 0; info[k].pad = 0;
+    }
+    __syncthreads();
+    uint32_t *H = hist + k * (uint64_t)B2D_HIST;
+    for (uint32_t i = tid; i < B2D_HIST; i += K3_THREADS) H[i] = s_hist[i];
+}
+
+/* ------------------------------------------------------------------------- */
+/* K4: Huffman plan per sub-block                                             */
+/* ------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(64)
+k_plan(const uint32_t *__restrict__ hist, const b2d_subinfo *__restrict__ info, b2d_plan *__restrict__ plan,
+       b2d_huff_scratch *__restrict__ scratch, uint32_t nsub, int force_stored) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nsub) return;
+    if (!info[k].tok_count) { plan[k].hdr_bits = 0; plan[k].body_bits = 0; plan[k].type = 1; return; }
+    const uint32_t *H = hist + (uint64_t)k * B2D_HIST;
+    b2d_plan_subblock(H, H + B2D_LL_CODES, info[k].in_len, &plan[k], &scratch[k], force_stored);
+}
+
+/* ------------------------------------------------------------------------- */
+/* K5: offsets                                                                */
+/* ------------------------------------------------------------------------- */
+/* bits the sub-block occupies when it starts at bit offset `at` inside its device block */
+__device__ __forceinline__ uint64_t sub_bits(const b2d_plan &P, const b2d_subinfo &I, uint64_t at) {
+    if (!I.tok_count) return 0;
+    if (P.type == 0) { uint64_t e = (at + P.hdr_bits + 7) & ~7ull; return e + 32 + 8ull * I.in_len - at; }
+    return (uint64_t)P.hdr_bits + P.body_bits;
+}
+
+__global__ void __launch_bounds__(1024)
+k_scan(const b2d_plan *__restrict__ plan, b2d_subinfo *__restrict__ info, uint32_t nsub, uint32_t nblocks,
+       uint64_t *__restrict__ block_off, uint64_t *__restrict__ total) {
+    __shared__ uint64_t s_w[32];
+    __shared__ uint64_t s_carry;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid == 0) s_carry = *total;      /* bytes already produced by earlier batches of this call */
+    __syncthreads();
+    for (uint32_t base = 0; base < nblocks; base += 1024) {
+        const uint32_t b = base + tid;
+        uint64_t bytes = 0;
+        if (b < nblocks) {
+            uint64_t bits = 0;
+            for (uint32_t s = 0; s < B2D_NSUB; ++s) {
+                const uint32_t k = b * B2D_NSUB + s;
+                if (k >= nsub) break;
+                info[k].bit_off = (uint32_t)bits;
+                bits += sub_bits(plan[k], info[k], bits);
+            }
+            bits += 3; bits = (bits + 7) & ~7ull; bits += 32;
+            bytes = bits >> 3;
+        }
+        uint64_t incl = bytes;
+#pragma unroll
+        for (uint32_t o = 1; o < 32; o <<= 1) { uint64_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+        if (lane == 31) s_w[warp] = incl;
+        __syncthreads();
+        uint64_t wb = 0, tot = 0;
+        for (uint32_t w = 0; w < 32; ++w) { uint64_t v = s_w[w]; if (w < warp) wb += v; tot += v; }
+        const uint64_t carry = s_carry;
+        if (b < nblocks) block_off[b] = carry + wb + incl - bytes;
+        __syncthreads();
+        if (tid == 0) s_carry = carry + tot;
+        __syncthreads();
+    }
+    if (tid == 0) { block_off[nblocks] = s_carry; *total = s_carry; }
+}
+
+/* ------------------------------------------------------------------------- */
+/* K6: bit emitter                                                            */
+/* ------------------------------------------------------------------------- */
+#define K6_THREADS 256
+
+struct bitsink {
+    uint32_t *out;       /* zero-initialised output words */
+    uint64_t acc;        /* pending bits, LSB first        */
+    uint32_t fill;       /* valid bits in acc (< 32 after flush) */
+    uint64_t word;       /* index of the word acc's bit 0 belongs to */
+    bool first;
+};
+__device__ __forceinline__ void sink_open(bitsink &s, uint32_t *out, uint64_t bitpos) {
+    s.out = out; s.word = bitpos >> 5; s.fill = (uint32_t)(bitpos & 31u); s.acc = 0; s.first = true;
+}
+__device__ __forceinline__ void sink_put(bitsink &s, uint64_t value, uint32_t count) {   /* count <= 32 */
+    s.acc |= value << s.fill;
+    s.fill += count;
+    if (s.fill >= 32u) {
+        const uint32_t w = (uint32_t)s.acc;
+        if (s.first) { atomicOr(&s.out[s.word], w); s.first = false; } else s.out[s.word] = w;
+        s.word++; s.acc >>= 32; s.fill -= 32u;
+    }
+}
+__device__ __forceinline__ void sink_close(bitsink &s) {
+    if (s.fill) atomicOr(&s.out[s.word], (uint32_t)s.acc);
+}
+
+__device__ __forceinline__ void tok_bits(uint32_t x, const uint32_t *ll, const uint32_t *dc, uint64_t *val, uint32_t *cnt) {
+    if (!b2d_tok_is_match(x)) { const uint32_t c = ll[x]; *val = c & 0xffffu; *cnt = c >> 16; return; }
+    uint32_t ls, le, lv, ds, de, dv;
+    b2d_len_sym(b2d_tok_len3(x), &ls, &le, &lv);
+    b2d_dist_sym(b2d_tok_dist1(x), &ds, &de, &dv);
+    const uint32_t c1 = ll[257u + ls], c2 = dc[ds];
+    uint64_t v = c1 & 0xffffu; uint32_t nb = c1 >> 16;
+    v |= (uint64_t)lv << nb; nb += le;
+    v |= (uint64_t)(c2 & 0xffffu) << nb; nb += c2 >> 16;
+    v |= (uint64_t)dv << nb; nb += de;
+    *val = v; *cnt = nb;                      /* <= 15+5+15+13 = 48 bits */
+}
+
+__global__ void __launch_bounds__(K6_THREADS)
+k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const b2d_subinfo *__restrict__ info,
+       const b2d_plan *__restrict__ plan, const uint64_t *__restrict__ block_off, uint32_t nsub,
+       uint32_t *__restrict__ out) {
+    __shared__ uint32_t s_ll[B2D_LL_CODES], s_d[B2D_D_CODES];
+    __shared__ uint32_t s_wsum[K6_THREADS / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t k = blockIdx.x;
+    const uint32_t b = k / B2D_NSUB;
+    const b2d_subinfo I = info[k];
+    const b2d_plan *P = &plan[k];
+    const uint64_t base = block_off[b] * 8ull + I.bit_off;       /* absolute bit position of this sub-block */
+    const bool last_of_block = (k % B2D_NSUB == B2D_NSUB - 1) || (k == nsub - 1);
+    uint64_t endbit = base;
+    if (I.tok_count) {
+        const uint32_t type = P->type, hdr_bits = P->hdr_bits;
+        /* header bits: thread j places hdr word j */
+        for (uint32_t j = tid; 32u * j < hdr_bits; j += K6_THREADS) {
+            const uint32_t nb = hdr_bits - 32u * j < 32u ? hdr_bits - 32u * j : 32u;
+            uint32_t v = P->hdr[j];
+            if (nb < 32u) v &= (1u << nb) - 1u;
+            const uint64_t bp = base + 32ull * j;
+            const uint32_t sh = (uint32_t)(bp & 31u);
+            atomicOr(&out[bp >> 5], v << sh);
+            if (sh && (v >> (32u - sh))) atomicOr(&out[(bp >> 5) + 1], v >> (32u - sh));
+        }
+        if (type == 0) {
+            /* stored: pad to a byte, LEN, NLEN, raw bytes */
+            const uint64_t hb = ((base + hdr_bits + 7) & ~7ull) >> 3;          /* byte offset of LEN */
+            const uint8_t *src = data + (uint64_t)k * B2D_SUB;
+            const uint32_t L = I.in_len;
+            const uint64_t total = 4ull + L;                                   /* bytes to place from hb */
+            const uint64_t w0 = hb >> 2, w1 = (hb + total + 3) >> 2;
+            for (uint64_t w = w0 + tid; w < w1; w += K6_THREADS) {
+                uint32_t v = 0;
+#pragma unroll
+                for (uint32_t j = 0; j < 4; ++j) {
+                    const uint64_t byte = 4 * w + j;
+                    if (byte < hb || byte >= hb + total) continue;
+                    const uint32_t r = (uint32_t)(byte - hb);
+                    uint32_t x;
+                    if (r == 0) x = L & 0xffu; else if (r == 1) x = (L >> 8) & 0xffu;
+                    else if (r == 2) x = (~L) & 0xffu; else if (r == 3) x = ((~L) >> 8) & 0xffu;
+                    else x = src[r - 4];
+                    v |= x << (8 * j);
+                }
+                if (w == w0 || w == w1 - 1) atomicOr(&out[w], v); else out[w] = v;
+            }
+            endbit = (hb + total) * 8ull;
+        } else {
+            for (uint32_t i = tid; i < B2D_LL_CODES; i += K6_THREADS) s_ll[i] = P->ll_code[i];
+            if (tid < B2D_D_CODES) s_d[tid] = P->d_code[tid];
+            __syncthreads();
+            const uint32_t nt = I.tok_count;
+            const uint32_t per = (nt + K6_THREADS - 1) / K6_THREADS;
+            const uint32_t t0 = tid * per < nt ? tid * per : nt;
+            const uint32_t t1 = t0 + per < nt ? t0 + per : nt;
+            const uint32_t *t = tok + (uint64_t)k * B2D_SUB;
+            uint32_t mybits = 0;
+            for (uint32_t i = t0; i < t1; ++i) { uint64_t v; uint32_t c; tok_bits(__ldg(t + i), s_ll, s_d, &v, &c); mybits += c; }
+            uint32_t incl = mybits;
+#pragma unroll
+            for (uint32_t o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+            if (lane == 31) s_wsum[warp] = incl;
+            __syncthreads();
+            uint32_t wb = 0, tot = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < K6_THREADS / 32; ++w) { uint32_t v = s_wsum[w]; if (w < warp) wb += v; tot += v; }
+            const uint64_t body = base + hdr_bits;
+            if (t1 > t0) {
+                bitsink s; sink_open(s, out, body + wb + incl - mybits);
+                for (uint32_t i = t0; i < t1; ++i) {
+                    uint64_t v; uint32_t c; tok_bits(__ldg(t + i), s_ll, s_d, &v, &c);
+                    if (c > 32u) { sink_put(s, v & 0xffffffffull, 32u); sink_put(s, v >> 32, c - 32u); }
+                    else sink_put(s, v, c);
+                }
+                sink_close(s);
+            }
+            if (tid == 0) {   /* end-of-block code */
+                const uint32_t c = s_ll[256];
+                bitsink s; sink_open(s, out, body + tot); sink_put(s, c & 0xffffu, c >> 16); sink_close(s);
+            }
+            endbit = body + tot + (s_ll[256] >> 16);
+        }
+    }
+    if (last_of_block && tid == 0) {
+        /* sync-flush marker: empty stored block, 000 + pad + 00 00 ff ff (trees.c:593-602) */
+        const uint64_t hb = ((endbit + 3 + 7) & ~7ull) >> 3;
+        const uint64_t bp = (hb + 2) * 8ull;            /* the two 0xff bytes */
+        const uint32_t sh = (uint32_t)(bp & 31u);
+        atomicOr(&out[bp >> 5], 0xffffu << sh);
+        if (sh > 16u) atomicOr(&out[(bp >> 5) + 1], 0xffffu >> (32u - sh));
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* host-side launchers (called from b2d_api.cu)                               */
+/* ------------------------------------------------------------------------- */
+static size_t k1_smem() { return 2u * B2D_HASH_SIZE + 2u * K1_BATCH; }
+static size_t k2_smem() { return K2_IN_BYTES + 2u * (B2D_WINDOW + B2D_SUB) + 32u; }
+
+cudaError_t b2d_kernels_init(void) {
+    cudaError_t e = cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem());
+}
+
+cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st) {
+    const uint64_t n = J->n;
+    if (n == 0) return cudaSuccess;
+    const uint32_t nblocks = (uint32_t)((n + B2D_BLOCK - 1) / B2D_BLOCK);
+    const uint32_t nsub = (uint32_t)((n + B2D_SUB - 1) / B2D_SUB);
+    const b2d_policy pol = b2d_level_policy(J->level);
+    const uint8_t *data = J->buf + J->D;
+    if (J->level > 0) {
+        k_chains<<<nblocks, 32, k1_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd);
+        k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
+                                                    pol.depth, (uint32_t)pol.nice);
+    } else {
+        cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
+        if (e != cudaSuccess) return e;
+    }
+    k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy);
+    k_plan<<<(nsub + 63) / 64, 64, 0, st>>>(J->hist, J->info, J->plan, J->scratch, nsub, J->level == 0);
+    k_scan<<<1, 1024, 0, st>>>(J->plan, J->info, nsub, nblocks, J->block_off, J->total);
+    k_emit<<<nsub, K6_THREADS, 0, st>>>(data, J->tok, J->info, J->plan, J->block_off, nsub,
+                                        reinterpret_cast<uint32_t *>(J->out));
+    return cudaGetLastError();
+}

@@ -72,6 +72,8 @@ def twin():
 
 
 def twin_deflate(data: bytes, level: int, zdict: bytes = b"") -> bytes:
+    if not data:
+        return b"\x00\x00\x00\xff\xff"       # the empty job is only the sync marker
     zdict = zdict[-32768:]
     buf = zdict + data + b"\0" * 64
     cap = len(data) + (len(data) >> 10) + 1024
