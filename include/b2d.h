@@ -55,10 +55,11 @@ int b2d_compress_and_crc(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t 
 /* General host-buffer form used for zlib_ng.compress / compressobj
  * (zlib_compress_impl, zlib_ngmodule.c:199-273; Compress.compress/flush :530-784):
  * same stream as above; `final` != 0 appends the BFINAL empty fixed block 03 00
- * (what gzip_ng_threaded.py:333 appends).  crc / adler may be NULL; adler is the
+ * (what gzip_ng_threaded.py:333 appends).  window_bits (9..15) caps match
+ * distances at 2^window_bits for the small-wbits forms.  crc / adler may be NULL; adler is the
  * Adler-32 of `data` continued from *adler's incoming value, crc likewise. */
-int b2d_deflate_host(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t n, const uint8_t *dict, uint64_t dict_n,
-                     int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler);
+int b2d_deflate_host(b2d_ctx *ctx, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                     uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler);
 
 /* zlib_ng.crc32 / adler32 (zlib_ngmodule.c:1517-1562, 1455-1500) on host bytes */
 int b2d_crc32(b2d_ctx *ctx, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out);

@@ -46,7 +46,7 @@ static void twin_chains(const uint8_t *buf, size_t D, size_t n, size_t b, uint16
 
 /* stage 2 */
 static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const uint16_t *prevd,
-                         uint32_t *match, b2d_policy pol) {
+                         uint32_t *match, b2d_policy pol, uint32_t max_dist) {
     size_t job_end = D + n;
     size_t start = D + b * (size_t)B2D_BLOCK;
     size_t end = start + B2D_BLOCK < job_end ? start + B2D_BLOCK : job_end;
@@ -61,7 +61,7 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
             for (int step = 0; step < pol.depth && d != 0; step++) {
                 cand -= d;
                 size_t dist = p - cand;
-                if (dist > B2D_WINDOW) break;
+                if (dist > max_dist) break;
                 uint32_t l = 0;
                 while (l < maxl && buf[cand + l] == buf[p + l]) l++;
                 if (l > best) { best = l; bd = (uint32_t)dist; if (l >= (uint32_t)pol.nice || l == maxl) break; }
@@ -134,7 +134,7 @@ typedef struct {
 /* Run all stages. buf = [dict (D bytes) | data (n bytes)], readable for B2D_IN_PAD more.
  * Returns compressed size, or 0 if cap is too small. If st_out != NULL the
  * intermediate arrays are handed to the caller (free with b2d_twin_free). */
-size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, uint8_t *out, size_t cap,
+size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, uint32_t max_dist, uint8_t *out, size_t cap,
                            twin_state **st_out) {
     b2d_policy pol = b2d_level_policy(level);
     size_t nb = (n + B2D_BLOCK - 1) / B2D_BLOCK;
@@ -152,7 +152,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     b2d_huff_scratch *scr = (b2d_huff_scratch *)malloc(sizeof *scr);
     if (level > 0) {
         for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head);
-        for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol);
+        for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol, max_dist);
     }
     for (size_t k = 0; k < nsub; k++) twin_parse(buf, D, n, k, S->match, S->tok, S->info, S->hist, pol);
     for (size_t k = 0; k < nsub; k++) {
@@ -223,7 +223,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
 }
 
 size_t b2d_twin_deflate(const uint8_t *buf, size_t D, size_t n, int level, uint8_t *out, size_t cap) {
-    return b2d_twin_deflate_ex(buf, D, n, level, out, cap, NULL);
+    return b2d_twin_deflate_ex(buf, D, n, level, B2D_WINDOW, out, cap, NULL);
 }
 
 void b2d_twin_free(twin_state *S) {

@@ -220,7 +220,9 @@ extern "C" int b2d_adler32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint
 }
 
 /* ---- deflate ---------------------------------------------------------------- */
-static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uint64_t n, uint64_t readable, int level, uint8_t *out) {
+static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uint64_t n, uint64_t readable, int level, uint8_t *out,
+                     uint32_t max_dist = B2D_WINDOW) {
+    J->max_dist = max_dist;
     J->buf = buf; J->D = D; J->n = n; J->buf_readable = readable; J->level = level;
     J->prevd = c->prevd; J->match = c->match; J->tok = c->tok; J->info = c->info; J->hist = c->hist;
     J->plan = c->plan; J->scratch = c->scratch; J->block_off = c->block_off; J->total = c->d_total; J->out = out;
@@ -264,12 +266,15 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     return B2D_OK;
 }
 
-extern "C" int b2d_deflate_host(b2d_ctx *c, int level, const uint8_t *data, uint64_t n, const uint8_t *dict, uint64_t dict_n,
-                                int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler) {
+extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler) {
     if (!c || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
     if (level < 0 || level > 9) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    if (window_bits < 9 || window_bits > 15) return fail(B2D_STREAM_ERROR, "window_bits outside 9..15");
+    const uint32_t max_dist = 1u << window_bits;
     std::lock_guard<std::mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
+    if (dict_n > max_dist) { dict += dict_n - max_dist; dict_n = max_dist; }
     if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
     uint64_t produced = 0;
     uint32_t crc_acc = crc ? *crc : 0, adler_acc = adler ? *adler : 1;
@@ -302,7 +307,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, const uint8_t *data, uint
         const uint64_t bound = align_up(b2d_deflate_bound(m), 4);
         CU(cudaMemsetAsync(c->d_out, 0, bound, c->st));
         CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
-        b2d_job J; fill_job(c, &J, c->d_in, D, m, c->d_in_cap, level, c->d_out);
+        b2d_job J; fill_job(c, &J, c->d_in, D, m, c->d_in_cap, level, c->d_out, max_dist);
         CU(b2d_launch_pipeline(&J, c->st));
         c->launches += level > 0 ? 6 : 4;
         CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
@@ -341,5 +346,5 @@ extern "C" int b2d_compress_and_crc(b2d_ctx *c, int level, const uint8_t *data, 
                                     uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc) {
     if (!crc) return fail(B2D_STREAM_ERROR, "null argument");
     *crc = 0;
-    return b2d_deflate_host(c, level, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr);
+    return b2d_deflate_host(c, level, 15, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr);
 }

@@ -121,7 +121,8 @@ __device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off
 
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
-        const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice) {
+        const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
+        uint32_t max_dist) {
     extern __shared__ __align__(16) uint8_t smem2[];
     uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES);       /* 2*(W+SUB)+16 */
@@ -167,7 +168,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
                 if (d > cand) break;                       /* (cannot happen: links stay inside the window) */
                 cand -= d;
                 const uint32_t dist = pr - cand;
-                if (dist > B2D_WINDOW) break;
+                if (dist > max_dist) break;
                 if (ldu32(s_in, cand + best - 3) == own_end && ldu32(s_in, cand) == own0) {
                     uint32_t l = 4;
                     while (l < maxl) {
@@ -514,7 +515,7 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st) {
     if (J->level > 0) {
         k_chains<<<nblocks, 32, k1_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd);
         k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
-                                                    pol.depth, (uint32_t)pol.nice);
+                                                    pol.depth, (uint32_t)pol.nice, J->max_dist);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
         if (e != cudaSuccess) return e;

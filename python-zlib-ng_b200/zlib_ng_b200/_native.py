@@ -35,7 +35,7 @@ SIGNATURES = {
     "b2d_deflate_bound": (_u64, [_u64]),
     "b2d_compress_and_crc": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
                                             _P(_u64), _P(_u32)]),
-    "b2d_deflate_host": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, ctypes.c_int, _u8p,
+    "b2d_deflate_host": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _u8p, _u64, _u8p, _u64, ctypes.c_int, _u8p,
                                         _u64, _P(_u64), _P(_u32), _P(_u32)]),
     "b2d_crc32": (ctypes.c_int, [ctypes.c_void_p, _u32, _u8p, _u64, _P(_u32)]),
     "b2d_adler32": (ctypes.c_int, [ctypes.c_void_p, _u32, _u8p, _u64, _P(_u32)]),

@@ -1,0 +1,478 @@
+"""Block-parallel gzip writer on B200 — drop-in for ``zlib_ng.gzip_ng_threaded``
+(reference: src/zlib_ng/gzip_ng_threaded.py).
+
+``open(filename, mode, compresslevel, ..., threads=N, block_size=B)`` keeps the
+reference's signature (gzip_ng_threaded.py:22-24).  What changes is what sits
+behind it.  The reference hands ``block_size`` pieces to N CPU threads, each
+calling ``compress_and_crc`` (gzip_ng_threaded.py:299-322, 361-380).  Here
+the writer gathers ``threads * block_size`` bytes straight into *pinned* host
+memory (the only host copy), and one submitter per GPU sends that batch through
+the kernels primed with the 32 KiB before it; the member's CRC is folded with
+crc32_combine exactly as the reference's writer thread does (:382-398).
+Header, terminator ``03 00`` and trailer are the reference's (:269-284,
+:324-338), including its header quirk of packing the OS byte before XFL.
+
+Reading is not on the accelerated path: "rb" goes to CPython's
+gzip module.
+"""
+from __future__ import annotations
+
+import builtins
+import ctypes
+import gzip as _stdgzip
+import io
+import multiprocessing
+import os
+import queue
+import struct
+import threading
+
+from . import _native, zlib_ng
+
+DEFLATE_WINDOW_SIZE = 2 ** 15
+_COMPRESS_LEVEL_TRADEOFF = 6
+_MIN_BATCH = 128 * 1024
+
+
+def open(filename, mode="rb", compresslevel=_COMPRESS_LEVEL_TRADEOFF, encoding=None, errors=None, newline=None,
+         *, threads=1, block_size=1024 * 1024):
+    """Same contract as the reference's open(): returns a BufferedReader,
+    a (flushable) BufferedWriter or a TextIOWrapper.  threads == 0 means the
+    serial writer (gzip_ng.open in the reference); threads < 0 means "all"."""
+    if threads == 0:
+        from . import gzip_ng
+        return gzip_ng.open(filename, mode, compresslevel, encoding, errors, newline)
+    if threads < 0:
+        try:
+            threads = len(os.sched_getaffinity(0))
+        except Exception:
+            try:
+                threads = multiprocessing.cpu_count()
+            except Exception:
+                threads = 1
+    if "r" in mode:
+        gzip_file = io.BufferedReader(_ThreadedGzipReader(filename, block_size=block_size))
+    else:
+        gzip_file = FlushableBufferedWriter(
+            _ThreadedGzipWriter(filename, mode.replace("t", "b"), block_size=block_size, level=compresslevel,
+                                threads=threads),
+            buffer_size=block_size)
+    if "t" in mode:
+        return io.TextIOWrapper(gzip_file, encoding, errors, newline)
+    return gzip_file
+
+
+def open_as_binary_stream(filename, open_mode):
+    if isinstance(filename, (str, bytes)) or hasattr(filename, "__fspath__"):
+        return builtins.open(filename, open_mode), True
+    if hasattr(filename, "read") or hasattr(filename, "write"):
+        return filename, False
+    raise TypeError("filename must be a str or bytes object, or a file")
+
+
+class _ThreadedGzipReader(io.RawIOBase):
+    """Streamed gzip reader.  Inflate is outside the accelerated path; this wraps
+    CPython's GzipFile so that "rb" keeps working for callers of open()."""
+
+    def __init__(self, filename, queue_size=2, block_size=1024 * 1024):
+        self.raw, self.closefd = open_as_binary_stream(filename, "rb")
+        self.fileobj = _stdgzip.GzipFile(fileobj=self.raw, mode="rb")
+        self.pos = 0
+        self._closed = False
+
+    def readinto(self, b):
+        if self._closed:
+            raise ValueError("I/O operation on closed file")
+        n = self.fileobj.readinto(b)
+        self.pos += n
+        return n
+
+    def readable(self) -> bool:
+        return True
+
+    def tell(self) -> int:
+        if self._closed:
+            raise ValueError("I/O operation on closed file")
+        return self.pos
+
+    def close(self) -> None:
+        if self._closed:
+            return
+        self.fileobj.close()
+        if self.closefd:
+            self.raw.close()
+        self._closed = True
+
+    @property
+    def closed(self) -> bool:
+        return self._closed
+
+
+class FlushableBufferedWriter(io.BufferedWriter):
+    def flush(self):
+        super().flush()
+        self.raw.flush()
+
+
+class _PinnedBuffer:
+    """[32 KiB dictionary area | batch bytes] in page-locked host memory."""
+
+    def __init__(self, ctx, batch):
+        self.ctx = ctx
+        self.size = DEFLATE_WINDOW_SIZE + batch
+        self.ptr = ctx.host_alloc(self.size)
+        self.view = memoryview((ctypes.c_char * self.size).from_address(self.ptr)).cast("B")
+        self.fill = 0          # data bytes
+        self.dict_n = 0        # dictionary bytes stored right before the data
+
+    def free(self):
+        if self.ptr:
+            try:
+                self.view.release()
+            except BufferError:
+                pass
+            self.ctx.host_free(self.ptr)
+            self.ptr = 0
+
+
+class _ThreadedGzipWriter(io.RawIOBase):
+    """Batched GPU submitter behind the reference's writer interface."""
+
+    def __init__(self, filename, mode: str = "wb", level: int = zlib_ng.Z_DEFAULT_COMPRESSION, threads: int = 1,
+                 queue_size: int = 1, block_size: int = 1024 * 1024):
+        self._closed = True
+        if "t" in mode or "r" in mode:
+            raise ValueError("Only binary writing is supported")
+        if "b" not in mode:
+            mode += "b"
+        if threads < 1:
+            raise ValueError(f"threads should be at least 1, got {threads}")
+        self.lock = threading.Lock()
+        self._calling_thread = threading.current_thread()
+        self.exception = None
+        self.level = level
+        self._zlevel = zlib_ng._level(level)          # raises zlib_ng.error("Bad compression level")
+        self.block_size = block_size
+        self.threads = threads
+        devices = _devices()
+        self._contexts = [_context_for(d) for d in devices]
+        # one batch = what the reference would have in flight across its threads
+        self.batch = max(block_size * threads // len(devices), 1)
+        self._out_cap = self.batch + max(self.batch // 10, 500)
+        nw = len(devices)
+        self.input_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)]
+        self.output_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)] if nw > 1 else []
+        self._free = queue.Queue()
+        self._buffers = []
+        for i in range(nw * (max(queue_size, 1) + 2)):
+            buf = _PinnedBuffer(self._contexts[i % nw], self.batch)
+            self._buffers.append(buf)
+            self._free.put(buf)
+        self._cur = None
+        self._last_tail = b""
+        self.index = 0
+        self._crc = 0
+        self._size = 0
+        self.running = False
+        if nw > 1:
+            self.compression_workers = [threading.Thread(target=self._compress, args=(i,)) for i in range(nw)]
+            self.output_worker = threading.Thread(target=self._write)
+        else:
+            self.compression_workers = []
+            self.output_worker = threading.Thread(target=self._compress_and_write)
+        self.raw, self.closefd = open_as_binary_stream(filename, mode)
+        self._closed = False
+        self._write_gzip_header()
+        self.start()
+
+    # ---- framing (gzip_ng_threaded.py:269-284, 324-338 in the reference)
+    def _write_gzip_header(self):
+        if self.level == zlib_ng.Z_BEST_COMPRESSION:
+            xfl = 2
+        elif self.level == zlib_ng.Z_BEST_SPEED:
+            xfl = 4
+        else:
+            xfl = 0
+        # the reference packs (…, mtime, os=0xff, xfl): byte 8 = 0xff, byte 9 = xfl
+        self.raw.write(struct.pack("<BBBBIBB", 0x1F, 0x8B, 8, 0, 0, 0xFF, xfl))
+
+    def _check_closed(self, msg=None):
+        if self._closed:
+            raise ValueError("I/O operation on closed file")
+
+    def start(self):
+        self.running = True
+        self.output_worker.start()
+        for w in self.compression_workers:
+            w.start()
+
+    def stop(self):
+        """Stop, but do not care for remaining work"""
+        self.running = False
+        for w in self.compression_workers:
+            w.join()
+        self.output_worker.join()
+        for b in self._buffers:
+            b.free()
+        self._buffers = []
+
+    # ---- producer side
+    def _take_buffer(self):
+        while True:
+            try:
+                buf = self._free.get(timeout=0.05)
+                break
+            except queue.Empty:
+                with self.lock:
+                    if self.exception:
+                        raise self.exception
+                if not self.running:
+                    raise ValueError("writer is not running")
+        tail = self._last_tail
+        buf.dict_n = len(tail)
+        buf.fill = 0
+        if tail:
+            buf.view[DEFLATE_WINDOW_SIZE - len(tail):DEFLATE_WINDOW_SIZE] = tail
+        return buf
+
+    def _submit_current(self):
+        buf = self._cur
+        self._cur = None
+        if buf is None:
+            return
+        if buf.fill == 0 or self.exception:
+            self._free.put(buf)
+            return
+        lo = DEFLATE_WINDOW_SIZE
+        data = buf.view[lo:lo + buf.fill]
+        zdict = buf.view[lo - buf.dict_n:lo]
+        # the next batch is primed with the last 32 KiB of the stream so far
+        both = buf.view[lo - buf.dict_n:lo + buf.fill]
+        self._last_tail = bytes(both[-DEFLATE_WINDOW_SIZE:])
+        worker = self.index % len(self.input_queues)
+        self.index += 1
+        self.input_queues[worker].put((data, zdict, buf))
+
+    def write(self, b) -> int:
+        self._check_closed()
+        with self.lock:
+            if self.exception:
+                raise self.exception
+        mv = memoryview(b)
+        if mv.ndim != 1 or mv.format != "B":
+            mv = mv.cast("B")
+        length = mv.nbytes
+        pos = 0
+        while pos < length:
+            if self._cur is None:
+                self._cur = self._take_buffer()
+            buf = self._cur
+            k = min(length - pos, self.batch - buf.fill)
+            o = DEFLATE_WINDOW_SIZE + buf.fill
+            buf.view[o:o + k] = mv[pos:pos + k]
+            buf.fill += k
+            pos += k
+            if buf.fill == self.batch:
+                self._submit_current()
+        return length
+
+    def _end_gzip_stream(self):
+        self._check_closed()
+        self._submit_current()
+        for q in list(self.input_queues) + list(self.output_queues):
+            self._join(q)
+        with self.lock:
+            if self.exception:
+                return
+        self.raw.write(b"\x03\x00")          # = zlib_ng.compress(b"", wbits=-15): BFINAL fixed block with only EOB
+        self.raw.write(struct.pack("<II", self._crc, self._size & 0xFFFFFFFF))
+        self._crc = 0
+        self._size = 0
+        self._last_tail = b""
+        self.raw.flush()
+
+    def _join(self, q):
+        """queue.join() that gives up once a worker has failed (nobody would drain the queue)"""
+        import time
+        while q.unfinished_tasks:
+            if self.exception or not self.output_worker.is_alive():
+                return
+            time.sleep(0.0005)
+
+    def flush(self):
+        self._end_gzip_stream()
+        with self.lock:
+            if self.exception:
+                raise self.exception
+        self._write_gzip_header()
+
+    def close(self) -> None:
+        if self._closed:
+            return
+        try:
+            self._end_gzip_stream()
+        finally:
+            self.stop()
+        if self.exception:
+            self.raw.close()
+            self._closed = True
+            raise self.exception
+        if self.closefd:
+            self.raw.close()
+        self._closed = True
+
+    @property
+    def closed(self) -> bool:
+        return self._closed
+
+    def writable(self) -> bool:
+        return True
+
+    # ---- consumer side
+    def _alive(self):
+        return self.running and self._calling_thread.is_alive()
+
+    def _run_job(self, index, job, out_buf):
+        data, zdict = job[0], job[1]
+        daddr, n, k1 = _native._addr(data)
+        zaddr, zn, k2 = _native._addr(zdict)
+        out_n = ctypes.c_uint64(0)
+        crc = ctypes.c_uint32(0)
+        ctx = self._contexts[index]
+        rc = _native.lib().b2d_compress_and_crc(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
+                                                out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc))
+        del k1, k2
+        if rc == _native.B2D_BUF_ERROR:
+            raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}")
+        if rc:
+            zlib_ng._raise(rc, "while compressing data")
+        return out_buf.view[:out_n.value], crc.value, n
+
+    def _release(self, job):
+        if len(job) > 2 and job[2] is not None:
+            self._free.put(job[2])
+
+    def _compress_and_write(self):
+        in_queue = self.input_queues[0]
+        out_buf = _OutBuffer(self._contexts[0], self._out_cap)
+        try:
+            while True:
+                try:
+                    job = in_queue.get(timeout=0.05)
+                except queue.Empty:
+                    if not self._alive():
+                        return
+                    continue
+                try:
+                    compressed, crc, n = self._run_job(0, job, out_buf)
+                    self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
+                    self._size += n
+                    self.raw.write(compressed)
+                except Exception as e:
+                    self._release(job)
+                    in_queue.task_done()
+                    self._set_error_and_empty_queue(e, in_queue)
+                    return
+                self._release(job)
+                in_queue.task_done()
+        finally:
+            out_buf.free()
+
+    def _compress(self, index: int):
+        in_queue = self.input_queues[index]
+        out_queue = self.output_queues[index]
+        out_buf = _OutBuffer(self._contexts[index], self._out_cap)
+        try:
+            while True:
+                try:
+                    job = in_queue.get(timeout=0.05)
+                except queue.Empty:
+                    if not self._alive():
+                        return
+                    continue
+                try:
+                    compressed, crc, n = self._run_job(index, job, out_buf)
+                    compressed = bytes(compressed)
+                except Exception as e:
+                    self._release(job)
+                    in_queue.task_done()
+                    self._set_error_and_empty_queue(e, in_queue)
+                    return
+                self._release(job)
+                out_queue.put((compressed, crc, n))
+                in_queue.task_done()
+        finally:
+            out_buf.free()
+
+    def _write(self):
+        index = 0
+        nq = len(self.output_queues)
+        while True:
+            q = self.output_queues[index % nq]
+            try:
+                compressed, crc, n = q.get(timeout=0.05)
+            except queue.Empty:
+                if not self._alive():
+                    return
+                continue
+            try:
+                self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
+                self._size += n
+                self.raw.write(compressed)
+            except Exception as e:
+                q.task_done()
+                self._set_error_and_empty_queue(e, q)
+                return
+            q.task_done()
+            index += 1
+
+    def _set_error_and_empty_queue(self, error, q):
+        with self.lock:
+            self.exception = error
+            self.running = False
+        for qq in list(self.input_queues) + list(self.output_queues):
+            while True:
+                try:
+                    job = qq.get(timeout=0.05)
+                    if qq in self.input_queues:
+                        self._release(job)
+                    qq.task_done()
+                except queue.Empty:
+                    break
+
+
+class _OutBuffer:
+    def __init__(self, ctx, cap):
+        self.ctx = ctx
+        self.cap = max(cap, 16)
+        self.ptr = ctx.host_alloc(self.cap)
+        self.view = memoryview((ctypes.c_char * self.cap).from_address(self.ptr)).cast("B")
+
+    def free(self):
+        if self.ptr:
+            try:
+                self.view.release()
+            except BufferError:
+                pass
+            self.ctx.host_free(self.ptr)
+            self.ptr = 0
+
+
+_ctx_lock = threading.Lock()
+_ctx_by_device = {}
+
+
+def _devices():
+    """GPUs the writer spreads batches over: B2D_DEVICES="0,1,…" or "all"; default device 0."""
+    spec = os.environ.get("B2D_DEVICES", "0").strip()
+    if spec == "all":
+        n = _native.lib().b2d_device_count()
+        return list(range(max(n, 1)))
+    return [int(x) for x in spec.split(",") if x.strip() != ""] or [0]
+
+
+def _context_for(device: int):
+    try:
+        return _native.default_context(device)
+    except _native.NativeError as e:
+        raise zlib_ng.error(f"Error {e.code} while opening the B200 device: {e.msg}") from None

@@ -34,7 +34,7 @@ def deflate_host(nat, ctx, data: bytes, level: int, zdict: bytes = b"", final: b
     n = ctypes.c_uint64(0)
     crc = ctypes.c_uint32(0)
     adler = ctypes.c_uint32(1)
-    rc = L.b2d_deflate_host(ctx.handle, level, data, len(data), zdict, len(zdict), 1 if final else 0,
+    rc = L.b2d_deflate_host(ctx.handle, level, 15, data, len(data), zdict, len(zdict), 1 if final else 0,
                             ctypes.cast(out, ctypes.c_void_p), cap, ctypes.byref(n), ctypes.byref(crc),
                             ctypes.byref(adler))
     nat.check(rc)

@@ -1,0 +1,126 @@
+"""CPU-only tests: the C-ABI library loads and exports what include/b2d.h
+declares, its pure-host functions agree with the oracle and the golden
+vectors, and the CPU twin of the kernels (the byte-for-byte model the GPU tests
+compare against) round-trips and stays within the ratio tolerance of the
+reference's own sizes (tests/golden/reference_vectors.json, produced by the
+reference built from /root/reference)."""
+import os
+import re
+import zlib
+
+import numpy as np
+import pytest
+
+import synthdata
+from helpers import ROOT, golden, oracle, orc_inflate, twin_deflate
+
+
+def _native():
+    from zlib_ng_b200 import _native
+    return _native
+
+
+def test_library_exports_every_declared_symbol():
+    nat = _native()
+    hdr = open(os.path.join(ROOT, "include", "b2d.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(b2d_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    assert declared == set(nat.SIGNATURES), declared ^ set(nat.SIGNATURES)
+    L = nat.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+
+
+def test_no_cpu_fallback_without_a_device():
+    nat = _native()
+    if nat.lib().b2d_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(nat.NativeError) as e:
+        nat.Context(0)
+    assert "no CPU fallback" in str(e.value)
+    from zlib_ng_b200 import zlib_ng
+    with pytest.raises(zlib_ng.error):
+        zlib_ng.crc32(b"abc")
+    with pytest.raises(zlib_ng.error):
+        zlib_ng.compress(b"abc")
+
+
+def test_host_combine_functions():
+    L = _native().lib()
+    O = oracle()
+    for r in golden("reference_vectors.json")["combine"]:
+        assert L.b2d_crc32_combine(r["crc1"], r["crc2"], r["len2"]) == r["expect"]
+    rng = np.random.default_rng(2)
+    data = rng.integers(0, 256, 200_000, dtype=np.uint8).tobytes()
+    for cut in (0, 1, 5552, 65521, 100_000, 199_999, 200_000):
+        a, b = data[:cut], data[cut:]
+        assert L.b2d_crc32_combine(zlib.crc32(a), zlib.crc32(b), len(b)) == zlib.crc32(data)
+        assert L.b2d_adler32_combine(zlib.adler32(a), zlib.adler32(b), len(b)) == zlib.adler32(data)
+        assert L.b2d_adler32_combine(zlib.adler32(a), zlib.adler32(b), len(b)) == \
+            O.orc_adler32_combine(zlib.adler32(a), zlib.adler32(b), len(b))
+    assert L.b2d_adler32_combine(1, 1, -1) == 0xFFFFFFFF
+
+
+def test_deflate_bound_covers_stored_worst_case():
+    L = _native().lib()
+    for n in (0, 1, 32767, 32768, 32769, 131072, 131073, 1 << 20, (1 << 30) + 7):
+        nsub, nblk = -(-n // 32768), max(-(-n // 131072), 1)
+        assert L.b2d_deflate_bound(n) >= n + 5 * nsub + 5 * nblk + 2
+
+
+def test_python_layer_argument_handling_without_gpu():
+    from zlib_ng_b200 import zlib_ng
+    assert zlib_ng.crc32_combine(0, 0, 0) == 0
+    with pytest.raises(TypeError):
+        zlib_ng.crc32_combine("a", 1, 1)
+    assert zlib_ng._wrapper(15) == ("zlib", 15) and zlib_ng._wrapper(-9) == ("raw", 9)
+    assert zlib_ng._wrapper(31) == ("gzip", 15) and zlib_ng._wrapper(8) == ("zlib", 9)
+    with pytest.raises(ValueError):
+        zlib_ng._wrapper(0)
+    with pytest.raises(zlib_ng.error):
+        zlib_ng._level(10)
+    assert zlib_ng._level(-1) == 6
+    assert zlib_ng._gzip_header(9)[8:] == b"\x02\x03" and zlib_ng._gzip_header(1)[8] == 4
+    for lvl, flg in ((1, 0x01), (5, 0x5E), (6, 0x9C), (9, 0xDA)):
+        assert zlib_ng._zlib_header(lvl, 15, b"") == bytes([0x78, flg])
+    # inflate half is served by CPython's zlib
+    assert zlib_ng.decompress(zlib.compress(b"abc")) == b"abc"
+
+
+# ---------------------------------------------------------------- the twin (model of the kernels)
+@pytest.mark.parametrize("kind,n,seed", [("fastq", 300_000, 1), ("mixed", 1_000_000, 2), ("mixed", 131_073, 3)])
+@pytest.mark.parametrize("level", [0, 1, 3, 6, 9])
+def test_twin_round_trips(kind, n, seed, level):
+    data = synthdata.make(kind, n, seed).tobytes()
+    out = twin_deflate(data, level)
+    assert out.endswith(b"\x00\x00\xff\xff")
+    assert orc_inflate(out, n, need_final=False) == data
+    assert zlib.decompressobj(-15).decompress(out) == data
+
+
+def test_twin_with_dictionary():
+    data = synthdata.make("fastq", 400_000, 5).tobytes()
+    zdict, body = data[:150_000], data[150_000:]
+    out = twin_deflate(body, 6, zdict)
+    assert zlib.decompressobj(-15, zdict=zdict[-32768:]).decompress(out) == body
+    assert orc_inflate(out, len(body), zdict=zdict, need_final=False) == body
+    assert len(out) < len(twin_deflate(body, 6))
+
+
+def test_twin_degenerate_inputs():
+    for data in (b"\0" * 200_000, b"a", b"ab" * 40_000, os.urandom(100_000), bytes(range(256)) * 300):
+        for level in (1, 6):
+            assert zlib.decompressobj(-15).decompress(twin_deflate(data, level)) == data
+    rnd = os.urandom(300_000)
+    assert len(twin_deflate(rnd, 6)) <= len(rnd) + 5 * 10 + 5 * 3      # stored fallback
+
+
+@pytest.mark.parametrize("row", [r for r in golden("reference_vectors.json")["sizes"] if r["n"] <= (4 << 20)],
+                         ids=lambda r: f"{r['kind']}{r['seed']}-L{r['level']}")
+def test_ratio_vs_reference_golden(row):
+    """size(ours, level L) <= 1.03 x size(reference, level L, same 128 KiB blocks) — BASELINE.json's tolerance."""
+    data = synthdata.make(row["kind"], row["n"], row["seed"]).tobytes()
+    ours = len(twin_deflate(data, row["level"]))
+    assert ours <= 1.03 * row["threaded_blocks"], (ours, row["threaded_blocks"], ours / row["threaded_blocks"])
+    assert ours <= 1.03 * row["single_stream"]
