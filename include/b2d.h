@@ -87,6 +87,11 @@ int b2d_host_free(b2d_ctx *ctx, void *ptr);
 int b2d_copy_h2d(b2d_ctx *ctx, void *d_dst, const void *h_src, uint64_t bytes);
 int b2d_copy_d2h(b2d_ctx *ctx, void *h_dst, const void *d_src, uint64_t bytes);
 int b2d_device_sync(b2d_ctx *ctx);
+/* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
+ * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit. */
+#define B2D_NSTAGES 6
+int b2d_profile(b2d_ctx *ctx, int enable);
+int b2d_profile_read(b2d_ctx *ctx, double *stage_ms, uint64_t *stage_launches, int reset);
 /* number of this library's kernel launches since the context was created */
 uint64_t b2d_launch_count(b2d_ctx *ctx);
 

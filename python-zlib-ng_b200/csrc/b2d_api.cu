@@ -37,6 +37,7 @@ extern "C" uint64_t b2d_deflate_bound(uint64_t n) {
     return n + 5 * nsub + 5 * (nblk ? nblk : 1) + 2 + 8;
 }
 
+#define PROF_BATCHES 64
 struct b2d_ctx {
     int device;
     uint64_t max_batch;
@@ -54,6 +55,11 @@ struct b2d_ctx {
     uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
     b2d_cksum_ws *ck;
     uint64_t launches;
+    /* optional per-stage timing of device-resident calls */
+    int profiling;
+    cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
+    double stage_ms[B2D_NSTAGE];
+    uint64_t stage_launches[B2D_NSTAGE];
 };
 
 static void ctx_free(b2d_ctx *c) {
@@ -65,6 +71,7 @@ static void ctx_free(b2d_ctx *c) {
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     b2d_cksum_ws_destroy(c->ck);
+    for (int i = 0; i < PROF_BATCHES; ++i) for (int j = 0; j <= B2D_NSTAGE; ++j) if (c->pev[i][j]) cudaEventDestroy(c->pev[i][j]);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -228,6 +235,39 @@ static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uin
     J->plan = c->plan; J->scratch = c->scratch; J->block_off = c->block_off; J->total = c->d_total; J->out = out;
 }
 
+/* fold the event pairs of `nb` profiled batches into the per-stage totals */
+static int prof_drain(b2d_ctx *c, int nb, int level) {
+    CU(cudaStreamSynchronize(c->st));
+    for (int i = 0; i < nb; ++i)
+        for (int j = 0; j < B2D_NSTAGE; ++j) {
+            float t = 0;
+            CU(cudaEventElapsedTime(&t, c->pev[i][j], c->pev[i][j + 1]));
+            c->stage_ms[j] += t;
+            if (level > 0 || j >= 2) c->stage_launches[j] += 1;
+        }
+    return B2D_OK;
+}
+
+extern "C" int b2d_profile(b2d_ctx *c, int enable) {
+    if (!c) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (enable && !c->pev[0][0])
+        for (int i = 0; i < PROF_BATCHES; ++i) for (int j = 0; j <= B2D_NSTAGE; ++j) CU(cudaEventCreate(&c->pev[i][j]));
+    c->profiling = enable ? 1 : 0;
+    return B2D_OK;
+}
+extern "C" int b2d_profile_read(b2d_ctx *c, double *stage_ms, uint64_t *stage_launches, int reset) {
+    if (!c) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    for (int j = 0; j < B2D_NSTAGE; ++j) {
+        if (stage_ms) stage_ms[j] = c->stage_ms[j];
+        if (stage_launches) stage_launches[j] = c->stage_launches[j];
+        if (reset) { c->stage_ms[j] = 0; c->stage_launches[j] = 0; }
+    }
+    return B2D_OK;
+}
+
 extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
                                   uint64_t out_cap, uint64_t *out_n, uint32_t *crc, float *ms) {
     if (!c || !out_n || (!d_buf && n) || !d_out) return fail(B2D_STREAM_ERROR, "null argument");
@@ -241,13 +281,19 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     CU(cudaMemsetAsync(d_out, 0, align_up(b2d_deflate_bound(n), 4) <= out_cap ? align_up(b2d_deflate_bound(n), 4) : out_cap, c->st));
     CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
     const uint64_t readable = dict_n + n + B2D_DEVICE_PAD;
+    int nprof = 0;
     for (uint64_t off = 0; off < n; off += c->max_batch) {
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
         /* re-base so the work buffers are indexed from (at most) 32 KiB + 15 bytes before the batch */
         const uint64_t abs0 = dict_n + off;
         const uint64_t base = abs0 > B2D_WINDOW ? (abs0 - B2D_WINDOW) & ~(uint64_t)15 : 0;
         b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out);
-        CU(b2d_launch_pipeline(&J, c->st));
+        cudaEvent_t *pe = nullptr;
+        if (c->profiling) {
+            if (nprof == PROF_BATCHES) { int rc = prof_drain(c, nprof, level); if (rc) return rc; nprof = 0; }
+            pe = c->pev[nprof++];
+        }
+        CU(b2d_launch_pipeline(&J, c->st, pe));
         c->launches += level > 0 ? 6 : 4;
     }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
@@ -255,6 +301,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
     CU(cudaStreamSynchronize(c->st));
     if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    if (nprof) { int rc = prof_drain(c, nprof, level); if (rc) return rc; }
     if (crc) *crc = n ? b2d_crc32_dev_finish(c->ck, n, 0) : 0;
     *out_n = *c->h_total;
     if (n == 0) {   /* the empty job is just the sync marker: 00 00 00 ff ff */
@@ -308,7 +355,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         CU(cudaMemsetAsync(c->d_out, 0, bound, c->st));
         CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
         b2d_job J; fill_job(c, &J, c->d_in, D, m, c->d_in_cap, level, c->d_out, max_dist);
-        CU(b2d_launch_pipeline(&J, c->st));
+        CU(b2d_launch_pipeline(&J, c->st, nullptr));
         c->launches += level > 0 ? 6 : 4;
         CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
         if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_in + D, m, c->st)); c->launches += crc_launches(c->d_in + D, m); }

@@ -505,25 +505,36 @@ cudaError_t b2d_kernels_init(void) {
     return cudaFuncSetAttribute(k_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem());
 }
 
-cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st) {
+cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev) {
+    /* ev (optional): B2D_NSTAGE + 1 events recorded around the stages, for per-kernel timing */
     const uint64_t n = J->n;
     if (n == 0) return cudaSuccess;
     const uint32_t nblocks = (uint32_t)((n + B2D_BLOCK - 1) / B2D_BLOCK);
     const uint32_t nsub = (uint32_t)((n + B2D_SUB - 1) / B2D_SUB);
     const b2d_policy pol = b2d_level_policy(J->level);
     const uint8_t *data = J->buf + J->D;
-    if (J->level > 0) {
+#define MARK(i) do { if (ev) { cudaError_t e_ = cudaEventRecord(ev[i], st); if (e_ != cudaSuccess) return e_; } } while (0)
+    MARK(0);
+    if (J->level > 0)
         k_chains<<<nblocks, 32, k1_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd);
+    MARK(1);
+    if (J->level > 0) {
         k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
                                                     pol.depth, (uint32_t)pol.nice, J->max_dist);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
         if (e != cudaSuccess) return e;
     }
+    MARK(2);
     k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy);
+    MARK(3);
     k_plan<<<(nsub + 63) / 64, 64, 0, st>>>(J->hist, J->info, J->plan, J->scratch, nsub, J->level == 0);
+    MARK(4);
     k_scan<<<1, 1024, 0, st>>>(J->plan, J->info, nsub, nblocks, J->block_off, J->total);
+    MARK(5);
     k_emit<<<nsub, K6_THREADS, 0, st>>>(data, J->tok, J->info, J->plan, J->block_off, nsub,
                                         reinterpret_cast<uint32_t *>(J->out));
+    MARK(6);
+#undef MARK
     return cudaGetLastError();
 }

@@ -26,7 +26,8 @@ typedef struct {
 } b2d_job;
 
 cudaError_t b2d_kernels_init(void);
-cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st);
+#define B2D_NSTAGE 6   /* chains, match, parse, plan, scan, emit */
+cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev);
 
 /* checksums (b2d_checksum.cu) */
 typedef struct b2d_cksum_ws b2d_cksum_ws;
