@@ -29,6 +29,7 @@ typedef struct {
     uint32_t bl_freq[B2D_BL_CODES];
     uint32_t bl_code[B2D_BL_CODES];
     uint32_t dfix[B2D_D_CODES];
+    int hlit, hdist, hclen, nseq;   /* carried between the phases of b2d_plan_subblock */
 } b2d_huff_scratch;
 
 /* in-place heapsort of n unique u32 keys, ascending */
@@ -61,8 +62,8 @@ B2D_HDN void b2d_sort_keys(uint32_t *a, int n) {
 /* Code lengths for n symbols (n <= 286) with every length <= maxbits.
  * At least two symbols always receive a code (zlib-ng trees.c:341-350 does the
  * same) so the code is never incomplete. */
-B2D_HDN void b2d_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t *lens,
-                              b2d_huff_scratch *S) {
+/* phase 1: one key per used symbol, (freq << 9) | symbol; returns their number (>= 2) */
+B2D_HDN int b2d_huff_keys(const uint32_t *freq, int n, uint8_t *lens, b2d_huff_scratch *S) {
     int m = 0;
     for (int i = 0; i < n; i++) { lens[i] = 0; if (freq[i]) S->key[m++] = (freq[i] << 9) | (uint32_t)i; }
     if (m == 0) { S->key[0] = (1u << 9) | 0u; S->key[1] = (1u << 9) | 1u; m = 2; }
@@ -71,7 +72,11 @@ B2D_HDN void b2d_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t 
         S->key[1] = (1u << 9) | (s == 0u ? 1u : 0u);
         m = 2;
     }
-    b2d_sort_keys(S->key, m);
+    return m;
+}
+
+/* phase 3 (phase 2 = sort S->key[0..m) ascending; keys are unique, so any sort gives the same order) */
+B2D_HDN void b2d_huff_from_sorted(int m, int maxbits, uint8_t *lens, b2d_huff_scratch *S) {
     for (int i = 0; i < m; i++) S->w[i] = S->key[i] >> 9;
     int li = 0, ni = m, nn = m;
     while (nn < 2 * m - 1) {
@@ -97,6 +102,13 @@ B2D_HDN void b2d_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t 
     int k = 0;   /* least frequent symbols take the longest codes */
     for (int b = maxbits; b >= 1; b--)
         for (uint32_t c = 0; c < cnt[b]; c++) lens[S->key[k++] & 511u] = (uint8_t)b;
+}
+
+B2D_HDN void b2d_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t *lens,
+                              b2d_huff_scratch *S) {
+    int m = b2d_huff_keys(freq, n, lens, S);
+    b2d_sort_keys(S->key, m);
+    b2d_huff_from_sorted(m, maxbits, lens, S);
 }
 
 /* canonical codes, bit-reversed, packed (len << 16) | code (RFC 1951 3.2.2) */
@@ -127,12 +139,8 @@ B2D_HD uint32_t b2d_fixed_ll_len(uint32_t sym) { return sym < 144u ? 8u : sym < 
  * ll_freq must already count the end-of-block symbol (ll_freq[256] == 1).
  * in_len = input bytes the sub-block covers (for the stored alternative).
  * force_stored = level 0 (deflate_stored.c in the reference). */
-B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
-                               b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
-    const uint8_t bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
-    /* ---- dynamic alternative ---- */
-    b2d_huff_lengths(ll_freq, B2D_LL_CODES, 15, S->ll_len, S);
-    b2d_huff_lengths(d_freq, B2D_D_CODES, 15, S->d_len, S);
+/* after ll_len / d_len: trailing-zero trimming, run-length coding of the length sequence, bl_freq */
+B2D_HDN void b2d_plan_mid(b2d_huff_scratch *S) {
     int hlit = B2D_LL_CODES; while (hlit > 257 && S->ll_len[hlit - 1] == 0) hlit--;
     int hdist = B2D_D_CODES; while (hdist > 1 && S->d_len[hdist - 1] == 0) hdist--;
     /* run-length encode the concatenated length sequence */
@@ -153,7 +161,14 @@ B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, 
             while (r > 0) { S->seq_sym[nseq] = (uint8_t)v; S->seq_ext[nseq++] = 0; S->bl_freq[v]++; r--; }
         }
     }
-    b2d_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S);
+    S->hlit = hlit; S->hdist = hdist; S->nseq = nseq;
+}
+
+/* after bl_len: costs, stored / fixed / dynamic choice, codes and header bits */
+B2D_HDN void b2d_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
+                          b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
+    const uint8_t bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+    const int hlit = S->hlit, hdist = S->hdist, nseq = S->nseq;
     int hclen = B2D_BL_CODES; while (hclen > 4 && S->bl_len[bl_order[hclen - 1]] == 0) hclen--;
     uint32_t dyn_hdr = 3u + 5u + 5u + 4u + 3u * (uint32_t)hclen;
     for (int i = 0; i < nseq; i++) {
@@ -213,6 +228,15 @@ B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, 
             else if (s == 18u) b2d_put_bits(P->hdr, &P->hdr_bits, S->seq_ext[i], 7);
         }
     }
+}
+
+B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
+                               b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
+    b2d_huff_lengths(ll_freq, B2D_LL_CODES, 15, S->ll_len, S);
+    b2d_huff_lengths(d_freq, B2D_D_CODES, 15, S->d_len, S);
+    b2d_plan_mid(S);
+    b2d_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S);
+    b2d_plan_end(ll_freq, d_freq, in_len, P, S, force_stored);
 }
 
 #endif /* B2D_HUFF_H */

@@ -90,19 +90,34 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
             const bool inspan = q >= span_start && q < end;
             const bool active = inspan && q + 5 <= job_end;
             const uint32_t r = (uint32_t)(q - span_start);
-            const uint32_t m = __match_any_sync(FULL, active ? h : (0x10000u | lane));
-            const uint32_t lower = m & ((1u << lane) - 1u);
+            /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
+             * writes its own position, read back — if every lane still sees its own value no two
+             * lanes share a bucket and `old` is each lane's predecessor.  Otherwise (same hash twice
+             * within 32 bytes: runs, short periods) match.any orders the colliding lanes. */
+            const uint32_t r16 = r & 0xffffu;
+            const uint32_t old = active ? head[h] : 0u;
+            __syncwarp();
+            if (active) head[h] = (uint16_t)r16;
+            __syncwarp();
+            const bool lost = active && head[h] != r16;
             uint32_t d = 0;
-            if (active) {
-                if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
-                else {
-                    uint32_t dd = (r - head[h]) & 0xffffu;
-                    if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
+            if (__any_sync(FULL, lost)) {
+                const uint32_t m = __match_any_sync(FULL, active ? h : (0x10000u | lane));
+                const uint32_t lower = m & ((1u << lane) - 1u);
+                if (active) {
+                    if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
+                    else {
+                        const uint32_t dd = (r - old) & 0xffffu;
+                        if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
+                    }
                 }
+                __syncwarp();
+                if (active && (m >> lane) == 1u) head[h] = (uint16_t)r16;
+                __syncwarp();
+            } else if (active) {
+                const uint32_t dd = (r - old) & 0xffffu;
+                if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
             }
-            __syncwarp();
-            if (active && (m >> lane) == 1u) head[h] = (uint16_t)(r & 0xffffu);
-            __syncwarp();
             if (inspan && (q >= start || b == 0)) prevd[q] = (uint16_t)d;
         }
     }
@@ -299,14 +314,64 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 /* ------------------------------------------------------------------------- */
 /* K4: Huffman plan per sub-block                                             */
 /* ------------------------------------------------------------------------- */
-__global__ void __launch_bounds__(64)
+#define K4_WARPS 8
+struct k4_warp_smem {
+    b2d_huff_scratch S;
+    b2d_plan P;
+    uint32_t hist[B2D_HIST];
+};
+
+/* ascending sort of S->key[0..m) by the whole warp: rank of each (unique) key = number of smaller keys */
+__device__ __forceinline__ void warp_rank_sort(b2d_huff_scratch *S, int m, uint32_t lane) {
+    for (int i = (int)lane; i < m; i += 32) {
+        const uint32_t k = S->key[i];
+        int r = 0;
+        for (int j = 0; j < m; ++j) r += S->key[j] < k;
+        S->w[r] = k;
+    }
+    __syncwarp();
+    for (int i = (int)lane; i < m; i += 32) S->key[i] = S->w[i];
+    __syncwarp();
+}
+
+/* one code-length set: lane 0 builds the keys and runs the serial tree phases, the warp sorts */
+__device__ __forceinline__ void warp_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t *lens,
+                                                  b2d_huff_scratch *S, uint32_t lane) {
+    int m = 0;
+    if (lane == 0) m = b2d_huff_keys(freq, n, lens, S);
+    m = __shfl_sync(FULL, m, 0);
+    __syncwarp();
+    warp_rank_sort(S, m, lane);
+    if (lane == 0) b2d_huff_from_sorted(m, maxbits, lens, S);
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(K4_WARPS * 32)
 k_plan(const uint32_t *__restrict__ hist, const b2d_subinfo *__restrict__ info, b2d_plan *__restrict__ plan,
-       b2d_huff_scratch *__restrict__ scratch, uint32_t nsub, int force_stored) {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+       uint32_t nsub, int force_stored) {
+    extern __shared__ __align__(16) uint8_t smem4[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t k = blockIdx.x * K4_WARPS + warp;
     if (k >= nsub) return;
-    if (!info[k].tok_count) { plan[k].hdr_bits = 0; plan[k].body_bits = 0; plan[k].type = 1; return; }
+    k4_warp_smem *W = reinterpret_cast<k4_warp_smem *>(smem4) + warp;
+    if (!info[k].tok_count) {
+        if (lane == 0) { plan[k].hdr_bits = 0; plan[k].body_bits = 0; plan[k].type = 1; }
+        return;
+    }
     const uint32_t *H = hist + (uint64_t)k * B2D_HIST;
-    b2d_plan_subblock(H, H + B2D_LL_CODES, info[k].in_len, &plan[k], &scratch[k], force_stored);
+    for (uint32_t i = lane; i < B2D_HIST; i += 32) W->hist[i] = H[i];
+    __syncwarp();
+    b2d_huff_scratch *S = &W->S;
+    warp_huff_lengths(W->hist, B2D_LL_CODES, 15, S->ll_len, S, lane);
+    warp_huff_lengths(W->hist + B2D_LL_CODES, B2D_D_CODES, 15, S->d_len, S, lane);
+    if (lane == 0) b2d_plan_mid(S);
+    __syncwarp();
+    warp_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S, lane);
+    if (lane == 0) b2d_plan_end(W->hist, W->hist + B2D_LL_CODES, info[k].in_len, &W->P, S, force_stored);
+    __syncwarp();
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(&W->P);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&plan[k]);
+    for (uint32_t i = lane; i < sizeof(b2d_plan) / 4; i += 32) dst[i] = src[i];
 }
 
 /* ------------------------------------------------------------------------- */
@@ -497,10 +562,13 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 /* host-side launchers (called from b2d_api.cu)                               */
 /* ------------------------------------------------------------------------- */
 static size_t k1_smem() { return 2u * B2D_HASH_SIZE + 2u * K1_BATCH; }
+static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
 static size_t k2_smem() { return K2_IN_BYTES + 2u * (B2D_WINDOW + B2D_SUB) + 32u; }
 
 cudaError_t b2d_kernels_init(void) {
     cudaError_t e = cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k4_smem());
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem());
 }
@@ -528,7 +596,7 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     MARK(2);
     k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy);
     MARK(3);
-    k_plan<<<(nsub + 63) / 64, 64, 0, st>>>(J->hist, J->info, J->plan, J->scratch, nsub, J->level == 0);
+    k_plan<<<(nsub + K4_WARPS - 1) / K4_WARPS, K4_WARPS * 32, k4_smem(), st>>>(J->hist, J->info, J->plan, nsub, J->level == 0);
     MARK(4);
     k_scan<<<1, 1024, 0, st>>>(J->plan, J->info, nsub, nblocks, J->block_off, J->total);
     MARK(5);
