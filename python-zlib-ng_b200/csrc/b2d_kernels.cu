@@ -223,14 +223,20 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     const uint64_t sub_start = k * (uint64_t)B2D_SUB;
     const uint32_t len = (uint32_t)(n - sub_start < B2D_SUB ? n - sub_start : B2D_SUB);
     const uint32_t *m = match + sub_start;
-    /* match lengths -> one byte each (len-3, 0 = no match) */
+    /* match lengths -> one byte each (len-3, 0 = no match); sub_start is a multiple of 4 positions */
     for (uint32_t i = tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
         uint32_t pk = 0;
+        if (4 * i + 4 <= len) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(m) + i);
+            const uint32_t l0 = v.x >> 16, l1 = v.y >> 16, l2 = v.z >> 16, l3 = v.w >> 16;
+            pk = (l0 ? l0 - 3u : 0u) | ((l1 ? l1 - 3u : 0u) << 8) | ((l2 ? l2 - 3u : 0u) << 16) | ((l3 ? l3 - 3u : 0u) << 24);
+        } else {
 #pragma unroll
-        for (uint32_t j = 0; j < 4; ++j) {
-            const uint32_t pos = 4 * i + j;
-            const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
-            pk |= (l ? l - 3u : 0u) << (8 * j);
+            for (uint32_t j = 0; j < 4; ++j) {
+                const uint32_t pos = 4 * i + j;
+                const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
+                pk |= (l ? l - 3u : 0u) << (8 * j);
+            }
         }
         reinterpret_cast<uint32_t *>(s_len)[i] = pk;
     }
@@ -276,18 +282,28 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 #pragma unroll
     for (uint32_t j = 0; j < 4; ++j) { s_base[4 * tid + j] = run; run += c[j]; }
     __syncthreads();
-    /* compaction: warp handles bitmap words warp, warp+8, ... ; lane = bit */
+    /* compaction: a warp takes 4 bitmap words per trip (lane = bit) and issues the global loads of
+     * all four before using any, so their latency overlaps */
     uint32_t *t = tok + sub_start;
     const uint8_t *src = data + sub_start;
-    for (uint32_t w = warp; w < K3_WORDS; w += K3_THREADS / 32) {
-        const uint32_t rw = s_reach[w];
-        if (!rw) continue;
-        const uint32_t pos = 32u * w + lane;
-        if ((rw >> lane) & 1u) {
-            const uint32_t idx = s_base[w] + __popc(rw & ((1u << lane) - 1u));
-            if ((s_take[w] >> lane) & 1u) {
-                const uint32_t mm = __ldg(m + pos);
-                const uint32_t ml = b2d_match_len(mm), md = b2d_match_dist(mm);
+    for (uint32_t w0 = warp * 4u; w0 < K3_WORDS; w0 += (K3_THREADS / 32) * 4u) {
+        uint32_t rw[4], val[4];
+        bool reached[4], take[4];
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+            rw[j] = s_reach[w0 + j];
+            const uint32_t pos = 32u * (w0 + j) + lane;
+            reached[j] = (rw[j] >> lane) & 1u;
+            take[j] = (s_take[w0 + j] >> lane) & 1u;
+            val[j] = 0;
+            if (reached[j]) val[j] = take[j] ? __ldg(m + pos) : (uint32_t)__ldg(src + pos);
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+            if (!reached[j]) continue;
+            const uint32_t idx = s_base[w0 + j] + __popc(rw[j] & ((1u << lane) - 1u));
+            if (take[j]) {
+                const uint32_t ml = b2d_match_len(val[j]), md = b2d_match_dist(val[j]);
                 uint32_t ls, le, lv, ds, de, dv;
                 b2d_len_sym(ml - 3u, &ls, &le, &lv);
                 b2d_dist_sym(md - 1u, &ds, &de, &dv);
@@ -295,9 +311,8 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
                 atomicAdd(&s_hist[B2D_LL_CODES + ds], 1u);
                 t[idx] = b2d_tok_match(ml, md);
             } else {
-                const uint32_t ch = src[pos];
-                atomicAdd(&s_hist[ch], 1u);
-                t[idx] = ch;
+                atomicAdd(&s_hist[val[j]], 1u);
+                t[idx] = val[j];
             }
         }
     }
