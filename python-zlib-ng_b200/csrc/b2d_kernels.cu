@@ -167,41 +167,61 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         }
     }
     __syncthreads();
-    for (uint64_t p = tile_start + tid; p < tile_end; p += K2_THREADS) {
-        const uint64_t rel = p - D;
-        const uint64_t uend = (rel / B2D_UNIT + 1) * B2D_UNIT + D;
-        const uint64_t lim = uend < tile_end ? uend : tile_end;
-        const uint32_t maxl = lim - p < B2D_MAX_MATCH ? (uint32_t)(lim - p) : B2D_MAX_MATCH;
+    const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
+    const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
+    const uint32_t tile_off = (uint32_t)(tile_start - ws_al);
+    uint32_t *mout = match + (tile_start - D);
+    for (uint32_t t = tid; t < tile_len; t += K2_THREADS) {
+        /* no match crosses a parse unit (tile starts are unit-aligned relative to the data) */
+        const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
+        uint32_t maxl = to_unit < to_end ? to_unit : to_end;
+        if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
         uint32_t best = 3, bd = 0;
-        if (maxl >= B2D_MIN_MATCH) {
-            const uint32_t pr = (uint32_t)(p - ws_al);
-            const uint32_t own0 = ldu32(s_in, pr);
-            uint32_t own_end = own0;
-            uint32_t d = s_prev[p - wp_al];
-            uint32_t cand = pr;                            /* smem byte index of the candidate */
-            for (int step = 0; step < depth && d != 0; ++step) {
-                if (d > cand) break;                       /* (cannot happen: links stay inside the window) */
+        const uint32_t pr = tile_off + t;                   /* smem byte index of this position */
+        uint32_t d = s_prev[pr - poff];
+        if (maxl >= B2D_MIN_MATCH && d != 0) {
+            /* the position's first 16 bytes stay in registers: most compares end inside them */
+            uint32_t own[4];
+            {
+                const uint32_t wi = pr >> 2, sh = (pr & 3u) << 3;
+                const uint32_t a0 = s_in[wi], a1 = s_in[wi + 1], a2 = s_in[wi + 2], a3 = s_in[wi + 3], a4 = s_in[wi + 4];
+                own[0] = __funnelshift_r(a0, a1, sh); own[1] = __funnelshift_r(a1, a2, sh);
+                own[2] = __funnelshift_r(a2, a3, sh); own[3] = __funnelshift_r(a3, a4, sh);
+            }
+            uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
+            uint32_t cand = pr;
+            for (int step = 0;;) {
+                if (d > cand) break;                        /* (cannot happen: links stay inside the window) */
                 cand -= d;
                 const uint32_t dist = pr - cand;
                 if (dist > max_dist) break;
-                if (ldu32(s_in, cand + best - 3) == own_end && ldu32(s_in, cand) == own0) {
-                    uint32_t l = 4;
-                    while (l < maxl) {
-                        const uint32_t x = ldu32(s_in, cand + l) ^ ldu32(s_in, pr + l);
-                        if (x) { l += (uint32_t)(__ffs((int)x) - 1) >> 3; break; }
-                        l += 4;
+                if (s_in8[cand + best] == own_b) {
+                    uint32_t l, x;
+                    if ((x = ldu32(s_in, cand) ^ own[0]) != 0) l = 0;
+                    else if ((x = ldu32(s_in, cand + 4) ^ own[1]) != 0) l = 4;
+                    else if ((x = ldu32(s_in, cand + 8) ^ own[2]) != 0) l = 8;
+                    else if ((x = ldu32(s_in, cand + 12) ^ own[3]) != 0) l = 12;
+                    else {
+                        l = 16;
+                        while (l < maxl) {
+                            x = ldu32(s_in, cand + l) ^ ldu32(s_in, pr + l);
+                            if (x) break;
+                            l += 4;
+                        }
                     }
+                    if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
                     if (l > maxl) l = maxl;
                     if (l > best) {
                         best = l; bd = dist;
                         if (l >= nice || l == maxl) break;
-                        own_end = ldu32(s_in, pr + best - 3);
+                        own_b = s_in8[pr + best];
                     }
                 }
                 d = s_prev[cand - poff];
+                if (++step >= depth || d == 0) break;
             }
         }
-        match[rel] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+        mout[t] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
     }
 }
 
