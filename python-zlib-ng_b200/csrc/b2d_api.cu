@@ -54,6 +54,12 @@ struct b2d_ctx {
     uint64_t *h_total;                      /* pinned                                         */
     uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
     b2d_cksum_ws *ck;
+    /* second slot + copy streams: lets b2d_deflate_host overlap H2D(j+1), kernels(j) and D2H(j-1) */
+    uint8_t *d_in2, *d_out2;
+    uint64_t *d_total2;
+    b2d_cksum_ws *ck2;
+    cudaStream_t st_in, st_out;
+    cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
     uint64_t launches;
     /* optional per-stage timing of device-resident calls */
     int profiling;
@@ -67,7 +73,15 @@ static void ctx_free(b2d_ctx *c) {
     cudaSetDevice(c->device);
     cudaFree(c->d_in); cudaFree(c->d_out); cudaFree(c->prevd); cudaFree(c->match); cudaFree(c->tok);
     cudaFree(c->hist); cudaFree(c->info); cudaFree(c->plan); cudaFree(c->scratch); cudaFree(c->block_off);
-    cudaFree(c->d_total);
+    cudaFree(c->d_total); cudaFree(c->d_in2); cudaFree(c->d_out2); cudaFree(c->d_total2);
+    b2d_cksum_ws_destroy(c->ck2);
+    for (int i = 0; i < 2; ++i) {
+        if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
+        if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
+        if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
+    }
+    if (c->st_in) cudaStreamDestroy(c->st_in);
+    if (c->st_out) cudaStreamDestroy(c->st_out);
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     b2d_cksum_ws_destroy(c->ck);
@@ -110,11 +124,12 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     CC(cudaMalloc(&c->scratch, nsub * sizeof(b2d_huff_scratch)));
     CC(cudaMalloc(&c->block_off, (nblk + 1) * sizeof(uint64_t)));
     CC(cudaMalloc(&c->d_total, sizeof(uint64_t)));
-    CC(cudaMallocHost(&c->h_total, sizeof(uint64_t)));
+    CC(cudaMallocHost(&c->h_total, 2 * sizeof(uint64_t)));
     c->h_stage_cap = (B2D_WINDOW + max_batch) > c->d_out_cap ? (B2D_WINDOW + max_batch) : c->d_out_cap;
     if (c->h_stage_cap > (64ull << 20)) c->h_stage_cap = 64ull << 20;   /* staged in pieces */
     CC(cudaMallocHost(&c->h_stage, c->h_stage_cap));
     CC(b2d_cksum_ws_create(&c->ck));
+    /* the second slot is allocated on first use (ensure_second_slot) */
 #undef CC
     *out = c;
     return B2D_OK;
@@ -313,6 +328,85 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     return B2D_OK;
 }
 
+/* second input/output slot, copy streams and events: only callers that stream several batches from
+ * pinned memory pay for them */
+static int ensure_second_slot(b2d_ctx *c) {
+    if (c->d_in2) return B2D_OK;
+    CU(cudaMalloc(&c->d_in2, c->d_in_cap));
+    CU(cudaMalloc(&c->d_out2, c->d_out_cap));
+    CU(cudaMalloc(&c->d_total2, sizeof(uint64_t)));
+    CU(b2d_cksum_ws_create(&c->ck2));
+    CU(cudaStreamCreateWithFlags(&c->st_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->st_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_comp[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_out[i], cudaEventDisableTiming));
+    }
+    return B2D_OK;
+}
+
+/* Pinned host input and output, more than one batch: three-stage software pipeline.
+ *   st_in : H2D of batch j   (waits until the kernels of batch j-2 released the slot)
+ *   st    : kernels + CRC of batch j (waits for its H2D and for the D2H of batch j-2)
+ *   st_out: D2H of batch j-1 (issued once the host knows its size)
+ * The host only blocks on "kernels of batch j-1 done", by which time batch j is already queued. */
+static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                  uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t reserve, uint64_t *produced_out,
+                                  uint32_t *crc_acc) {
+    int rc = ensure_second_slot(c);
+    if (rc) return rc;
+    uint8_t *d_in[2] = {c->d_in, c->d_in2}, *d_out[2] = {c->d_out, c->d_out2};
+    uint64_t *d_total[2] = {c->d_total, c->d_total2};
+    b2d_cksum_ws *ck[2] = {c->ck, c->ck2};
+    const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
+    uint64_t produced = 0;
+    auto finish = [&](uint64_t j) -> int {          /* batch j: wait for its kernels, fold its CRC, start its D2H */
+        const int s = (int)(j & 1);
+        const uint64_t m = (j + 1 == nb) ? n - j * c->max_batch : c->max_batch;
+        CU(cudaEventSynchronize(c->ev_comp[s]));
+        if (crc_acc) *crc_acc = b2d_crc32_dev_finish(ck[s], m, *crc_acc);
+        const uint64_t got = c->h_total[s];
+        if (produced + got + reserve > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+        CU(cudaMemcpyAsync(out + produced, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
+        CU(cudaEventRecord(c->ev_out[s], c->st_out));
+        produced += got;
+        return B2D_OK;
+    };
+    for (uint64_t j = 0; j < nb; ++j) {
+        const int s = (int)(j & 1);
+        const uint64_t off = j * c->max_batch;
+        const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
+        uint64_t D;
+        if (j >= 2) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));      /* slot's input no longer read */
+        if (j == 0) {
+            D = dict_n;
+            if (D) { CU(cudaMemcpyAsync(d_in[s], dict, D, cudaMemcpyHostToDevice, c->st_in)); }
+            CU(cudaMemcpyAsync(d_in[s] + D, data, m, cudaMemcpyHostToDevice, c->st_in));
+        } else {
+            D = B2D_WINDOW;
+            CU(cudaMemcpyAsync(d_in[s], data + off - B2D_WINDOW, B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in));
+        }
+        CU(cudaEventRecord(c->ev_in[s], c->st_in));
+        CU(cudaStreamWaitEvent(c->st, c->ev_in[s], 0));
+        if (j >= 2) CU(cudaStreamWaitEvent(c->st, c->ev_out[s], 0));         /* slot's output already copied out */
+        CU(cudaMemsetAsync(d_out[s], 0, align_up(b2d_deflate_bound(m), 4), c->st));
+        CU(cudaMemsetAsync(d_total[s], 0, sizeof(uint64_t), c->st));
+        b2d_job J; fill_job(c, &J, d_in[s], D, m, c->d_in_cap, level, d_out[s], max_dist);
+        J.total = d_total[s];
+        CU(b2d_launch_pipeline(&J, c->st, nullptr));
+        c->launches += level > 0 ? 6 : 4;
+        CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+        if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, c->st)); c->launches += crc_launches(d_in[s] + D, m); }
+        CU(cudaEventRecord(c->ev_comp[s], c->st));
+        if (j >= 1 && (rc = finish(j - 1))) { cudaDeviceSynchronize(); return rc; }
+    }
+    if ((rc = finish(nb - 1))) { cudaDeviceSynchronize(); return rc; }
+    CU(cudaStreamSynchronize(c->st_out));
+    *produced_out = produced;
+    return B2D_OK;
+}
+
 extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
                                 uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler) {
     if (!c || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
@@ -328,6 +422,20 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
     cudaPointerAttributes at;
     const bool pinned = n && cudaPointerGetAttributes(&at, data) == cudaSuccess && at.type == cudaMemoryTypeHost;
     cudaGetLastError();
+    {
+        cudaPointerAttributes ot;
+        const bool opinned = out && cudaPointerGetAttributes(&ot, out) == cudaSuccess && ot.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (pinned && opinned && !adler && n > c->max_batch) {
+            int rc = deflate_host_pipelined(c, level, max_dist, data, n, dict, dict_n, out, out_cap, final ? 2 : 0, &produced,
+                                            crc ? &crc_acc : nullptr);
+            if (rc) return rc;
+            if (final) { out[produced++] = 0x03; out[produced++] = 0x00; }
+            *out_n = produced;
+            if (crc) *crc = crc_acc;
+            return B2D_OK;
+        }
+    }
     auto h2d = [&](uint8_t *dst, const uint8_t *src, uint64_t bytes, bool src_pinned) -> int {
         if (src_pinned) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st)); return B2D_OK; }
         for (uint64_t o = 0; o < bytes; o += c->h_stage_cap) {

@@ -229,3 +229,33 @@ def test_device_resident_variants(nat, ctx):
         ctx.device_free(d_in)
         ctx.device_free(d_out)
     assert ctx.launch_count() > 0
+
+
+def test_pinned_multi_batch_pipelined_path(nat):
+    """pinned in/out and more than one batch -> the overlapped H2D / kernels / D2H path; same bytes as ever"""
+    L = nat.lib()
+    data = synthdata.make("mixed", 9_000_001, 55).tobytes()
+    zdict = synthdata.make("fastq", 20_000, 56).tobytes()
+    n = len(data)
+    c = nat.Context(0, 1 << 20)
+    cap = int(L.b2d_deflate_bound(n)) + 16
+    h_in, h_out = c.host_alloc(n), c.host_alloc(cap)
+    try:
+        ctypes.memmove(h_in, data, n)
+        for final in (0, 1):
+            out_n, crc = ctypes.c_uint64(0), ctypes.c_uint32(0)
+            nat.check(L.b2d_deflate_host(c.handle, 6, 15, ctypes.c_void_p(h_in), n, zdict, len(zdict), final,
+                                         ctypes.c_void_p(h_out), cap, ctypes.byref(out_n), ctypes.byref(crc), None))
+            got = ctypes.string_at(h_out, out_n.value)
+            want = twin_deflate(data, 6, zdict) + (b"\x03\x00" if final else b"")
+            assert got == want
+            assert crc.value == zlib.crc32(data)
+        # too small an output buffer is reported, not overrun
+        out_n, crc = ctypes.c_uint64(0), ctypes.c_uint32(0)
+        rc = L.b2d_deflate_host(c.handle, 6, 15, ctypes.c_void_p(h_in), n, None, 0, 0, ctypes.c_void_p(h_out), 2_000_000,
+                                ctypes.byref(out_n), ctypes.byref(crc), None)
+        assert rc == nat.B2D_BUF_ERROR
+    finally:
+        c.host_free(h_in)
+        c.host_free(h_out)
+        c.close()
