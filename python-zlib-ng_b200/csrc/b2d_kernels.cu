@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(K3_THREADS)
 k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict__ match,
         uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy) {
     __shared__ __align__(16) uint8_t s_len[B2D_SUB + 16];
-    __shared__ uint32_t s_reach[K3_WORDS], s_take[K3_WORDS], s_base[K3_WORDS];
+    __shared__ uint32_t s_reach[K3_WORDS], s_base[K3_WORDS];
     __shared__ uint32_t s_hist[B2D_HIST];
     __shared__ uint32_t s_wsum[K3_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -261,29 +261,45 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
         reinterpret_cast<uint32_t *>(s_len)[i] = pk;
     }
     for (uint32_t i = tid; i < B2D_HIST; i += K3_THREADS) s_hist[i] = 0;
+    for (uint32_t i = tid; i < K3_WORDS; i += K3_THREADS) s_reach[i] = 0;
     __syncthreads();
-    /* chase: lane u of warp 0 parses unit u */
+    /* lazy rule applied to every position at once (b2d_parse_step): a position keeps its length byte if
+     * a match would be taken there, else 0.  Results sit in registers until every thread has read. */
+    {
+        uint32_t *W = reinterpret_cast<uint32_t *>(s_len);
+        uint32_t outw[B2D_SUB / 4 / K3_THREADS];
+#pragma unroll
+        for (uint32_t r = 0; r < B2D_SUB / 4 / K3_THREADS; ++r) {
+            const uint32_t wi = r * K3_THREADS + tid;
+            const uint32_t a = W[wi], b = W[wi + 1];
+            const uint64_t v = ((uint64_t)b << 32) | a;
+            uint32_t o = 0;
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) {
+                const uint32_t l0 = (uint32_t)(v >> (8 * j)) & 255u, l1 = (uint32_t)(v >> (8 * j + 8)) & 255u,
+                               l2 = (uint32_t)(v >> (8 * j + 16)) & 255u;
+                bool take = l0 != 0;
+                if (lazy >= 1 && l1 > l0) take = false;
+                if (lazy >= 2 && l2 > l0 + 1u) take = false;
+                if (take) o |= l0 << (8 * j);
+            }
+            outw[r] = o;
+        }
+        __syncthreads();
+#pragma unroll
+        for (uint32_t r = 0; r < B2D_SUB / 4 / K3_THREADS; ++r) W[r * K3_THREADS + tid] = outw[r];
+    }
+    __syncthreads();
+    /* chase: lane u of warp 0 walks unit u; one dependent shared load per token */
     if (warp == 0) {
         const uint32_t ustart = lane * B2D_UNIT;
         const uint32_t uend = ustart + B2D_UNIT < len ? ustart + B2D_UNIT : len;
-        uint32_t i = ustart, cw = ustart >> 5, rw = 0, tw = 0;
+        uint32_t i = ustart;
         while (i < uend) {
-            const uint32_t l0 = s_len[i], l1 = s_len[i + 1], l2 = s_len[i + 2];
-            uint32_t step = 1;
-            bool take = l0 != 0;
-            if (take && lazy >= 1 && l1 > l0) take = false;
-            if (take && lazy >= 2 && l2 > l0 + 1u) take = false;
-            if (take) step = l0 + 3u;
-            const uint32_t w = i >> 5;
-            if (w != cw) { s_reach[cw] = rw; s_take[cw] = tw; for (uint32_t z = cw + 1; z < w; ++z) { s_reach[z] = 0; s_take[z] = 0; } cw = w; rw = 0; tw = 0; }
-            rw |= 1u << (i & 31u);
-            if (take) tw |= 1u << (i & 31u);
-            i += step;
+            const uint32_t v = s_len[i];
+            atomicOr(&s_reach[i >> 5], 1u << (i & 31u));
+            i += v ? v + 3u : 1u;
         }
-        /* flush and clear the rest of the unit's words */
-        const uint32_t wend = (ustart + B2D_UNIT) >> 5;
-        if (ustart < len) { s_reach[cw] = rw; s_take[cw] = tw; cw++; }
-        for (uint32_t z = cw; z < wend; ++z) { s_reach[z] = 0; s_take[z] = 0; }
     }
     __syncthreads();
     /* exclusive scan of per-word token counts: thread t owns words 4t..4t+3 */
@@ -314,7 +330,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
             rw[j] = s_reach[w0 + j];
             const uint32_t pos = 32u * (w0 + j) + lane;
             reached[j] = (rw[j] >> lane) & 1u;
-            take[j] = (s_take[w0 + j] >> lane) & 1u;
+            take[j] = s_len[pos] != 0;
             val[j] = 0;
             if (reached[j]) val[j] = take[j] ? __ldg(m + pos) : (uint32_t)__ldg(src + pos);
         }
