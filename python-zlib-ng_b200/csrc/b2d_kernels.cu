@@ -42,6 +42,7 @@
 /* ------------------------------------------------------------------------- */
 /* K1: hash chains                                                            */
 /* ------------------------------------------------------------------------- */
+#define K_NOLINK 0xffffu   /* prevd value of a position without a predecessor: beyond any max_dist */
 #define K1_BATCH 512u   /* bytes staged per step group (16 steps of 32 positions) */
 
 __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n,
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
             if (active) head[h] = (uint16_t)r16;
             __syncwarp();
             const bool lost = active && head[h] != r16;
-            uint32_t d = 0;
+            uint32_t d = K_NOLINK;
             if (__any_sync(FULL, lost)) {
                 const uint32_t m = __match_any_sync(FULL, active ? h : (0x10000u | lane));
                 const uint32_t lower = m & ((1u << lane) - 1u);
@@ -163,7 +164,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         const uint64_t pd_lim = (job_end + 7) & ~(uint64_t)7;   /* prevd allocation is padded to 8 */
         for (uint32_t i = tid; i < np; i += K2_THREADS) {
             uint64_t e = wp_al + 8ull * i;
-            p4[i] = (e + 8 <= pd_lim) ? __ldg(reinterpret_cast<const uint4 *>(prevd + e)) : make_uint4(0, 0, 0, 0);
+            p4[i] = (e + 8 <= pd_lim) ? __ldg(reinterpret_cast<const uint4 *>(prevd + e)) : make_uint4(FULL, FULL, FULL, FULL);
         }
     }
     __syncthreads();
@@ -178,8 +179,10 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
         uint32_t best = 3, bd = 0;
         const uint32_t pr = tile_off + t;                   /* smem byte index of this position */
-        uint32_t d = s_prev[pr - poff];
-        if (maxl >= B2D_MIN_MATCH && d != 0) {
+        /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
+         * pushes the running distance past max_dist, so one compare ends the walk either way */
+        uint32_t dist = s_prev[pr - poff];
+        if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
             /* the position's first 16 bytes stay in registers: most compares end inside them */
             uint32_t own[4];
             {
@@ -189,12 +192,9 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
                 own[2] = __funnelshift_r(a2, a3, sh); own[3] = __funnelshift_r(a3, a4, sh);
             }
             uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
-            uint32_t cand = pr;
-            for (int step = 0;;) {
-                if (d > cand) break;                        /* (cannot happen: links stay inside the window) */
-                cand -= d;
-                const uint32_t dist = pr - cand;
-                if (dist > max_dist) break;
+            int step = depth;
+            do {
+                const uint32_t cand = pr - dist;
                 if (s_in8[cand + best] == own_b) {
                     uint32_t l, x;
                     if ((x = ldu32(s_in, cand) ^ own[0]) != 0) l = 0;
@@ -217,9 +217,8 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
                         own_b = s_in8[pr + best];
                     }
                 }
-                d = s_prev[cand - poff];
-                if (++step >= depth || d == 0) break;
-            }
+                dist += s_prev[cand - poff];
+            } while (--step > 0 && dist <= max_dist);
         }
         mout[t] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
     }
