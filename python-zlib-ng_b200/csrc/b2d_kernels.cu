@@ -71,6 +71,17 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
         return make_uint4(0, 0, 0, 0);
     };
     uint4 *stage4 = reinterpret_cast<uint4 *>(stage);
+    /* positions are handled as 32-bit offsets r from span_start; a batch that starts before the span
+     * (c0 is rounded down) gives wrapped-around offsets that fail every range test */
+    const uint32_t span_len = (uint32_t)(end - span_start);
+    const uint64_t job_rel64 = job_end - span_start;
+    const uint32_t job_rel = job_rel64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)job_rel64;
+    const uint32_t act_len = span_len + 5u <= job_rel ? span_len : (job_rel >= 5u ? job_rel - 4u : 0u);  /* r < act_len: hashable */
+    const uint32_t wlo = b == 0 ? 0u : (uint32_t)halo;          /* first offset this block writes links for */
+    uint16_t *pd = prevd + span_start;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t rel = (uint32_t)(c0 - span_start) + lane;          /* offset of this lane's position in step 0 */
+    uint32_t ring = (uint32_t)(c0 & (2 * K1_BATCH - 1)) + lane;
     /* the batch at byte offset c lives in ring slot (c / 512) & 1 */
     stage4[(uint32_t)((c0 >> 9) & 1) * 32 + lane] = load16(c0);
     uint4 nxt = load16(c0 + K1_BATCH);
@@ -81,45 +92,43 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
         __syncwarp();
 #pragma unroll 4
         for (uint32_t k = 0; k < K1_BATCH / 32; ++k) {
-            const uint64_t q = c + 32u * k + lane;
-            const uint32_t qo = (uint32_t)(q & (2 * K1_BATCH - 1));   /* byte offset in the ring */
+            const uint32_t qo = ring & (2 * K1_BATCH - 1);   /* byte offset in the ring */
             const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
             const uint32_t sh = (qo & 3u) << 3;
-            const uint32_t w = __funnelshift_r(w0, w1, sh);
-            const uint32_t b4 = (w1 >> sh) & 0xffu;
-            const uint32_t h = b2d_hash5(w, b4);
-            const bool inspan = q >= span_start && q < end;
-            const bool active = inspan && q + 5 <= job_end;
-            const uint32_t r = (uint32_t)(q - span_start);
+            const uint32_t h = b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu);
+            const uint32_t r = rel;
+            const bool active = r < act_len;
             /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
              * writes its own position, read back — if every lane still sees its own value no two
-             * lanes share a bucket and `old` is each lane's predecessor.  Otherwise (same hash twice
-             * within 32 bytes: runs, short periods) match.any orders the colliding lanes. */
+             * lanes share a bucket and `old` is each lane's predecessor. */
             const uint32_t r16 = r & 0xffffu;
             const uint32_t old = active ? head[h] : 0u;
             __syncwarp();
             if (active) head[h] = (uint16_t)r16;
             __syncwarp();
             const bool lost = active && head[h] != r16;
-            uint32_t d = K_NOLINK;
+            const uint32_t dd = (r - old) & 0xffffu;
+            uint32_t d = (active && dd != 0 && dd <= r && dd <= B2D_WINDOW) ? dd : K_NOLINK;
             if (__any_sync(FULL, lost)) {
-                const uint32_t m = __match_any_sync(FULL, active ? h : (0x10000u | lane));
-                const uint32_t lower = m & ((1u << lane) - 1u);
-                if (active) {
+                /* Some bucket was hit twice (runs, short periods, small alphabets).  The losers write
+                 * again, so the first winner of such a bucket sees a foreign value too: now every lane
+                 * of a shared bucket knows it.  match.any costs ~12 cycles per distinct key, so only
+                 * those lanes bring their bucket; everyone else shares one dummy key. */
+                if (lost) head[h] = (uint16_t)r16;
+                __syncwarp();
+                const bool shared = active && (lost || head[h] != r16);
+                const uint32_t m = __match_any_sync(FULL, shared ? h : 0x10000u);
+                if (shared) {
+                    const uint32_t lower = m & lt_mask;
                     if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
-                    else {
-                        const uint32_t dd = (r - old) & 0xffffu;
-                        if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
-                    }
                 }
                 __syncwarp();
-                if (active && (m >> lane) == 1u) head[h] = (uint16_t)r16;
+                if (shared && (m >> lane) == 1u) head[h] = (uint16_t)r16;   /* highest lane of the bucket is the head */
                 __syncwarp();
-            } else if (active) {
-                const uint32_t dd = (r - old) & 0xffffu;
-                if (dd != 0 && dd <= r && dd <= B2D_WINDOW) d = dd;
             }
-            if (inspan && (q >= start || b == 0)) prevd[q] = (uint16_t)d;
+            if (r < span_len && r >= wlo) pd[r] = (uint16_t)d;
+            rel += 32u;
+            ring += 32u;
         }
     }
 }
