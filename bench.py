@@ -257,6 +257,12 @@ def main():
     stage_n = (ctypes.c_uint64 * 6)()
     L.b2d_profile_read(ctx.handle, stage_ms, stage_n, 1)
     nat.check(L.b2d_profile(ctx.handle, 0))
+    # the same kernels timed alone (one stream, no overlap between batches): explains the shares
+    nat.check(L.b2d_profile(ctx.handle, 2))
+    device_pass()
+    alone_ms = (ctypes.c_double * 6)()
+    L.b2d_profile_read(ctx.handle, alone_ms, None, 1)
+    nat.check(L.b2d_profile(ctx.handle, 0))
     dev_ms_max = allreduce_max(dist, local, dev_ms)
     value = world * n * a.steps / (dev_ms_max * 1e-3) / 1e9
     ratio = out_n / n
@@ -277,6 +283,7 @@ def main():
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                 "kernel_ms_per_step": {k: v / a.steps for k, v in shares.items()},
+                "kernel_ms_per_step_alone": {STAGES[i]: alone_ms[i] for i in range(6)},
                 "note": "DEFLATE is bound by shared-memory / integer work, not HBM; see DESIGN.md §5"}
 
     # ------------------------------------------------------------------ end to end through the C ABI, host buffers

@@ -31,7 +31,8 @@ extern "C" {
 typedef struct b2d_ctx b2d_ctx;
 
 /* One context = one GPU + its work buffers (sized for `max_batch` input bytes per
- * launch sequence; 0 selects 256 MiB; rounded up to 128 KiB).  Calls on one
+ * launch sequence; 0 selects 256 MiB; rounded up to 128 KiB, then down to a whole
+ * number of chain-stage waves when it spans more than one).  Calls on one
  * context are serialised internally; use one context per GPU.
  * Stands in for ParallelCompress__new__ / zng_deflateInit2 (zlib_ngmodule.c:1617-1674). */
 int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out);
@@ -88,7 +89,10 @@ int b2d_copy_h2d(b2d_ctx *ctx, void *d_dst, const void *h_src, uint64_t bytes);
 int b2d_copy_d2h(b2d_ctx *ctx, void *h_dst, const void *d_src, uint64_t bytes);
 int b2d_device_sync(b2d_ctx *ctx);
 /* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
- * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit. */
+ * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit.
+ * enable = 1 times the kernels as they run in production (consecutive batches of a
+ * call overlap on two streams, so a stage's time includes what it shares the SMs
+ * with); enable = 2 also keeps every batch on one stream (kernels timed alone). */
 #define B2D_NSTAGES 6
 int b2d_profile(b2d_ctx *ctx, int enable);
 int b2d_profile_read(b2d_ctx *ctx, double *stage_ms, uint64_t *stage_launches, int reset);

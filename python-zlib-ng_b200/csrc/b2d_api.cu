@@ -38,6 +38,31 @@ extern "C" uint64_t b2d_deflate_bound(uint64_t n) {
 }
 
 #define PROF_BATCHES 64
+#define B2D_NSLOT 3     /* input/output slots of the host pipeline: one more than compute lanes */
+/* per-batch intermediates of the kernel pipeline.  Two of them ("lanes") let consecutive batches of one
+ * call run on two streams, so one batch's kernels fill the SMs the other's tail waves leave idle. */
+struct b2d_work {
+    uint16_t *prevd; uint32_t *match, *tok, *hist;
+    b2d_subinfo *info; b2d_plan *plan;
+    uint64_t *block_off;
+};
+static void work_free(b2d_work *w) {
+    cudaFree(w->prevd); cudaFree(w->match); cudaFree(w->tok); cudaFree(w->hist); cudaFree(w->info); cudaFree(w->plan);
+    cudaFree(w->block_off);
+    memset(w, 0, sizeof(*w));
+}
+static cudaError_t work_alloc(b2d_work *w, uint64_t max_batch) {
+    const uint64_t nsub = max_batch / B2D_SUB, nblk = max_batch / B2D_BLOCK;
+    cudaError_t e;
+    if ((e = cudaMalloc(&w->prevd, (B2D_WINDOW + max_batch + 64) * sizeof(uint16_t))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->match, max_batch * sizeof(uint32_t))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->tok, max_batch * sizeof(uint32_t))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->hist, nsub * B2D_HIST * sizeof(uint32_t))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->info, nsub * sizeof(b2d_subinfo))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->plan, nsub * sizeof(b2d_plan))) != cudaSuccess) return e;
+    return cudaMalloc(&w->block_off, (nblk + 1) * sizeof(uint64_t));
+}
+
 struct b2d_ctx {
     int device;
     uint64_t max_batch;
@@ -47,19 +72,19 @@ struct b2d_ctx {
     /* work buffers for one batch */
     uint8_t *d_in;  uint64_t d_in_cap;      /* WINDOW + max_batch + pad (host-buffer calls)   */
     uint8_t *d_out; uint64_t d_out_cap;     /* bound(max_batch) rounded (host-buffer calls)   */
-    uint16_t *prevd; uint32_t *match, *tok, *hist;
-    b2d_subinfo *info; b2d_plan *plan; b2d_huff_scratch *scratch;
-    uint64_t *block_off;
+    b2d_work wk[2];                         /* lane 1 is allocated on first use (ensure_second_lane) */
+    cudaStream_t st2;                       /* lane 1's stream (lane 0 runs on st)            */
+    cudaEvent_t ev_scan[2], ev_fork, ev_join;
     uint64_t *d_total;                      /* running output byte offset of a call           */
     uint64_t *h_total;                      /* pinned                                         */
     uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
     b2d_cksum_ws *ck;
     /* second slot + copy streams: lets b2d_deflate_host overlap H2D(j+1), kernels(j) and D2H(j-1) */
-    uint8_t *d_in2, *d_out2;
-    uint64_t *d_total2;
-    b2d_cksum_ws *ck2;
+    uint8_t *d_inx[B2D_NSLOT - 1], *d_outx[B2D_NSLOT - 1];      /* slots 1.. (slot 0 = d_in / d_out / d_total / ck) */
+    uint64_t *d_totalx[B2D_NSLOT - 1];
+    b2d_cksum_ws *ckx[B2D_NSLOT - 1];
     cudaStream_t st_in, st_out;
-    cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
+    cudaEvent_t ev_in[B2D_NSLOT], ev_comp[B2D_NSLOT], ev_out[B2D_NSLOT];
     uint64_t launches;
     /* optional per-stage timing of device-resident calls */
     int profiling;
@@ -71,11 +96,14 @@ struct b2d_ctx {
 static void ctx_free(b2d_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_in); cudaFree(c->d_out); cudaFree(c->prevd); cudaFree(c->match); cudaFree(c->tok);
-    cudaFree(c->hist); cudaFree(c->info); cudaFree(c->plan); cudaFree(c->scratch); cudaFree(c->block_off);
-    cudaFree(c->d_total); cudaFree(c->d_in2); cudaFree(c->d_out2); cudaFree(c->d_total2);
-    b2d_cksum_ws_destroy(c->ck2);
-    for (int i = 0; i < 2; ++i) {
+    cudaFree(c->d_in); cudaFree(c->d_out); work_free(&c->wk[0]); work_free(&c->wk[1]);
+    for (int i = 0; i < 2; ++i) if (c->ev_scan[i]) cudaEventDestroy(c->ev_scan[i]);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->st2) cudaStreamDestroy(c->st2);
+    cudaFree(c->d_total);
+    for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
+    for (int i = 0; i < B2D_NSLOT; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
         if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
         if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
@@ -103,9 +131,13 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     if (max_batch == 0) max_batch = 256ull << 20;
     max_batch = align_up(max_batch, B2D_BLOCK);
     if (max_batch > (2048ull << 20)) return fail(B2D_STREAM_ERROR, "max_batch above 2 GiB");
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail_cuda(e, "cudaSetDevice");
+    {   /* a batch of several waves of the chain stage is rounded down to whole waves (output is unaffected) */
+        const uint64_t wave = b2d_chain_wave_bytes();
+        if (wave && max_batch >= wave) max_batch = max_batch / wave * wave;
+    }
     b2d_ctx *c = new b2d_ctx();
     c->device = device; c->max_batch = max_batch; c->st = nullptr; c->ev0 = c->ev1 = nullptr;
-    const uint64_t nsub = max_batch / B2D_SUB, nblk = max_batch / B2D_BLOCK;
 #define CC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { int rc_ = fail_cuda(e_, #x); ctx_free(c); return rc_; } } while (0)
     CC(cudaSetDevice(device));
     CC(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
@@ -115,16 +147,9 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     c->d_out_cap = align_up(b2d_deflate_bound(max_batch), 256);
     CC(cudaMalloc(&c->d_in, c->d_in_cap));
     CC(cudaMalloc(&c->d_out, c->d_out_cap));
-    CC(cudaMalloc(&c->prevd, (B2D_WINDOW + max_batch + 64) * sizeof(uint16_t)));
-    CC(cudaMalloc(&c->match, max_batch * sizeof(uint32_t)));
-    CC(cudaMalloc(&c->tok, max_batch * sizeof(uint32_t)));
-    CC(cudaMalloc(&c->hist, nsub * B2D_HIST * sizeof(uint32_t)));
-    CC(cudaMalloc(&c->info, nsub * sizeof(b2d_subinfo)));
-    CC(cudaMalloc(&c->plan, nsub * sizeof(b2d_plan)));
-    CC(cudaMalloc(&c->scratch, nsub * sizeof(b2d_huff_scratch)));
-    CC(cudaMalloc(&c->block_off, (nblk + 1) * sizeof(uint64_t)));
+    CC(work_alloc(&c->wk[0], max_batch));
     CC(cudaMalloc(&c->d_total, sizeof(uint64_t)));
-    CC(cudaMallocHost(&c->h_total, 2 * sizeof(uint64_t)));
+    CC(cudaMallocHost(&c->h_total, (B2D_NSLOT + 1) * sizeof(uint64_t)));
     c->h_stage_cap = (B2D_WINDOW + max_batch) > c->d_out_cap ? (B2D_WINDOW + max_batch) : c->d_out_cap;
     if (c->h_stage_cap > (64ull << 20)) c->h_stage_cap = 64ull << 20;   /* staged in pieces */
     CC(cudaMallocHost(&c->h_stage, c->h_stage_cap));
@@ -243,16 +268,30 @@ extern "C" int b2d_adler32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint
 
 /* ---- deflate ---------------------------------------------------------------- */
 static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uint64_t n, uint64_t readable, int level, uint8_t *out,
-                     uint32_t max_dist = B2D_WINDOW) {
+                     uint32_t max_dist = B2D_WINDOW, int lane = 0) {
+    const b2d_work *w = &c->wk[lane];
     J->max_dist = max_dist;
     J->buf = buf; J->D = D; J->n = n; J->buf_readable = readable; J->level = level;
-    J->prevd = c->prevd; J->match = c->match; J->tok = c->tok; J->info = c->info; J->hist = c->hist;
-    J->plan = c->plan; J->scratch = c->scratch; J->block_off = c->block_off; J->total = c->d_total; J->out = out;
+    J->prevd = w->prevd; J->match = w->match; J->tok = w->tok; J->info = w->info; J->hist = w->hist;
+    J->plan = w->plan; J->block_off = w->block_off; J->total = c->d_total; J->out = out;
+    J->scan_wait = nullptr; J->scan_done = nullptr;
+}
+
+/* second set of intermediates + its stream: only multi-batch calls pay for them */
+static int ensure_second_lane(b2d_ctx *c) {
+    if (c->st2) return B2D_OK;
+    CU(work_alloc(&c->wk[1], c->max_batch));
+    for (int i = 0; i < 2; ++i) CU(cudaEventCreateWithFlags(&c->ev_scan[i], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&c->st2, cudaStreamNonBlocking));
+    return B2D_OK;
 }
 
 /* fold the event pairs of `nb` profiled batches into the per-stage totals */
 static int prof_drain(b2d_ctx *c, int nb, int level) {
     CU(cudaStreamSynchronize(c->st));
+    if (c->st2) CU(cudaStreamSynchronize(c->st2));
     for (int i = 0; i < nb; ++i)
         for (int j = 0; j < B2D_NSTAGE; ++j) {
             float t = 0;
@@ -269,7 +308,7 @@ extern "C" int b2d_profile(b2d_ctx *c, int enable) {
     CU(cudaSetDevice(c->device));
     if (enable && !c->pev[0][0])
         for (int i = 0; i < PROF_BATCHES; ++i) for (int j = 0; j <= B2D_NSTAGE; ++j) CU(cudaEventCreate(&c->pev[i][j]));
-    c->profiling = enable ? 1 : 0;
+    c->profiling = enable == 2 ? 2 : (enable ? 1 : 0);
     return B2D_OK;
 }
 extern "C" int b2d_profile_read(b2d_ctx *c, double *stage_ms, uint64_t *stage_launches, int reset) {
@@ -297,20 +336,32 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
     const uint64_t readable = dict_n + n + B2D_DEVICE_PAD;
     int nprof = 0;
-    for (uint64_t off = 0; off < n; off += c->max_batch) {
+    /* several batches alternate between two lanes (streams + intermediates); b2d_profile(ctx, 2) keeps
+     * one lane so that the stage times are those of kernels running alone */
+    const bool two = n > c->max_batch && c->profiling != 2;
+    if (two) {
+        int rc = ensure_second_lane(c); if (rc) return rc;
+        CU(cudaEventRecord(c->ev_fork, c->st));
+        CU(cudaStreamWaitEvent(c->st2, c->ev_fork, 0));
+    }
+    uint64_t jb = 0;
+    for (uint64_t off = 0; off < n; off += c->max_batch, ++jb) {
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
+        const int lane = two ? (int)(jb & 1) : 0;
         /* re-base so the work buffers are indexed from (at most) 32 KiB + 15 bytes before the batch */
         const uint64_t abs0 = dict_n + off;
         const uint64_t base = abs0 > B2D_WINDOW ? (abs0 - B2D_WINDOW) & ~(uint64_t)15 : 0;
-        b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out);
+        b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out, B2D_WINDOW, lane);
+        if (two) { J.scan_wait = jb ? c->ev_scan[lane ^ 1] : nullptr; J.scan_done = c->ev_scan[lane]; }
         cudaEvent_t *pe = nullptr;
         if (c->profiling) {
             if (nprof == PROF_BATCHES) { int rc = prof_drain(c, nprof, level); if (rc) return rc; nprof = 0; }
             pe = c->pev[nprof++];
         }
-        CU(b2d_launch_pipeline(&J, c->st, pe));
+        CU(b2d_launch_pipeline(&J, lane ? c->st2 : c->st, pe));
         c->launches += level > 0 ? 6 : 4;
     }
+    if (two) { CU(cudaEventRecord(c->ev_join, c->st2)); CU(cudaStreamWaitEvent(c->st, c->ev_join, 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
     CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
@@ -331,14 +382,16 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
 /* second input/output slot, copy streams and events: only callers that stream several batches from
  * pinned memory pay for them */
 static int ensure_second_slot(b2d_ctx *c) {
-    if (c->d_in2) return B2D_OK;
-    CU(cudaMalloc(&c->d_in2, c->d_in_cap));
-    CU(cudaMalloc(&c->d_out2, c->d_out_cap));
-    CU(cudaMalloc(&c->d_total2, sizeof(uint64_t)));
-    CU(b2d_cksum_ws_create(&c->ck2));
+    if (c->st_in) return B2D_OK;
+    for (int i = 0; i < B2D_NSLOT - 1; ++i) {
+        CU(cudaMalloc(&c->d_inx[i], c->d_in_cap));
+        CU(cudaMalloc(&c->d_outx[i], c->d_out_cap));
+        CU(cudaMalloc(&c->d_totalx[i], sizeof(uint64_t)));
+        CU(b2d_cksum_ws_create(&c->ckx[i]));
+    }
     CU(cudaStreamCreateWithFlags(&c->st_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&c->st_out, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < B2D_NSLOT; ++i) {
         CU(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_comp[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_out[i], cudaEventDisableTiming));
@@ -347,22 +400,26 @@ static int ensure_second_slot(b2d_ctx *c) {
 }
 
 /* Pinned host input and output, more than one batch: three-stage software pipeline.
- *   st_in : H2D of batch j   (waits until the kernels of batch j-2 released the slot)
- *   st    : kernels + CRC of batch j (waits for its H2D and for the D2H of batch j-2)
+ *   st_in : H2D of batch j into slot j % 3 (waits until the kernels of batch j-3 released the slot)
+ *   st/st2: kernels + CRC of batch j on lane j & 1 (waits for its H2D and for the D2H of batch j-3);
+ *           consecutive batches overlap, which fills the tail waves of each other's kernels
  *   st_out: D2H of batch j-1 (issued once the host knows its size)
- * The host only blocks on "kernels of batch j-1 done", by which time batch j is already queued. */
+ * The host only blocks on "kernels of batch j-2 done", by which time batches j-1 and j are already queued. */
 static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, const uint8_t *data, uint64_t n, const uint8_t *dict,
                                   uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t reserve, uint64_t *produced_out,
                                   uint32_t *crc_acc) {
     int rc = ensure_second_slot(c);
     if (rc) return rc;
-    uint8_t *d_in[2] = {c->d_in, c->d_in2}, *d_out[2] = {c->d_out, c->d_out2};
-    uint64_t *d_total[2] = {c->d_total, c->d_total2};
-    b2d_cksum_ws *ck[2] = {c->ck, c->ck2};
+    if ((rc = ensure_second_lane(c))) return rc;
+    cudaStream_t cs[2] = {c->st, c->st2};       /* batch j computes on lane j & 1 */
+    uint8_t *d_in[B2D_NSLOT] = {c->d_in}, *d_out[B2D_NSLOT] = {c->d_out};
+    uint64_t *d_total[B2D_NSLOT] = {c->d_total};
+    b2d_cksum_ws *ck[B2D_NSLOT] = {c->ck};
+    for (int i = 1; i < B2D_NSLOT; ++i) { d_in[i] = c->d_inx[i - 1]; d_out[i] = c->d_outx[i - 1]; d_total[i] = c->d_totalx[i - 1]; ck[i] = c->ckx[i - 1]; }
     const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
     uint64_t produced = 0;
     auto finish = [&](uint64_t j) -> int {          /* batch j: wait for its kernels, fold its CRC, start its D2H */
-        const int s = (int)(j & 1);
+        const int s = (int)(j % B2D_NSLOT);
         const uint64_t m = (j + 1 == nb) ? n - j * c->max_batch : c->max_batch;
         CU(cudaEventSynchronize(c->ev_comp[s]));
         if (crc_acc) *crc_acc = b2d_crc32_dev_finish(ck[s], m, *crc_acc);
@@ -374,11 +431,12 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         return B2D_OK;
     };
     for (uint64_t j = 0; j < nb; ++j) {
-        const int s = (int)(j & 1);
+        const int s = (int)(j % B2D_NSLOT);
+        const int ln = (int)(j & 1);          /* compute lane */
         const uint64_t off = j * c->max_batch;
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
         uint64_t D;
-        if (j >= 2) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));      /* slot's input no longer read */
+        if (j >= B2D_NSLOT) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));      /* slot's input no longer read */
         if (j == 0) {
             D = dict_n;
             if (D) { CU(cudaMemcpyAsync(d_in[s], dict, D, cudaMemcpyHostToDevice, c->st_in)); }
@@ -388,19 +446,21 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
             CU(cudaMemcpyAsync(d_in[s], data + off - B2D_WINDOW, B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in));
         }
         CU(cudaEventRecord(c->ev_in[s], c->st_in));
-        CU(cudaStreamWaitEvent(c->st, c->ev_in[s], 0));
-        if (j >= 2) CU(cudaStreamWaitEvent(c->st, c->ev_out[s], 0));         /* slot's output already copied out */
-        CU(cudaMemsetAsync(d_out[s], 0, align_up(b2d_deflate_bound(m), 4), c->st));
-        CU(cudaMemsetAsync(d_total[s], 0, sizeof(uint64_t), c->st));
-        b2d_job J; fill_job(c, &J, d_in[s], D, m, c->d_in_cap, level, d_out[s], max_dist);
+        CU(cudaStreamWaitEvent(cs[ln], c->ev_in[s], 0));
+        if (j >= B2D_NSLOT) CU(cudaStreamWaitEvent(cs[ln], c->ev_out[s], 0));         /* slot's output already copied out */
+        CU(cudaMemsetAsync(d_out[s], 0, align_up(b2d_deflate_bound(m), 4), cs[ln]));
+        CU(cudaMemsetAsync(d_total[s], 0, sizeof(uint64_t), cs[ln]));
+        b2d_job J; fill_job(c, &J, d_in[s], D, m, c->d_in_cap, level, d_out[s], max_dist, ln);
         J.total = d_total[s];
-        CU(b2d_launch_pipeline(&J, c->st, nullptr));
+        CU(b2d_launch_pipeline(&J, cs[ln], nullptr));
         c->launches += level > 0 ? 6 : 4;
-        CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
-        if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, c->st)); c->launches += crc_launches(d_in[s] + D, m); }
-        CU(cudaEventRecord(c->ev_comp[s], c->st));
-        if (j >= 1 && (rc = finish(j - 1))) { cudaDeviceSynchronize(); return rc; }
+        CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
+        if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
+        CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
+        /* the host trails by two batches: j-1 and j stay queued on the two lanes while it waits for j-2 */
+        if (j >= 2 && (rc = finish(j - 2))) { cudaDeviceSynchronize(); return rc; }
     }
+    if (nb >= 2 && (rc = finish(nb - 2))) { cudaDeviceSynchronize(); return rc; }
     if ((rc = finish(nb - 1))) { cudaDeviceSynchronize(); return rc; }
     CU(cudaStreamSynchronize(c->st_out));
     *produced_out = produced;

@@ -202,9 +202,12 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
             }
             uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
             int step = depth;
+            const uint32_t lp = pr - poff;
+            uint32_t cb = pr + best;                        /* own_b's index; the candidate's is cb - dist */
             do {
-                const uint32_t cand = pr - dist;
-                if (s_in8[cand + best] == own_b) {
+                const uint32_t nd = s_prev[lp - dist];      /* next link: independent of the byte test below */
+                if (s_in8[cb - dist] == own_b) {
+                    const uint32_t cand = pr - dist;
                     uint32_t l, x;
                     if ((x = ldu32(s_in, cand) ^ own[0]) != 0) l = 0;
                     else if ((x = ldu32(s_in, cand + 4) ^ own[1]) != 0) l = 4;
@@ -223,10 +226,11 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
                     if (l > best) {
                         best = l; bd = dist;
                         if (l >= nice || l == maxl) break;
-                        own_b = s_in8[pr + best];
+                        cb = pr + best;
+                        own_b = s_in8[cb];
                     }
                 }
-                dist += s_prev[cand - poff];
+                dist += nd;
             } while (--step > 0 && dist <= max_dist);
         }
         mout[t] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
@@ -632,6 +636,16 @@ cudaError_t b2d_kernels_init(void) {
     return cudaFuncSetAttribute(k_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem());
 }
 
+/* input bytes one full wave of k_chains covers (resident warps on the device x B2D_BLOCK); batches
+ * that are a whole number of waves avoid a mostly-empty last wave in the longest-running stage */
+uint64_t b2d_chain_wave_bytes(void) {
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chains, 32, k1_smem()) != cudaSuccess) return 0;
+    return (uint64_t)sms * (uint64_t)per_sm * B2D_BLOCK;
+}
+
 cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev) {
     /* ev (optional): B2D_NSTAGE + 1 events recorded around the stages, for per-kernel timing */
     const uint64_t n = J->n;
@@ -657,7 +671,9 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     MARK(3);
     k_plan<<<(nsub + K4_WARPS - 1) / K4_WARPS, K4_WARPS * 32, k4_smem(), st>>>(J->hist, J->info, J->plan, nsub, J->level == 0);
     MARK(4);
+    if (J->scan_wait) { cudaError_t e = cudaStreamWaitEvent(st, J->scan_wait, 0); if (e != cudaSuccess) return e; }
     k_scan<<<1, 1024, 0, st>>>(J->plan, J->info, nsub, nblocks, J->block_off, J->total);
+    if (J->scan_done) { cudaError_t e = cudaEventRecord(J->scan_done, st); if (e != cudaSuccess) return e; }
     MARK(5);
     k_emit<<<nsub, K6_THREADS, 0, st>>>(data, J->tok, J->info, J->plan, J->block_off, nsub,
                                         reinterpret_cast<uint32_t *>(J->out));

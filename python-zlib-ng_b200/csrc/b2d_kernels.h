@@ -19,14 +19,17 @@ typedef struct {
     b2d_subinfo *info;         /* [nsub]                                            */
     uint32_t *hist;            /* [nsub * B2D_HIST]                                 */
     b2d_plan *plan;            /* [nsub]                                            */
-    b2d_huff_scratch *scratch; /* [nsub]                                            */
     uint64_t *block_off;       /* [nblocks + 1] byte offsets into out               */
     uint64_t *total;           /* device: in = bytes of out already used, out = after this job */
     uint8_t *out;              /* device output, 4-byte aligned, ZEROED by the caller from *total on */
+    /* batches of one call may run on two streams; *total is the only state they share, so the scan
+     * stage waits for the previous batch's scan and signals its own (both optional) */
+    cudaEvent_t scan_wait, scan_done;
 } b2d_job;
 
 cudaError_t b2d_kernels_init(void);
 #define B2D_NSTAGE 6   /* chains, match, parse, plan, scan, emit */
+uint64_t b2d_chain_wave_bytes(void);
 cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev);
 
 /* checksums (b2d_checksum.cu) */
