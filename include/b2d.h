@@ -31,8 +31,7 @@ extern "C" {
 typedef struct b2d_ctx b2d_ctx;
 
 /* One context = one GPU + its work buffers (sized for `max_batch` input bytes per
- * launch sequence; 0 selects 256 MiB; rounded up to 128 KiB, then down to a whole
- * number of chain-stage waves when it spans more than one).  Calls on one
+ * launch sequence; 0 selects 256 MiB; rounded up to 128 KiB).  Calls on one
  * context are serialised internally; use one context per GPU.
  * Stands in for ParallelCompress__new__ / zng_deflateInit2 (zlib_ngmodule.c:1617-1674). */
 int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out);

@@ -24,18 +24,18 @@
 static inline uint32_t ld32(const uint8_t *p) { uint32_t v; memcpy(&v, p, 4); return v; }
 
 /* stage 1: block b of the job buf[0 .. D+n), data starts at D */
-static void twin_chains(const uint8_t *buf, size_t D, size_t n, size_t b, uint16_t *prevd, uint16_t *head) {
+static void twin_chains(const uint8_t *buf, size_t D, size_t n, size_t b, uint16_t *prevd, uint16_t *head, int hash_bits) {
     size_t job_end = D + n;
     size_t start = D + b * (size_t)B2D_BLOCK;
     size_t end = start + B2D_BLOCK < job_end ? start + B2D_BLOCK : job_end;
     size_t halo = start < B2D_WINDOW ? start : B2D_WINDOW;
     size_t span_start = start - halo;
-    memset(head, 0xff, sizeof(uint16_t) * B2D_HASH_SIZE);
+    memset(head, 0xff, sizeof(uint16_t) * B2D_HASH_SIZE_MAX);
     for (size_t p = span_start; p < end; p++) {
         uint32_t r = (uint32_t)(p - span_start);
         uint16_t out = 0;
         if (p + 5 <= job_end) {
-            uint32_t h = b2d_hash5(ld32(buf + p), buf[p + 4]);
+            uint32_t h = b2d_hash5(ld32(buf + p), buf[p + 4], hash_bits);
             uint32_t d = (r - head[h]) & 0xffffu;
             if (d != 0 && d <= r && d <= B2D_WINDOW) out = (uint16_t)d;
             head[h] = (uint16_t)(r & 0xffffu);
@@ -148,10 +148,10 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     S->hist = (uint32_t *)calloc((nb * B2D_NSUB + 1) * (size_t)(B2D_LL_CODES + B2D_D_CODES), sizeof(uint32_t));
     S->plan = (b2d_plan *)calloc(nb * B2D_NSUB + 1, sizeof(b2d_plan));
     S->block_off = (uint64_t *)calloc(nb + 1, sizeof(uint64_t));
-    uint16_t *head = (uint16_t *)malloc(sizeof(uint16_t) * B2D_HASH_SIZE);
+    uint16_t *head = (uint16_t *)malloc(sizeof(uint16_t) * B2D_HASH_SIZE_MAX);
     b2d_huff_scratch *scr = (b2d_huff_scratch *)malloc(sizeof *scr);
     if (level > 0) {
-        for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head);
+        for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head, pol.hash_bits);
         for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol, max_dist);
     }
     for (size_t k = 0; k < nsub; k++) twin_parse(buf, D, n, k, S->match, S->tok, S->info, S->hist, pol);

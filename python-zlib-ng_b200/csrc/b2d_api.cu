@@ -132,10 +132,6 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     max_batch = align_up(max_batch, B2D_BLOCK);
     if (max_batch > (2048ull << 20)) return fail(B2D_STREAM_ERROR, "max_batch above 2 GiB");
     if ((e = cudaSetDevice(device)) != cudaSuccess) return fail_cuda(e, "cudaSetDevice");
-    {   /* a batch of several waves of the chain stage is rounded down to whole waves (output is unaffected) */
-        const uint64_t wave = b2d_chain_wave_bytes();
-        if (wave && max_batch >= wave) max_batch = max_batch / wave * wave;
-    }
     b2d_ctx *c = new b2d_ctx();
     c->device = device; c->max_batch = max_batch; c->st = nullptr; c->ev0 = c->ev1 = nullptr;
 #define CC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { int rc_ = fail_cuda(e_, #x); ctx_free(c); return rc_; } } while (0)

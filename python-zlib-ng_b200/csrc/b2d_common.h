@@ -33,8 +33,8 @@
                                   /* every unit is parsed by its own thread); costs <0.2 % */
 #define B2D_MIN_MATCH   4u        /* shortest match ever emitted (hash covers 5 bytes)    */
 #define B2D_MAX_MATCH   258u
-#define B2D_HASH_BITS   14
-#define B2D_HASH_SIZE   (1u << B2D_HASH_BITS)
+#define B2D_HASH_BITS_MAX 14      /* head table = 2^bits u16 entries; bits is per level (policy) */
+#define B2D_HASH_SIZE_MAX (1u << B2D_HASH_BITS_MAX)
 #define B2D_LL_CODES    286
 #define B2D_D_CODES     30
 #define B2D_BL_CODES    19
@@ -51,31 +51,39 @@ typedef struct {
     int depth;     /* candidates examined per position (hash-chain steps)        */
     int lazy;      /* 0 greedy, 1 one-ahead, 2 two-ahead                         */
     int nice;      /* stop searching once a match this long is found             */
+    int hash_bits; /* log2 of the head-table size: a smaller table keeps more blocks   */
+                   /* resident per SM in the chain stage, at a little ratio            */
 } b2d_policy;
 
+#ifndef HB_L1
+#define HB_L1 12
+#define HB_L23 13
+#define HB_L456 13
+#endif
 B2D_HD b2d_policy b2d_level_policy(int level) {
     b2d_policy p;
     switch (level) {
-        case 1:  p.depth = 1;  p.lazy = 0; p.nice = 258; break;
-        case 2:  p.depth = 2;  p.lazy = 0; p.nice = 258; break;
-        case 3:  p.depth = 3;  p.lazy = 1; p.nice = 258; break;
-        case 4:  p.depth = 4;  p.lazy = 1; p.nice = 258; break;
-        case 5:  p.depth = 6;  p.lazy = 2; p.nice = 258; break;
-        case 6:  p.depth = 8;  p.lazy = 2; p.nice = 258; break;
-        case 7:  p.depth = 16; p.lazy = 2; p.nice = 258; break;
-        case 8:  p.depth = 32; p.lazy = 2; p.nice = 258; break;
-        default: p.depth = 64; p.lazy = 2; p.nice = 258; break; /* 9 */
+        case 1:  p.depth = 1;  p.lazy = 0; p.nice = 258; p.hash_bits = HB_L1; break;
+        case 2:  p.depth = 2;  p.lazy = 0; p.nice = 258; p.hash_bits = HB_L23; break;
+        case 3:  p.depth = 3;  p.lazy = 1; p.nice = 258; p.hash_bits = HB_L23; break;
+        case 4:  p.depth = 4;  p.lazy = 1; p.nice = 258; p.hash_bits = HB_L456; break;
+        case 5:  p.depth = 6;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
+        case 6:  p.depth = 8;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
+        case 7:  p.depth = 16; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break;
+        case 8:  p.depth = 32; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break;
+        default: p.depth = 64; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break; /* 9, and 0 (unused there) */
     }
     return p;
 }
 
 /* ---- hashing ------------------------------------------------------------ */
-/* 5-byte multiplicative hash: w = bytes p..p+3 little-endian, b4 = byte p+4 */
-B2D_HD uint32_t b2d_hash5(uint32_t w, uint32_t b4) {
+/* 5-byte multiplicative hash: w = bytes p..p+3 little-endian, b4 = byte p+4; the top `bits` bits
+ * of the product index the head table */
+B2D_HD uint32_t b2d_hash5(uint32_t w, uint32_t b4, int bits) {
     uint32_t v = w * 0x9E3779B1u + b4 * 0x85EBCA6Bu;
     v ^= v >> 15;
     v *= 0x2C1B3C6Du;
-    return v >> (32 - B2D_HASH_BITS);
+    return v >> (32 - bits);
 }
 
 /* ---- match / token packing ---------------------------------------------- */

@@ -45,11 +45,12 @@
 #define K_NOLINK 0xffffu   /* prevd value of a position without a predecessor: beyond any max_dist */
 #define K1_BATCH 512u   /* bytes staged per step group (16 steps of 32 positions) */
 
+template <int HB>
 __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n,
                                                uint64_t buf_readable, uint16_t *__restrict__ prevd) {
     extern __shared__ __align__(16) uint8_t smem1[];
     uint16_t *head = reinterpret_cast<uint16_t *>(smem1);                         /* 32 KiB */
-    uint32_t *stage = reinterpret_cast<uint32_t *>(smem1 + 2u * B2D_HASH_SIZE);     /* 2 x 512 B ring */
+    uint32_t *stage = reinterpret_cast<uint32_t *>(smem1 + (2u << HB));            /* 2 x 512 B ring */
     const uint32_t lane = threadIdx.x;
     const uint64_t b = blockIdx.x;
     const uint64_t job_end = D + n;
@@ -61,7 +62,7 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
     {   /* head[] = 0xffff */
         uint4 ff = make_uint4(FULL, FULL, FULL, FULL);
         uint4 *h4 = reinterpret_cast<uint4 *>(head);
-        for (uint32_t i = lane; i < 2u * B2D_HASH_SIZE / 16u; i += 32) h4[i] = ff;
+        for (uint32_t i = lane; i < (2u << HB) / 16u; i += 32) h4[i] = ff;
     }
     const uint64_t c0 = span_start & ~(uint64_t)(K1_BATCH - 1);
     const uint64_t rd_lim = buf_readable & ~(uint64_t)15;
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
             const uint32_t qo = ring & (2 * K1_BATCH - 1);   /* byte offset in the ring */
             const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
             const uint32_t sh = (qo & 3u) << 3;
-            const uint32_t h = b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu);
+            const uint32_t h = b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu, HB);
             const uint32_t r = rel;
             const bool active = r < act_len;
             /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
@@ -624,7 +625,7 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 /* ------------------------------------------------------------------------- */
 /* host-side launchers (called from b2d_api.cu)                               */
 /* ------------------------------------------------------------------------- */
-static size_t k1_smem() { return 2u * B2D_HASH_SIZE + 2u * K1_BATCH; }
+static size_t k1_smem(int hb) { return (2u << hb) + 2u * K1_BATCH; }
 static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
 static size_t k2_smem() { return K2_IN_BYTES + 2u * (B2D_WINDOW + B2D_SUB) + 32u; }
 
@@ -633,17 +634,7 @@ cudaError_t b2d_kernels_init(void) {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k4_smem());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k1_smem());
-}
-
-/* input bytes one full wave of k_chains covers (resident warps on the device x B2D_BLOCK); batches
- * that are a whole number of waves avoid a mostly-empty last wave in the longest-running stage */
-uint64_t b2d_chain_wave_bytes(void) {
-    int dev = 0, sms = 0, per_sm = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chains, 32, k1_smem()) != cudaSuccess) return 0;
-    return (uint64_t)sms * (uint64_t)per_sm * B2D_BLOCK;
+    return cudaSuccess;   /* k_chains needs at most 33 KiB: below the default dynamic limit */
 }
 
 cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev) {
@@ -656,8 +647,15 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     const uint8_t *data = J->buf + J->D;
 #define MARK(i) do { if (ev) { cudaError_t e_ = cudaEventRecord(ev[i], st); if (e_ != cudaSuccess) return e_; } } while (0)
     MARK(0);
-    if (J->level > 0)
-        k_chains<<<nblocks, 32, k1_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd);
+    if (J->level > 0) {
+        /* the head table is 2^hash_bits u16: the smaller it is the more blocks an SM keeps in flight */
+        switch (pol.hash_bits) {
+            case 11: k_chains<11><<<nblocks, 32, k1_smem(11), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd); break;
+            case 12: k_chains<12><<<nblocks, 32, k1_smem(12), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd); break;
+            case 13: k_chains<13><<<nblocks, 32, k1_smem(13), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd); break;
+            default: k_chains<14><<<nblocks, 32, k1_smem(14), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd); break;
+        }
+    }
     MARK(1);
     if (J->level > 0) {
         k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,

@@ -29,7 +29,6 @@ typedef struct {
 
 cudaError_t b2d_kernels_init(void);
 #define B2D_NSTAGE 6   /* chains, match, parse, plan, scan, emit */
-uint64_t b2d_chain_wave_bytes(void);
 cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *ev);
 
 /* checksums (b2d_checksum.cu) */

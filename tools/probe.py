@@ -40,10 +40,11 @@ def main():
     cap = (int(L.b2d_deflate_bound(n)) + 3) & ~3
     d_out = ctx.device_alloc(cap)
     ctx.h2d(d_in, data.ctypes.data_as(ctypes.c_void_p), n)
-    nat.check(L.b2d_profile(ctx.handle, 1))
     for lvl in [int(x) for x in a.levels.split(",") if x]:
-        L.b2d_profile_read(ctx.handle, None, None, 1)
-        for r in range(a.reps):
+        for r in range(a.reps + 1):
+            if r == a.reps:      # one more pass on a single stream with per-kernel events
+                nat.check(L.b2d_profile(ctx.handle, 2))
+                L.b2d_profile_read(ctx.handle, None, None, 1)
             out_n = ctypes.c_uint64(0)
             ms = ctypes.c_float(0)
             nat.check(L.b2d_deflate_device(ctx.handle, lvl, ctypes.c_void_p(d_in), 0, n, ctypes.c_void_p(d_out), cap,
@@ -51,7 +52,8 @@ def main():
             print(f"L{lvl} rep{r}: {ms.value:.2f} ms  {n / ms.value / 1e6:.2f} GB/s  ratio {out_n.value / n:.4f}", flush=True)
         sm = (ctypes.c_double * 6)()
         L.b2d_profile_read(ctx.handle, sm, None, 1)
-        print("   stage ms/rep:", " ".join(f"{nm}={sm[i] / a.reps:.2f}" for i, nm in enumerate(["chains", "match", "parse", "plan", "scan", "emit"])), flush=True)
+        nat.check(L.b2d_profile(ctx.handle, 0))
+        print("   stage ms alone:", " ".join(f"{nm}={sm[i]:.2f}" for i, nm in enumerate(["chains", "match", "parse", "plan", "scan", "emit"])), flush=True)
         if a.verify:
             host = np.empty(out_n.value, dtype=np.uint8)
             ctx.d2h(host.ctypes.data_as(ctypes.c_void_p), d_out, out_n.value)
