@@ -308,10 +308,17 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
         const uint32_t ustart = lane * B2D_UNIT;
         const uint32_t uend = ustart + B2D_UNIT < len ? ustart + B2D_UNIT : len;
         uint32_t i = ustart;
+        const uint64_t *L8 = reinterpret_cast<const uint64_t *>(s_len);
         while (i < uend) {
-            const uint32_t v = s_len[i];
-            atomicOr(&s_reach[i >> 5], 1u << (i & 31u));
-            i += v ? v + 3u : 1u;
+            /* the 8-byte group holding i, shifted so that byte 0 is position i: if nothing is left in
+             * it, every position up to the group's end is a literal (literal runs go 8 at a time) */
+            const uint32_t o = i & 7u;
+            const uint64_t g = L8[i >> 3] >> (8u * o);
+            const uint32_t v = (uint32_t)g & 255u;
+            uint32_t k = 1;                                   /* positions marked reached */
+            if (g == 0) { k = 8u - o; if (i + k > uend) k = uend - i; }
+            atomicOr(&s_reach[i >> 5], ((1u << k) - 1u) << (i & 31u));
+            i += v ? v + 3u : k;
         }
     }
     __syncthreads();
@@ -581,12 +588,28 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
             if (tid < B2D_D_CODES) s_d[tid] = P->d_code[tid];
             __syncthreads();
             const uint32_t nt = I.tok_count;
-            const uint32_t per = (nt + K6_THREADS - 1) / K6_THREADS;
+            /* each thread owns a run of tokens whose length is a multiple of 4, read as uint4 with the
+             * next group already in flight (the loop is otherwise bound by the load latency) */
+            const uint32_t per = ((nt + K6_THREADS - 1) / K6_THREADS + 3u) & ~3u;
             const uint32_t t0 = tid * per < nt ? tid * per : nt;
             const uint32_t t1 = t0 + per < nt ? t0 + per : nt;
-            const uint32_t *t = tok + (uint64_t)k * B2D_SUB;
+            const uint4 *t4 = reinterpret_cast<const uint4 *>(tok + (uint64_t)k * B2D_SUB);
+            const uint32_t g0 = t0 >> 2, g1 = (t1 + 3u) >> 2;
             uint32_t mybits = 0;
-            for (uint32_t i = t0; i < t1; ++i) { uint64_t v; uint32_t c; tok_bits(__ldg(t + i), s_ll, s_d, &v, &c); mybits += c; }
+            if (t1 > t0) {          /* (an empty run has t0 = nt, which need not be a multiple of 4) */
+                uint4 q = __ldg(t4 + g0);
+                for (uint32_t g = g0; g < g1; ++g) {
+                    const uint4 cur = q;
+                    if (g + 1 < g1) q = __ldg(t4 + g + 1);
+                    const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+                    for (uint32_t j = 0; j < 4; ++j) {
+                        if (4u * g + j >= t1) break;          /* slots past the last token hold stale words */
+                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, &v, &c);
+                        mybits += c;
+                    }
+                }
+            }
             uint32_t incl = mybits;
 #pragma unroll
             for (uint32_t o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
@@ -598,10 +621,18 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
             const uint64_t body = base + hdr_bits;
             if (t1 > t0) {
                 bitsink s; sink_open(s, out, body + wb + incl - mybits);
-                for (uint32_t i = t0; i < t1; ++i) {
-                    uint64_t v; uint32_t c; tok_bits(__ldg(t + i), s_ll, s_d, &v, &c);
-                    if (c > 32u) { sink_put(s, v & 0xffffffffull, 32u); sink_put(s, v >> 32, c - 32u); }
-                    else sink_put(s, v, c);
+                uint4 q = __ldg(t4 + g0);
+                for (uint32_t g = g0; g < g1; ++g) {
+                    const uint4 cur = q;
+                    if (g + 1 < g1) q = __ldg(t4 + g + 1);
+                    const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+                    for (uint32_t j = 0; j < 4; ++j) {
+                        if (4u * g + j >= t1) break;
+                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, &v, &c);
+                        if (c > 32u) { sink_put(s, v & 0xffffffffull, 32u); sink_put(s, v >> 32, c - 32u); }
+                        else sink_put(s, v, c);
+                    }
                 }
                 sink_close(s);
             }

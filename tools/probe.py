@@ -31,7 +31,10 @@ def main():
     a = ap.parse_args()
     n = a.mib << 20
     t = time.time()
-    base = synthdata.make(a.kind, min(n, 64 << 20), 1)
+    if a.kind.startswith("seg"):       # one segment kind of the mixed generator: seg0 text .. seg5 base64
+        base = synthdata._segment(int(a.kind[3:]), min(n, 64 << 20), synthdata._rng(7))
+    else:
+        base = synthdata.make(a.kind, min(n, 64 << 20), 1)
     data = np.tile(base, (n + base.size - 1) // base.size)[:n]
     print(f"gen {time.time() - t:.1f}s", flush=True)
     L = nat.lib()
