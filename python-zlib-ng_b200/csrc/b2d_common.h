@@ -55,6 +55,10 @@ typedef struct {
                    /* resident per SM in the chain stage, at a little ratio            */
 } b2d_policy;
 
+#ifndef D_L6
+#define D_L5 5
+#define D_L6 6
+#endif
 #ifndef HB_L1
 #define HB_L1 12
 #define HB_L23 13
@@ -67,8 +71,8 @@ B2D_HD b2d_policy b2d_level_policy(int level) {
         case 2:  p.depth = 2;  p.lazy = 0; p.nice = 258; p.hash_bits = HB_L23; break;
         case 3:  p.depth = 3;  p.lazy = 1; p.nice = 258; p.hash_bits = HB_L23; break;
         case 4:  p.depth = 4;  p.lazy = 1; p.nice = 258; p.hash_bits = HB_L456; break;
-        case 5:  p.depth = 6;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
-        case 6:  p.depth = 8;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
+        case 5:  p.depth = D_L5;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
+        case 6:  p.depth = D_L6;  p.lazy = 2; p.nice = 258; p.hash_bits = HB_L456; break;
         case 7:  p.depth = 16; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break;
         case 8:  p.depth = 32; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break;
         default: p.depth = 64; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break; /* 9, and 0 (unused there) */

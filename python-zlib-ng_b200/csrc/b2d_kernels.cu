@@ -385,7 +385,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 /* ------------------------------------------------------------------------- */
 /* K4: Huffman plan per sub-block                                             */
 /* ------------------------------------------------------------------------- */
-#define K4_WARPS 8
+#define K4_WARPS 7
 struct k4_warp_smem {
     b2d_huff_scratch S;
     b2d_plan P;
