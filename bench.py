@@ -80,6 +80,28 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """Keep stdout for the one JSON line: anything else (NCCL's version banner, library chatter written
+    to fd 1 from C) goes to stderr."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_JSON_FD, data)
+
+
 def dist_setup(n_gpus):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -211,10 +233,11 @@ def main():
                                            f"ratio {out_n / sample_n:.4f}"},
                 "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
+        emit_line(line)
         return 0
 
     # ------------------------------------------------------------------ this repo's arm
+    claim_stdout()
     rank, world, local, dist = dist_setup(a.gpus)
     # synthetic data first (numpy), CUDA afterwards
     base, reps = make_workload(a.kind, n, 2 + rank, a.base_mib)
@@ -371,7 +394,7 @@ def main():
             line["cpu_baseline"] = cpu
         if extra:
             line["extra"] = extra
-        print(json.dumps(line))
+        emit_line(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
