@@ -102,6 +102,35 @@ def emit_line(line):
         os.write(_JSON_FD, data)
 
 
+def bind_to_gpu_numa_node(local):
+    """Run this rank's host threads (and therefore first-touch its pinned buffers) on the NUMA node
+    the GPU hangs off: with 4-8 ranks the end-to-end number is otherwise limited by the inter-socket
+    link, not by PCIe.  Returns a short description for the config, or None when nothing was done."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = bus.lower()
+        if len(bus.split(":")[0]) == 8:      # nvml pads the domain to 8 hex digits, sysfs uses 4
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return f"numa node {node} ({len(cpus)} cpus)"
+    except Exception:
+        return None
+
+
 def dist_setup(n_gpus):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -239,6 +268,7 @@ def main():
     # ------------------------------------------------------------------ this repo's arm
     claim_stdout()
     rank, world, local, dist = dist_setup(a.gpus)
+    config["host_binding"] = bind_to_gpu_numa_node(local) if world > 1 else None
     # synthetic data first (numpy), CUDA afterwards
     base, reps = make_workload(a.kind, n, 2 + rank, a.base_mib)
     from zlib_ng_b200 import _native as nat

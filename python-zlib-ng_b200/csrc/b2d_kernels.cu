@@ -203,23 +203,37 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
             }
             uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
             int step = depth;
-            const uint32_t lp = pr - poff;
-            uint32_t cb = pr + best;                        /* own_b's index; the candidate's is cb - dist */
+            const uint32_t osh = (pr & 3u) << 3;
+            /* byte addresses inside the shared window, so that a step's two loads are one subtract each */
+            const uint8_t *lpb = reinterpret_cast<const uint8_t *>(s_prev + (pr - poff));
+            const uint8_t *cbp = s_in8 + pr + best;         /* own_b's address; the candidate's is cbp - dist */
             do {
-                const uint32_t nd = s_prev[lp - dist];      /* next link: independent of the byte test below */
-                if (s_in8[cb - dist] == own_b) {
+                const uint32_t nd = *reinterpret_cast<const uint16_t *>(lpb - 2u * dist);   /* next link: independent of the test below */
+                if (*(cbp - dist) == own_b) {
                     const uint32_t cand = pr - dist;
+                    uint32_t cw = cand >> 2;
+                    const uint32_t csh = (cand & 3u) << 3;
+                    const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
+                    const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own[0];
+                    const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own[1];
                     uint32_t l, x;
-                    if ((x = ldu32(s_in, cand) ^ own[0]) != 0) l = 0;
-                    else if ((x = ldu32(s_in, cand + 4) ^ own[1]) != 0) l = 4;
-                    else if ((x = ldu32(s_in, cand + 8) ^ own[2]) != 0) l = 8;
-                    else if ((x = ldu32(s_in, cand + 12) ^ own[3]) != 0) l = 12;
+                    if (x0 | x1) { x = x0 ? x0 : x1; l = x0 ? 0u : 4u; }      /* most compares end in the first 8 bytes */
                     else {
-                        l = 16;
-                        while (l < maxl) {
-                            x = ldu32(s_in, cand + l) ^ ldu32(s_in, pr + l);
-                            if (x) break;
-                            l += 4;
+                        const uint32_t a3 = s_in[cw + 3], a4 = s_in[cw + 4];
+                        if ((x = __funnelshift_r(a2, a3, csh) ^ own[2]) != 0) l = 8;
+                        else if ((x = __funnelshift_r(a3, a4, csh) ^ own[3]) != 0) l = 12;
+                        else {
+                            /* long match: 8 bytes per trip, each aligned word of either side loaded once */
+                            l = 16;
+                            cw += 4;
+                            uint32_t ow = (pr >> 2) + 4u, cp = a4, op = s_in[ow];
+                            while (l < maxl) {
+                                const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], o1 = s_in[ow + 1], o2 = s_in[ow + 2];
+                                if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, o1, osh)) != 0) break;
+                                l += 4;
+                                if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(o1, o2, osh)) != 0) break;
+                                l += 4; cw += 2; ow += 2; cp = c2; op = o2;
+                            }
                         }
                     }
                     if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
@@ -227,8 +241,8 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
                     if (l > best) {
                         best = l; bd = dist;
                         if (l >= nice || l == maxl) break;
-                        cb = pr + best;
-                        own_b = s_in8[cb];
+                        cbp = s_in8 + pr + best;
+                        own_b = *cbp;
                     }
                 }
                 dist += nd;
