@@ -34,13 +34,13 @@ static void twin_chains(const uint8_t *buf, size_t D, size_t n, size_t b, uint16
     for (size_t p = span_start; p < end; p++) {
         uint32_t r = (uint32_t)(p - span_start);
         uint16_t out = 0;
-        if (p + 5 <= job_end) {
+        if (p + 5 <= end) {            /* the hash never looks past the block: blocks are independent of what follows */
             uint32_t h = b2d_hash5(ld32(buf + p), buf[p + 4], hash_bits);
             uint32_t d = (r - head[h]) & 0xffffu;
             if (d != 0 && d <= r && d <= B2D_WINDOW) out = (uint16_t)d;
             head[h] = (uint16_t)(r & 0xffffu);
         }
-        if (p >= start || b == 0) prevd[p] = out;
+        prevd[r] = out;      /* per-block links, indexed from span_start: a block depends on nothing but its own span */
     }
 }
 
@@ -50,6 +50,8 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
     size_t job_end = D + n;
     size_t start = D + b * (size_t)B2D_BLOCK;
     size_t end = start + B2D_BLOCK < job_end ? start + B2D_BLOCK : job_end;
+    size_t span_start = start - (start < B2D_WINDOW ? start : B2D_WINDOW);
+    prevd -= span_start;                               /* prevd[q] for absolute q >= span_start */
     for (size_t p = start; p < end; p++) {
         size_t uend = ((p - D) / B2D_UNIT + 1) * (size_t)B2D_UNIT + D;   /* no match crosses a parse unit */
         size_t lim = uend < end ? uend : end;
@@ -121,7 +123,7 @@ static void put(bitw *w, uint64_t value, uint32_t count) {
 }
 
 typedef struct {
-    uint16_t *prevd;      /* [D + n]            */
+    uint16_t *prevd;      /* [BLOCK + WINDOW] links of the block being processed */
     uint32_t *match;      /* [n]                */
     uint32_t *tok;        /* [nsub * SUB]       */
     b2d_subinfo *info;    /* [nsub]             */
@@ -141,7 +143,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     size_t nsub = (n + B2D_SUB - 1) / B2D_SUB;
     twin_state *S = (twin_state *)calloc(1, sizeof *S);
     S->nblocks = nb;
-    S->prevd = (uint16_t *)calloc(D + n + 8, sizeof(uint16_t));
+    S->prevd = (uint16_t *)calloc(B2D_BLOCK + B2D_WINDOW + 8, sizeof(uint16_t));   /* one block's span at a time */
     S->match = (uint32_t *)calloc(n + 8, sizeof(uint32_t));
     S->tok = (uint32_t *)calloc(nb * (size_t)B2D_BLOCK + 8, sizeof(uint32_t));
     S->info = (b2d_subinfo *)calloc(nb * B2D_NSUB + 1, sizeof(b2d_subinfo));
@@ -151,8 +153,10 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     uint16_t *head = (uint16_t *)malloc(sizeof(uint16_t) * B2D_HASH_SIZE_MAX);
     b2d_huff_scratch *scr = (b2d_huff_scratch *)malloc(sizeof *scr);
     if (level > 0) {
-        for (size_t b = 0; b < nb; b++) twin_chains(buf, D, n, b, S->prevd, head, pol.hash_bits);
-        for (size_t b = 0; b < nb; b++) twin_matches(buf, D, n, b, S->prevd, S->match, pol, max_dist);
+        for (size_t b = 0; b < nb; b++) {
+            twin_chains(buf, D, n, b, S->prevd, head, pol.hash_bits);
+            twin_matches(buf, D, n, b, S->prevd, S->match, pol, max_dist);
+        }
     }
     for (size_t k = 0; k < nsub; k++) twin_parse(buf, D, n, k, S->match, S->tok, S->info, S->hist, pol);
     for (size_t k = 0; k < nsub; k++) {
@@ -231,7 +235,6 @@ void b2d_twin_free(twin_state *S) {
     free(S->prevd); free(S->match); free(S->tok); free(S->info); free(S->hist); free(S->plan); free(S->block_off); free(S);
 }
 /* accessors for ctypes-side stage comparison */
-const uint16_t *b2d_twin_prevd(const twin_state *S) { return S->prevd; }
 const uint32_t *b2d_twin_match(const twin_state *S) { return S->match; }
 const uint32_t *b2d_twin_tok(const twin_state *S) { return S->tok; }
 const b2d_subinfo *b2d_twin_info(const twin_state *S) { return S->info; }

@@ -54,7 +54,7 @@ static void work_free(b2d_work *w) {
 static cudaError_t work_alloc(b2d_work *w, uint64_t max_batch) {
     const uint64_t nsub = max_batch / B2D_SUB, nblk = max_batch / B2D_BLOCK;
     cudaError_t e;
-    if ((e = cudaMalloc(&w->prevd, (B2D_WINDOW + max_batch + 64) * sizeof(uint16_t))) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&w->prevd, (nblk * (uint64_t)B2D_LINKS + 64) * sizeof(uint16_t))) != cudaSuccess) return e;
     if ((e = cudaMalloc(&w->match, max_batch * sizeof(uint32_t))) != cudaSuccess) return e;
     if ((e = cudaMalloc(&w->tok, max_batch * sizeof(uint32_t))) != cudaSuccess) return e;
     if ((e = cudaMalloc(&w->hist, nsub * B2D_HIST * sizeof(uint32_t))) != cudaSuccess) return e;

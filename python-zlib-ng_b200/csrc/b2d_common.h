@@ -29,6 +29,8 @@
 #define B2D_WINDOW      32768u    /* dictionary halo = DEFLATE window                     */
 #define B2D_SUB         32768u    /* one DEFLATE block per sub-block of input             */
 #define B2D_NSUB        (B2D_BLOCK / B2D_SUB)
+#define B2D_SPAN        (B2D_BLOCK + B2D_WINDOW)   /* positions a block hashes: itself + its dictionary */
+#define B2D_LINKS       (B2D_SPAN + 16u)           /* link entries per block (first up to 7 and last 8+ are alignment slack) */
 #define B2D_UNIT        1024u     /* parse unit: no token crosses a multiple of this (so   */
                                   /* every unit is parsed by its own thread); costs <0.2 % */
 #define B2D_MIN_MATCH   4u        /* shortest match ever emitted (hash covers 5 bytes)    */

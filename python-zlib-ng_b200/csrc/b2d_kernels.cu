@@ -75,11 +75,12 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
     /* positions are handled as 32-bit offsets r from span_start; a batch that starts before the span
      * (c0 is rounded down) gives wrapped-around offsets that fail every range test */
     const uint32_t span_len = (uint32_t)(end - span_start);
-    const uint64_t job_rel64 = job_end - span_start;
-    const uint32_t job_rel = job_rel64 > 0x7fffffffull ? 0x7fffffffu : (uint32_t)job_rel64;
-    const uint32_t act_len = span_len + 5u <= job_rel ? span_len : (job_rel >= 5u ? job_rel - 4u : 0u);  /* r < act_len: hashable */
-    const uint32_t wlo = b == 0 ? 0u : (uint32_t)halo;          /* first offset this block writes links for */
-    uint16_t *pd = prevd + span_start;
+    /* r < act_len: position can be hashed (its 5 bytes end inside the block; nothing after the block is
+     * ever looked at, so a block's output does not depend on what follows it) */
+    const uint32_t act_len = span_len >= 5u ? span_len - 4u : 0u;
+    /* every block keeps the links of its whole span (dictionary included) in its own array: a block's
+     * output then depends on nothing but its 32 KiB of history and its data, wherever batches are cut */
+    uint16_t *pd = prevd + b * (uint64_t)B2D_LINKS + (span_start & 7u);
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t rel = (uint32_t)(c0 - span_start) + lane;          /* offset of this lane's position in step 0 */
     uint32_t ring = (uint32_t)(c0 & (2 * K1_BATCH - 1)) + lane;
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
                 if (shared && (m >> lane) == 1u) head[h] = (uint16_t)r16;   /* highest lane of the bucket is the head */
                 __syncwarp();
             }
-            if (r < span_len && r >= wlo) pd[r] = (uint16_t)d;
+            if (r < span_len) pd[r] = (uint16_t)d;
             rel += 32u;
             ring += 32u;
         }
@@ -171,11 +172,12 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         }
         uint4 *p4 = reinterpret_cast<uint4 *>(s_prev);
         const uint32_t np = (uint32_t)((tile_end - wp_al + 7) >> 3);
-        const uint64_t pd_lim = (job_end + 7) & ~(uint64_t)7;   /* prevd allocation is padded to 8 */
-        for (uint32_t i = tid; i < np; i += K2_THREADS) {
-            uint64_t e = wp_al + 8ull * i;
-            p4[i] = (e + 8 <= pd_lim) ? __ldg(reinterpret_cast<const uint4 *>(prevd + e)) : make_uint4(FULL, FULL, FULL, FULL);
-        }
+        /* links of this tile's block, entry 0 = position (span_start & ~7) */
+        const uint64_t blk = k / B2D_NSUB;
+        const uint64_t bstart = D + blk * (uint64_t)B2D_BLOCK;
+        const uint64_t span_al = (bstart - (bstart < B2D_WINDOW ? bstart : B2D_WINDOW)) & ~(uint64_t)7;
+        const uint4 *src = reinterpret_cast<const uint4 *>(prevd + blk * (uint64_t)B2D_LINKS + (wp_al - span_al));
+        for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
     }
     __syncthreads();
     const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);

@@ -13,7 +13,7 @@ typedef struct {
     uint64_t buf_readable;     /* bytes of buf that may be read (>= D + n)          */
     int level;                 /* 0..9                                              */
     uint32_t max_dist;         /* longest match distance allowed (<= 32768)         */
-    uint16_t *prevd;           /* [align8(D + n)]                                   */
+    uint16_t *prevd;           /* [nblocks * B2D_LINKS] per-block link arrays       */
     uint32_t *match;           /* [n]                                               */
     uint32_t *tok;             /* [nsub * B2D_SUB]                                  */
     b2d_subinfo *info;         /* [nsub]                                            */
