@@ -86,6 +86,20 @@ def test_batch_size_does_not_change_output(nat):
     assert outs[0] == twin_deflate(data, 6)
 
 
+@pytest.mark.parametrize("level", [1, 6])
+def test_blocks_are_independent_given_their_dictionary(nat, ctx, level):
+    """A 128 KiB block's bytes depend only on the block and the 32 KiB before it: compressing the blocks one
+    call at a time, each with its predecessor's tail as zdict (what gzip_ng_threaded's workers do,
+    gzip_ng_threaded.py:340-368), gives the same bytes as one call over the whole buffer."""
+    data = synthdata.make("mixed", 1_000_000, 77).tobytes()
+    whole = deflate_host(nat, ctx, data, level)[0]
+    parts = []
+    for off in range(0, len(data), 131072):
+        parts.append(deflate_host(nat, ctx, data[off:off + 131072], level, zdict=data[max(0, off - 32768):off])[0])
+    assert b"".join(parts) == whole
+    assert twin_deflate(data, level) == whole
+
+
 def test_empty_and_final(nat, ctx):
     out, crc, adler = deflate_host(nat, ctx, b"", 6)
     assert out == b"\x00\x00\x00\xff\xff" and crc == 0 and adler == 1
