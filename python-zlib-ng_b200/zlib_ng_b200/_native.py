@@ -155,16 +155,18 @@ _default = {}
 _default_lock = threading.Lock()
 
 
-def default_context(device: int = 0) -> Context:
-    """Process-wide context per device, created on first use."""
-    ctx = _default.get(device)
+def default_context(device: int = 0, slot: int = 0) -> Context:
+    """Process-wide contexts, created on first use.  Slot 0 of a device serves the one-shot calls; the
+    streaming writer also opens slots 1.. so that several batches are in flight per GPU."""
+    key = (device, slot)
+    ctx = _default.get(key)
     if ctx is None:
         with _default_lock:
-            ctx = _default.get(device)
+            ctx = _default.get(key)
             if ctx is None:
                 mb = int(os.environ.get("B2D_MAX_BATCH_MIB", "64")) << 20
                 ctx = Context(device, mb)
-                _default[device] = ctx
+                _default[key] = ctx
     return ctx
 
 

@@ -32,6 +32,62 @@ from . import _native, zlib_ng
 DEFLATE_WINDOW_SIZE = 2 ** 15
 _COMPRESS_LEVEL_TRADEOFF = 6
 _MIN_BATCH = 128 * 1024
+# What one GPU call covers.  The reference keeps threads * block_size bytes in flight; a GPU wants more
+# per launch, so batches grow to this size unless the caller asked for blocks below 1 MiB in total
+# (then the reference's sizes, and its OverflowError on oversized blocks, are kept as they are).
+_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "32")) << 20
+# workers (each with its own GPU context and stream) per device: batch j+1's H2D and batch j-1's D2H
+# overlap batch j's kernels.  threads=N asks for min(N, this) of them.
+_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "3")), 1)
+_COPY_CHUNK = 4 << 20
+_copy_pool = None
+_copy_pool_lock = threading.Lock()
+
+
+def _parallel_copy(dst_addr: int, src, nbytes: int) -> None:
+    """memcpy into pinned memory; large copies are split over a few threads (ctypes.memmove drops the GIL)."""
+    saddr, _, keep = _native._addr(src)
+    if nbytes < 2 * _COPY_CHUNK:
+        ctypes.memmove(dst_addr, saddr, nbytes)
+        return
+    global _copy_pool
+    if _copy_pool is None:
+        with _copy_pool_lock:
+            if _copy_pool is None:
+                from concurrent.futures import ThreadPoolExecutor
+                _copy_pool = ThreadPoolExecutor(max_workers=int(os.environ.get("B2D_COPY_THREADS", "4")),
+                                                thread_name_prefix="b2d-copy")
+    futs = [_copy_pool.submit(ctypes.memmove, dst_addr + o, saddr + o, min(_COPY_CHUNK, nbytes - o))
+            for o in range(0, nbytes, _COPY_CHUNK)]
+    for f in futs:
+        f.result()
+    del keep
+
+
+class _PinnedPool:
+    """Page-locked host buffers are expensive to create (the driver pins every page), so writers hand
+    them back here instead of freeing them; they live until the process exits."""
+
+    def __init__(self):
+        self._lock = threading.Lock()
+        self._free = {}
+
+    def get(self, ctx, size):
+        key = (ctx.device, size)
+        with self._lock:
+            lst = self._free.get(key)
+            if lst:
+                return lst.pop()
+        ptr = ctx.host_alloc(size)
+        view = memoryview((ctypes.c_char * size).from_address(ptr)).cast("B")
+        return ptr, view
+
+    def put(self, ctx, size, ptr, view):
+        with self._lock:
+            self._free.setdefault((ctx.device, size), []).append((ptr, view))
+
+
+_pinned_pool = _PinnedPool()
 
 
 def open(filename, mode="rb", compresslevel=_COMPRESS_LEVEL_TRADEOFF, encoding=None, errors=None, newline=None,
@@ -120,19 +176,14 @@ class _PinnedBuffer:
     def __init__(self, ctx, batch):
         self.ctx = ctx
         self.size = DEFLATE_WINDOW_SIZE + batch
-        self.ptr = ctx.host_alloc(self.size)
-        self.view = memoryview((ctypes.c_char * self.size).from_address(self.ptr)).cast("B")
+        self.ptr, self.view = _pinned_pool.get(ctx, self.size)
         self.fill = 0          # data bytes
         self.dict_n = 0        # dictionary bytes stored right before the data
 
     def free(self):
         if self.ptr:
-            try:
-                self.view.release()
-            except BufferError:
-                pass
-            self.ctx.host_free(self.ptr)
-            self.ptr = 0
+            _pinned_pool.put(self.ctx, self.size, self.ptr, self.view)
+            self.ptr, self.view = 0, None
 
 
 class _ThreadedGzipWriter(io.RawIOBase):
@@ -155,19 +206,20 @@ class _ThreadedGzipWriter(io.RawIOBase):
         self.block_size = block_size
         self.threads = threads
         devices = _devices()
-        self._contexts = [_context_for(d) for d in devices]
-        # one batch = what the reference would have in flight across its threads
-        self.batch = max(block_size * threads // len(devices), 1)
+        # workers = (device, slot) pairs, each with its own GPU context: the counterpart of the
+        # reference's N compression threads (gzip_ng_threaded.py:233-246), round-robin like them
+        depth = min(threads, _STREAM_DEPTH)
+        self._contexts = [_context_for(d, slot) for slot in range(depth) for d in devices]
+        nw = len(self._contexts)
+        # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece
+        nominal = max(block_size * threads // nw, 1)
+        self.batch = nominal if block_size * threads < (1 << 20) else max(nominal, _STREAM_BATCH)
         self._out_cap = self.batch + max(self.batch // 10, 500)
-        nw = len(devices)
         self.input_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)]
         self.output_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)] if nw > 1 else []
         self._free = queue.Queue()
         self._buffers = []
-        for i in range(nw * (max(queue_size, 1) + 2)):
-            buf = _PinnedBuffer(self._contexts[i % nw], self.batch)
-            self._buffers.append(buf)
-            self._free.put(buf)
+        self._max_buffers = nw * (max(queue_size, 1) + 1) + 1
         self._cur = None
         self._last_tail = b""
         self.index = 0
@@ -220,9 +272,13 @@ class _ThreadedGzipWriter(io.RawIOBase):
     def _take_buffer(self):
         while True:
             try:
-                buf = self._free.get(timeout=0.05)
+                buf = self._free.get_nowait() if len(self._buffers) < self._max_buffers else self._free.get(timeout=0.05)
                 break
             except queue.Empty:
+                if len(self._buffers) < self._max_buffers:       # pinned input buffers are created on demand
+                    buf = _PinnedBuffer(self._contexts[len(self._buffers) % len(self._contexts)], self.batch)
+                    self._buffers.append(buf)
+                    break
                 with self.lock:
                     if self.exception:
                         raise self.exception
@@ -269,7 +325,10 @@ class _ThreadedGzipWriter(io.RawIOBase):
             buf = self._cur
             k = min(length - pos, self.batch - buf.fill)
             o = DEFLATE_WINDOW_SIZE + buf.fill
-            buf.view[o:o + k] = mv[pos:pos + k]
+            if k >= 2 * _COPY_CHUNK:
+                _parallel_copy(buf.ptr + o, mv[pos:pos + k], k)
+            else:
+                buf.view[o:o + k] = mv[pos:pos + k]
             buf.fill += k
             pos += k
             if buf.fill == self.batch:
@@ -381,7 +440,11 @@ class _ThreadedGzipWriter(io.RawIOBase):
     def _compress(self, index: int):
         in_queue = self.input_queues[index]
         out_queue = self.output_queues[index]
-        out_buf = _OutBuffer(self._contexts[index], self._out_cap)
+        # two pinned output buffers per worker: the writer thread owns one while the next batch fills the other
+        spare = queue.Queue()
+        bufs = [_OutBuffer(self._contexts[index], self._out_cap) for _ in range(2)]
+        for b in bufs:
+            spare.put(b)
         try:
             while True:
                 try:
@@ -390,19 +453,31 @@ class _ThreadedGzipWriter(io.RawIOBase):
                     if not self._alive():
                         return
                     continue
+                out_buf = None
+                while out_buf is None:
+                    try:
+                        out_buf = spare.get(timeout=0.05)
+                    except queue.Empty:
+                        if not self._alive():
+                            self._release(job)
+                            in_queue.task_done()
+                            return
                 try:
                     compressed, crc, n = self._run_job(index, job, out_buf)
-                    compressed = bytes(compressed)
                 except Exception as e:
                     self._release(job)
                     in_queue.task_done()
                     self._set_error_and_empty_queue(e, in_queue)
                     return
                 self._release(job)
-                out_queue.put((compressed, crc, n))
+                out_queue.put((compressed, crc, n, spare, out_buf))
                 in_queue.task_done()
         finally:
-            out_buf.free()
+            # the writer thread may still be writing from one of these: let it drain before they go back to the pool
+            if threading.current_thread() is not self.output_worker:
+                self.output_worker.join()
+            for b in bufs:
+                b.free()
 
     def _write(self):
         index = 0
@@ -410,7 +485,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
         while True:
             q = self.output_queues[index % nq]
             try:
-                compressed, crc, n = q.get(timeout=0.05)
+                compressed, crc, n, spare, out_buf = q.get(timeout=0.05)
             except queue.Empty:
                 if not self._alive():
                     return
@@ -423,6 +498,9 @@ class _ThreadedGzipWriter(io.RawIOBase):
                 q.task_done()
                 self._set_error_and_empty_queue(e, q)
                 return
+            finally:
+                compressed.release()
+                spare.put(out_buf)
             q.task_done()
             index += 1
 
@@ -445,17 +523,12 @@ class _OutBuffer:
     def __init__(self, ctx, cap):
         self.ctx = ctx
         self.cap = max(cap, 16)
-        self.ptr = ctx.host_alloc(self.cap)
-        self.view = memoryview((ctypes.c_char * self.cap).from_address(self.ptr)).cast("B")
+        self.ptr, self.view = _pinned_pool.get(ctx, self.cap)
 
     def free(self):
         if self.ptr:
-            try:
-                self.view.release()
-            except BufferError:
-                pass
-            self.ctx.host_free(self.ptr)
-            self.ptr = 0
+            _pinned_pool.put(self.ctx, self.cap, self.ptr, self.view)
+            self.ptr, self.view = 0, None
 
 
 _ctx_lock = threading.Lock()
@@ -471,8 +544,8 @@ def _devices():
     return [int(x) for x in spec.split(",") if x.strip() != ""] or [0]
 
 
-def _context_for(device: int):
+def _context_for(device: int, slot: int = 0):
     try:
-        return _native.default_context(device)
+        return _native.default_context(device, slot)
     except _native.NativeError as e:
         raise zlib_ng.error(f"Error {e.code} while opening the B200 device: {e.msg}") from None
