@@ -35,10 +35,10 @@ _MIN_BATCH = 128 * 1024
 # What one GPU call covers.  The reference keeps threads * block_size bytes in flight; a GPU wants more
 # per launch, so batches grow to this size unless the caller asked for blocks below 1 MiB in total
 # (then the reference's sizes, and its OverflowError on oversized blocks, are kept as they are).
-_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "32")) << 20
+_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
 # workers (each with its own GPU context and stream) per device: batch j+1's H2D and batch j-1's D2H
 # overlap batch j's kernels.  threads=N asks for min(N, this) of them.
-_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "3")), 1)
+_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "4")), 1)
 _COPY_CHUNK = 4 << 20
 _copy_pool = None
 _copy_pool_lock = threading.Lock()
@@ -55,7 +55,7 @@ def _parallel_copy(dst_addr: int, src, nbytes: int) -> None:
         with _copy_pool_lock:
             if _copy_pool is None:
                 from concurrent.futures import ThreadPoolExecutor
-                _copy_pool = ThreadPoolExecutor(max_workers=int(os.environ.get("B2D_COPY_THREADS", "4")),
+                _copy_pool = ThreadPoolExecutor(max_workers=int(os.environ.get("B2D_COPY_THREADS", "8")),
                                                 thread_name_prefix="b2d-copy")
     futs = [_copy_pool.submit(ctypes.memmove, dst_addr + o, saddr + o, min(_COPY_CHUNK, nbytes - o))
             for o in range(0, nbytes, _COPY_CHUNK)]
