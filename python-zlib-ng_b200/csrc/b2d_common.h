@@ -152,9 +152,13 @@ B2D_HD uint32_t b2d_parse_step(uint32_t l0, uint32_t l1, uint32_t l2, int lazy) 
 /* bit reversal of the low `len` bits (canonical codes are sent MSB-first inside
  * an LSB-first stream: zlib-ng trees.c:811-818) */
 B2D_HD uint32_t b2d_bitrev(uint32_t code, int len) {
+#if defined(__CUDA_ARCH__)
+    return len ? __brev(code) >> (32 - len) : 0u;
+#else
     uint32_t r = 0;
     for (int i = 0; i < len; i++) { r = (r << 1) | (code & 1u); code >>= 1; }
     return r;
+#endif
 }
 
 /* ---- per-sub-block plan written by the Huffman stage, read by the emitter -- */

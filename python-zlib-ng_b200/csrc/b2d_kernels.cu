@@ -421,15 +421,154 @@ __device__ __forceinline__ void warp_rank_sort(b2d_huff_scratch *S, int m, uint3
     __syncwarp();
 }
 
-/* one code-length set: lane 0 builds the keys and runs the serial tree phases, the warp sorts */
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+    for (uint32_t o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+
+/* b2d_huff_keys by the warp: one key per used symbol (any order: the keys are unique and get sorted) */
+__device__ __forceinline__ int warp_huff_keys(const uint32_t *freq, int n, uint8_t *lens, b2d_huff_scratch *S, uint32_t lane) {
+    int m = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + (int)lane;
+        const uint32_t f = i < n ? freq[i] : 0u;
+        if (i < n) lens[i] = 0;
+        const uint32_t used = __ballot_sync(FULL, f != 0);
+        if (f) S->key[m + __popc(used & ((1u << lane) - 1u))] = (f << 9) | (uint32_t)i;
+        m += __popc(used);
+    }
+    __syncwarp();
+    if (m < 2 && lane == 0) {          /* at least two symbols always receive a code (b2d_huff_keys) */
+        if (m == 0) { S->key[0] = (1u << 9) | 0u; S->key[1] = (1u << 9) | 1u; }
+        else { const uint32_t s0 = S->key[0] & 511u; S->key[1] = (1u << 9) | (s0 == 0u ? 1u : 0u); }
+    }
+    if (m < 2) m = 2;
+    __syncwarp();
+    return m;
+}
+
+/* one code-length set: keys and sort by the warp, the serial tree phases by lane 0 */
 __device__ __forceinline__ void warp_huff_lengths(const uint32_t *freq, int n, int maxbits, uint8_t *lens,
                                                   b2d_huff_scratch *S, uint32_t lane) {
-    int m = 0;
-    if (lane == 0) m = b2d_huff_keys(freq, n, lens, S);
-    m = __shfl_sync(FULL, m, 0);
-    __syncwarp();
+    const int m = warp_huff_keys(freq, n, lens, S, lane);
     warp_rank_sort(S, m, lane);
     if (lane == 0) b2d_huff_from_sorted(m, maxbits, lens, S);
+    __syncwarp();
+}
+
+/* b2d_canonical by the warp: lane b keeps next_code[b]; a symbol's code is next_code[len] plus the number
+ * of lower-numbered symbols of the same length */
+__device__ __forceinline__ void warp_canonical(const uint8_t *lens, int n, int maxbits, uint32_t *out, uint32_t lane) {
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t cnt = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + (int)lane;
+        const uint32_t l = i < n ? lens[i] : 0u;
+        for (int b = 1; b <= maxbits; ++b) {
+            const uint32_t mk = __ballot_sync(FULL, l == (uint32_t)b);
+            if (lane == (uint32_t)b) cnt += __popc(mk);
+        }
+    }
+    uint32_t code = 0, next = 0;
+    for (int b = 1; b <= maxbits; ++b) {
+        const uint32_t below = b >= 2 ? __shfl_sync(FULL, cnt, b - 1) : 0u;
+        code = (code + below) << 1;
+        if (lane == (uint32_t)b) next = code;
+    }
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + (int)lane;
+        const uint32_t l = i < n ? lens[i] : 0u;
+        uint32_t mine = 0;
+        for (int b = 1; b <= maxbits; ++b) {
+            const uint32_t mk = __ballot_sync(FULL, l == (uint32_t)b);
+            const uint32_t nb = __shfl_sync(FULL, next, b);
+            if (l == (uint32_t)b) mine = nb + __popc(mk & lt);
+            if (lane == (uint32_t)b) next += __popc(mk);
+        }
+        if (i < n) out[i] = l ? ((l << 16) | (__brev(mine) >> (32u - l))) : 0u;
+    }
+    __syncwarp();
+}
+
+__constant__ uint8_t c_bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+
+/* b2d_plan_end by the warp (same results): costs by reduction, code tables and header bits in parallel */
+__device__ __forceinline__ void warp_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
+                                              b2d_plan *P, b2d_huff_scratch *S, int force_stored, uint32_t lane) {
+    const int hlit = S->hlit, hdist = S->hdist, nseq = S->nseq;
+    int hclen = B2D_BL_CODES;
+    while (hclen > 4 && S->bl_len[c_bl_order[hclen - 1]] == 0) hclen--;
+    uint32_t hdr_part = 0, dyn_part = 0, fix_part = 0;
+    for (int i = (int)lane; i < nseq; i += 32) {
+        const uint32_t s = S->seq_sym[i];
+        hdr_part += S->bl_len[s] + (s == 16u ? 2u : s == 17u ? 3u : s == 18u ? 7u : 0u);
+    }
+    for (int i = (int)lane; i < B2D_LL_CODES; i += 32) {
+        const uint32_t f = ll_freq[i];
+        const uint32_t ex = i >= 257 ? b2d_len_extra_bits((uint32_t)i - 257u) : 0u;
+        dyn_part += f * (S->ll_len[i] + ex);
+        fix_part += f * (b2d_fixed_ll_len((uint32_t)i) + ex);
+    }
+    if (lane < B2D_D_CODES) {
+        const uint32_t f = d_freq[lane], ex = b2d_dist_extra_bits(lane);
+        dyn_part += f * (S->d_len[lane] + ex);
+        fix_part += f * (5u + ex);
+    }
+    const uint32_t dyn_hdr = 3u + 5u + 5u + 4u + 3u * (uint32_t)hclen + warp_sum(hdr_part);
+    const uint32_t dyn_body = warp_sum(dyn_part), fix_body = warp_sum(fix_part);
+    const uint32_t dyn_cost = dyn_hdr + dyn_body, fix_cost = 3u + fix_body;
+    const uint32_t sto_cost = 3u + 7u + 32u + 8u * in_len;   /* worst-case alignment pad */
+    for (uint32_t i = lane; i < B2D_HDR_WORDS; i += 32) P->hdr[i] = 0;
+    __syncwarp();
+    if ((force_stored || (sto_cost <= dyn_cost && sto_cost <= fix_cost)) && in_len <= 65535u) {
+        for (uint32_t i = lane; i < B2D_LL_CODES; i += 32) P->ll_code[i] = 0;
+        if (lane < B2D_D_CODES) P->d_code[lane] = 0;
+        if (lane == 0) { P->type = 0; P->body_bits = 0; P->pad = 0; P->hdr_bits = 3; }   /* BFINAL=0, BTYPE=00: three zero bits */
+    } else if (fix_cost <= dyn_cost) {
+        for (uint32_t i = lane; i < B2D_LL_CODES; i += 32) {
+            const uint32_t l = b2d_fixed_ll_len(i);
+            const uint32_t c = i < 144u ? 0x30u + i : i < 256u ? 0x190u + (i - 144u) : i < 280u ? i - 256u : 0xC0u + (i - 280u);
+            P->ll_code[i] = (l << 16) | b2d_bitrev(c, (int)l);
+        }
+        if (lane < B2D_D_CODES) P->d_code[lane] = (5u << 16) | b2d_bitrev(lane, 5);
+        if (lane == 0) { P->type = 1; P->body_bits = fix_body; P->pad = 0; P->hdr[0] = 2u; P->hdr_bits = 3; }   /* BTYPE=01 */
+    } else {
+        warp_canonical(S->ll_len, B2D_LL_CODES, 15, P->ll_code, lane);
+        warp_canonical(S->d_len, B2D_D_CODES, 15, P->d_code, lane);
+        warp_canonical(S->bl_len, B2D_BL_CODES, 7, S->bl_code, lane);
+        uint32_t nbits = 0;
+        if (lane == 0) {
+            b2d_put_bits(P->hdr, &nbits, 4u, 3);          /* BFINAL=0, BTYPE=10 */
+            b2d_put_bits(P->hdr, &nbits, (uint32_t)(hlit - 257), 5);
+            b2d_put_bits(P->hdr, &nbits, (uint32_t)(hdist - 1), 5);
+            b2d_put_bits(P->hdr, &nbits, (uint32_t)(hclen - 4), 4);
+            for (int i = 0; i < hclen; i++) b2d_put_bits(P->hdr, &nbits, S->bl_len[c_bl_order[i]], 3);
+        }
+        nbits = __shfl_sync(FULL, nbits, 0);
+        __syncwarp();
+        /* the run-length coded length sequence: lane i places item i at the prefix sum of the widths */
+        for (int base = 0; base < nseq; base += 32) {
+            const int i = base + (int)lane;
+            uint32_t val = 0, w = 0;
+            if (i < nseq) {
+                const uint32_t s = S->seq_sym[i], c = S->bl_code[s];
+                const uint32_t eb = s == 16u ? 2u : s == 17u ? 3u : s == 18u ? 7u : 0u;
+                val = (c & 0xffffu) | ((uint32_t)S->seq_ext[i] << (c >> 16));
+                w = (c >> 16) + eb;
+            }
+            uint32_t incl = w;
+#pragma unroll
+            for (uint32_t o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+            if (w) {
+                const uint32_t pos = nbits + incl - w, wi = pos >> 5, sh = pos & 31u;
+                atomicOr(&P->hdr[wi], val << sh);
+                if (sh + w > 32u) atomicOr(&P->hdr[wi + 1], val >> (32u - sh));
+            }
+            nbits += __shfl_sync(FULL, incl, 31);
+        }
+        if (lane == 0) { P->type = 2; P->body_bits = dyn_body; P->pad = 0; P->hdr_bits = nbits; }
+    }
     __syncwarp();
 }
 
@@ -454,8 +593,7 @@ k_plan(const uint32_t *__restrict__ hist, const b2d_subinfo *__restrict__ info, 
     if (lane == 0) b2d_plan_mid(S);
     __syncwarp();
     warp_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S, lane);
-    if (lane == 0) b2d_plan_end(W->hist, W->hist + B2D_LL_CODES, info[k].in_len, &W->P, S, force_stored);
-    __syncwarp();
+    warp_plan_end(W->hist, W->hist + B2D_LL_CODES, info[k].in_len, &W->P, S, force_stored, lane);
     const uint32_t *src = reinterpret_cast<const uint32_t *>(&W->P);
     uint32_t *dst = reinterpret_cast<uint32_t *>(&plan[k]);
     for (uint32_t i = lane; i < sizeof(b2d_plan) / 4; i += 32) dst[i] = src[i];
