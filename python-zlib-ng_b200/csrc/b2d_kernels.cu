@@ -272,22 +272,37 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     const uint64_t sub_start = k * (uint64_t)B2D_SUB;
     const uint32_t len = (uint32_t)(n - sub_start < B2D_SUB ? n - sub_start : B2D_SUB);
     const uint32_t *m = match + sub_start;
-    /* match lengths -> one byte each (len-3, 0 = no match); sub_start is a multiple of 4 positions */
-    for (uint32_t i = tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
-        uint32_t pk = 0;
-        if (4 * i + 4 <= len) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(m) + i);
-            const uint32_t l0 = v.x >> 16, l1 = v.y >> 16, l2 = v.z >> 16, l3 = v.w >> 16;
-            pk = (l0 ? l0 - 3u : 0u) | ((l1 ? l1 - 3u : 0u) << 8) | ((l2 ? l2 - 3u : 0u) << 16) | ((l3 ? l3 - 3u : 0u) << 24);
-        } else {
+    /* match lengths -> one byte each (len-3, 0 = no match); sub_start is a multiple of 4 positions.
+     * Whole uint4 groups first, eight loads in flight per thread; then the ragged end and the padding. */
+    {
+        uint32_t *W = reinterpret_cast<uint32_t *>(s_len);
+        const uint4 *m4 = reinterpret_cast<const uint4 *>(m);
+        const uint32_t full = len >> 2;                      /* groups of 4 positions entirely inside the sub-block */
+        for (uint32_t i0 = 0; i0 < full; i0 += 8u * K3_THREADS) {
+            uint4 v[8];
+#pragma unroll
+            for (uint32_t j = 0; j < 8; ++j) {
+                const uint32_t i = i0 + j * K3_THREADS + tid;
+                v[j] = i < full ? __ldg(m4 + i) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (uint32_t j = 0; j < 8; ++j) {
+                const uint32_t i = i0 + j * K3_THREADS + tid;
+                const uint32_t l0 = v[j].x >> 16, l1 = v[j].y >> 16, l2 = v[j].z >> 16, l3 = v[j].w >> 16;
+                if (i < full)
+                    W[i] = (l0 ? l0 - 3u : 0u) | ((l1 ? l1 - 3u : 0u) << 8) | ((l2 ? l2 - 3u : 0u) << 16) | ((l3 ? l3 - 3u : 0u) << 24);
+            }
+        }
+        for (uint32_t i = full + tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
+            uint32_t pk = 0;
 #pragma unroll
             for (uint32_t j = 0; j < 4; ++j) {
                 const uint32_t pos = 4 * i + j;
                 const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
                 pk |= (l ? l - 3u : 0u) << (8 * j);
             }
+            W[i] = pk;
         }
-        reinterpret_cast<uint32_t *>(s_len)[i] = pk;
     }
     for (uint32_t i = tid; i < B2D_HIST; i += K3_THREADS) s_hist[i] = 0;
     for (uint32_t i = tid; i < K3_WORDS; i += K3_THREADS) s_reach[i] = 0;
