@@ -88,16 +88,24 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
     stage4[(uint32_t)((c0 >> 9) & 1) * 32 + lane] = load16(c0);
     uint4 nxt = load16(c0 + K1_BATCH);
     __syncwarp();
+    /* hash of the lane's position in the step that starts at ring offset `ro` */
+    auto hash_at = [&](uint32_t ro) -> uint32_t {
+        const uint32_t qo = ro & (2 * K1_BATCH - 1);
+        const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
+        const uint32_t sh = (qo & 3u) << 3;
+        return b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu, HB);
+    };
+    uint32_t h_next = hash_at(ring);
     for (uint64_t c = c0; c < end; c += K1_BATCH) {
         stage4[(uint32_t)(((c >> 9) + 1) & 1) * 32 + lane] = nxt;
         nxt = load16(c + 2 * K1_BATCH);
         __syncwarp();
 #pragma unroll 4
         for (uint32_t k = 0; k < K1_BATCH / 32; ++k) {
-            const uint32_t qo = ring & (2 * K1_BATCH - 1);   /* byte offset in the ring */
-            const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
-            const uint32_t sh = (qo & 3u) << 3;
-            const uint32_t h = b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu, HB);
+            /* the next step's hash does not depend on the table: computed here so that its shared loads and
+             * multiplies overlap this step's read / write / read-back chain */
+            const uint32_t h = h_next;
+            h_next = hash_at(ring + 32u);
             const uint32_t r = rel;
             const bool active = r < act_len;
             /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
