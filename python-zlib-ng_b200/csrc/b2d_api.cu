@@ -9,6 +9,7 @@
  */
 #include <cuda_runtime.h>
 #include <mutex>
+#include <thread>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -84,6 +85,7 @@ struct b2d_ctx {
     uint64_t *d_totalx[B2D_NSLOT - 1];
     b2d_cksum_ws *ckx[B2D_NSLOT - 1];
     cudaStream_t st_in, st_out;
+    uint8_t *h_in_s[B2D_NSLOT], *h_out_s[B2D_NSLOT];   /* pinned staging per slot, for pageable callers (lazy) */
     cudaEvent_t ev_in[B2D_NSLOT], ev_comp[B2D_NSLOT], ev_out[B2D_NSLOT];
     uint64_t launches;
     /* optional per-stage timing of device-resident calls */
@@ -108,6 +110,7 @@ static void ctx_free(b2d_ctx *c) {
         if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
         if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
     }
+    for (int i = 0; i < B2D_NSLOT; ++i) { if (c->h_in_s[i]) cudaFreeHost(c->h_in_s[i]); if (c->h_out_s[i]) cudaFreeHost(c->h_out_s[i]); }
     if (c->st_in) cudaStreamDestroy(c->st_in);
     if (c->st_out) cudaStreamDestroy(c->st_out);
     if (c->h_total) cudaFreeHost(c->h_total);
@@ -207,6 +210,8 @@ extern "C" int b2d_adler32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, 
     return B2D_OK;
 }
 
+static int checksum_host_pipelined(b2d_ctx *c, const uint8_t *data, uint64_t n, uint32_t start, bool adler, uint32_t *out);
+
 /* host bytes -> device in pieces through the pinned stage (or directly when the
  * caller's buffer is itself pinned), calling `fn` on each resident piece */
 template <typename F>
@@ -237,6 +242,7 @@ extern "C" int b2d_crc32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64
     if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
     std::lock_guard<std::mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
+    if (n > c->max_batch) return checksum_host_pipelined(c, data, n, start, false, out);
     uint32_t crc = start;
     int rc = for_each_staged(c, data, n, [&](const uint8_t *d, uint64_t m) -> int {
         CU(b2d_crc32_dev(c->ck, d, m, crc, &crc, c->st));
@@ -251,6 +257,7 @@ extern "C" int b2d_adler32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint
     if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
     std::lock_guard<std::mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
+    if (n > c->max_batch) return checksum_host_pipelined(c, data, n, start, true, out);
     uint32_t a = start;
     int rc = for_each_staged(c, data, n, [&](const uint8_t *d, uint64_t m) -> int {
         CU(b2d_adler32_dev(c->ck, d, m, a, &a, c->st));
@@ -395,18 +402,44 @@ static int ensure_second_slot(b2d_ctx *c) {
     return B2D_OK;
 }
 
+/* host copy in a few threads: one thread moves ~10 GB/s, the pipeline wants more */
+static void par_memcpy(void *dst, const void *src, uint64_t n) {
+    const uint64_t piece = 8ull << 20;
+    if (n < 2 * piece) { memcpy(dst, src, n); return; }
+    const unsigned nt = 4;
+    std::thread th[nt];
+    const uint64_t per = (n / nt + 63) & ~63ull;
+    for (unsigned i = 0; i < nt; ++i) {
+        const uint64_t o = (uint64_t)i * per;
+        const uint64_t k = o >= n ? 0 : (n - o < per ? n - o : per);
+        th[i] = std::thread([=] { if (k) memcpy((uint8_t *)dst + o, (const uint8_t *)src + o, k); });
+    }
+    for (unsigned i = 0; i < nt; ++i) th[i].join();
+}
+
+static int ensure_staging(b2d_ctx *c, bool in, bool out) {
+    for (int i = 0; i < B2D_NSLOT; ++i) {
+        if (in && !c->h_in_s[i]) CU(cudaMallocHost(&c->h_in_s[i], c->d_in_cap));
+        if (out && !c->h_out_s[i]) CU(cudaMallocHost(&c->h_out_s[i], c->d_out_cap));
+    }
+    return B2D_OK;
+}
+
 /* Pinned host input and output, more than one batch: three-stage software pipeline.
  *   st_in : H2D of batch j into slot j % 3 (waits until the kernels of batch j-3 released the slot)
  *   st/st2: kernels + CRC of batch j on lane j & 1 (waits for its H2D and for the D2H of batch j-3);
  *           consecutive batches overlap, which fills the tail waves of each other's kernels
  *   st_out: D2H of batch j-1 (issued once the host knows its size)
- * The host only blocks on "kernels of batch j-2 done", by which time batches j-1 and j are already queued. */
+ * The host only blocks on "kernels of batch j-2 done", by which time batches j-1 and j are already queued.
+ * Pageable input / output goes through pinned staging slots (copied by a few host threads), so those callers
+ * get the same overlap. */
 static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, const uint8_t *data, uint64_t n, const uint8_t *dict,
                                   uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t reserve, uint64_t *produced_out,
-                                  uint32_t *crc_acc) {
+                                  uint32_t *crc_acc, uint32_t *adler_acc, bool in_pinned, bool out_pinned) {
     int rc = ensure_second_slot(c);
     if (rc) return rc;
     if ((rc = ensure_second_lane(c))) return rc;
+    if ((rc = ensure_staging(c, !in_pinned, !out_pinned))) return rc;
     cudaStream_t cs[2] = {c->st, c->st2};       /* batch j computes on lane j & 1 */
     uint8_t *d_in[B2D_NSLOT] = {c->d_in}, *d_out[B2D_NSLOT] = {c->d_out};
     uint64_t *d_total[B2D_NSLOT] = {c->d_total};
@@ -414,15 +447,33 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     for (int i = 1; i < B2D_NSLOT; ++i) { d_in[i] = c->d_inx[i - 1]; d_out[i] = c->d_outx[i - 1]; d_total[i] = c->d_totalx[i - 1]; ck[i] = c->ckx[i - 1]; }
     const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
     uint64_t produced = 0;
-    auto finish = [&](uint64_t j) -> int {          /* batch j: wait for its kernels, fold its CRC, start its D2H */
+    uint64_t drained = 0;                 /* bytes of `out` final (staged output only) */
+    uint64_t pend_off = 0, pend_n = 0; int pend_s = -1;
+    auto drain = [&]() -> int {          /* staged output: copy the batch whose D2H was issued last */
+        if (pend_s < 0) return B2D_OK;
+        CU(cudaEventSynchronize(c->ev_out[pend_s]));
+        par_memcpy(out + pend_off, c->h_out_s[pend_s], pend_n);
+        drained = pend_off + pend_n;
+        pend_s = -1;
+        return B2D_OK;
+    };
+    auto finish = [&](uint64_t j) -> int {          /* batch j: wait for its kernels, fold its checksums, start its D2H */
         const int s = (int)(j % B2D_NSLOT);
         const uint64_t m = (j + 1 == nb) ? n - j * c->max_batch : c->max_batch;
         CU(cudaEventSynchronize(c->ev_comp[s]));
         if (crc_acc) *crc_acc = b2d_crc32_dev_finish(ck[s], m, *crc_acc);
+        if (adler_acc) *adler_acc = b2d_adler32_dev_finish(ck[s], m, *adler_acc);
         const uint64_t got = c->h_total[s];
         if (produced + got + reserve > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
-        CU(cudaMemcpyAsync(out + produced, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
-        CU(cudaEventRecord(c->ev_out[s], c->st_out));
+        if (out_pinned) {
+            CU(cudaMemcpyAsync(out + produced, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
+            CU(cudaEventRecord(c->ev_out[s], c->st_out));
+        } else {
+            int rc2 = drain(); if (rc2) return rc2;     /* the previous batch's bytes, while this one's kernels ran */
+            CU(cudaMemcpyAsync(c->h_out_s[s], d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
+            CU(cudaEventRecord(c->ev_out[s], c->st_out));
+            pend_s = s; pend_off = produced; pend_n = got;
+        }
         produced += got;
         return B2D_OK;
     };
@@ -436,10 +487,19 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         if (j == 0) {
             D = dict_n;
             if (D) { CU(cudaMemcpyAsync(d_in[s], dict, D, cudaMemcpyHostToDevice, c->st_in)); }
-            CU(cudaMemcpyAsync(d_in[s] + D, data, m, cudaMemcpyHostToDevice, c->st_in));
+            if (in_pinned) { CU(cudaMemcpyAsync(d_in[s] + D, data, m, cudaMemcpyHostToDevice, c->st_in)); }
+            else {
+                par_memcpy(c->h_in_s[s], data, m);
+                CU(cudaMemcpyAsync(d_in[s] + D, c->h_in_s[s], m, cudaMemcpyHostToDevice, c->st_in));
+            }
         } else {
             D = B2D_WINDOW;
-            CU(cudaMemcpyAsync(d_in[s], data + off - B2D_WINDOW, B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in));
+            if (in_pinned) { CU(cudaMemcpyAsync(d_in[s], data + off - B2D_WINDOW, B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in)); }
+            else {
+                /* the slot's previous H2D (batch j-3) finished before that batch's kernels, which finish(j-3) waited for */
+                par_memcpy(c->h_in_s[s], data + off - B2D_WINDOW, B2D_WINDOW + m);
+                CU(cudaMemcpyAsync(d_in[s], c->h_in_s[s], B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in));
+            }
         }
         CU(cudaEventRecord(c->ev_in[s], c->st_in));
         CU(cudaStreamWaitEvent(cs[ln], c->ev_in[s], 0));
@@ -452,14 +512,60 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         c->launches += level > 0 ? 6 : 4;
         CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
         if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
+        if (adler_acc) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
         /* the host trails by two batches: j-1 and j stay queued on the two lanes while it waits for j-2 */
         if (j >= 2 && (rc = finish(j - 2))) { cudaDeviceSynchronize(); return rc; }
     }
     if (nb >= 2 && (rc = finish(nb - 2))) { cudaDeviceSynchronize(); return rc; }
     if ((rc = finish(nb - 1))) { cudaDeviceSynchronize(); return rc; }
+    if ((rc = drain())) { cudaDeviceSynchronize(); return rc; }
     CU(cudaStreamSynchronize(c->st_out));
     *produced_out = produced;
+    return B2D_OK;
+}
+
+/* crc32 / adler32 of a host buffer larger than one batch: copy-in (through pinned staging when the caller's
+ * memory is pageable), H2D and the checksum kernels of neighbouring pieces overlap; the host folds the
+ * pieces in order (the kernels compute each piece from a neutral start, see b2d_checksum.cu) */
+static int checksum_host_pipelined(b2d_ctx *c, const uint8_t *data, uint64_t n, uint32_t start, bool adler, uint32_t *out) {
+    cudaPointerAttributes at;
+    const bool pinned = cudaPointerGetAttributes(&at, data) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    int rc = ensure_second_slot(c);
+    if (rc) return rc;
+    if ((rc = ensure_staging(c, !pinned, false))) return rc;
+    uint8_t *d_in[B2D_NSLOT] = {c->d_in};
+    b2d_cksum_ws *ck[B2D_NSLOT] = {c->ck};
+    for (int i = 1; i < B2D_NSLOT; ++i) { d_in[i] = c->d_inx[i - 1]; ck[i] = c->ckx[i - 1]; }
+    const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
+    uint32_t acc = start;
+    auto piece = [&](uint64_t j) { return (j + 1 == nb) ? n - j * c->max_batch : c->max_batch; };
+    auto finish = [&](uint64_t j) -> int {
+        const int s = (int)(j % B2D_NSLOT);
+        CU(cudaEventSynchronize(c->ev_comp[s]));
+        acc = adler ? b2d_adler32_dev_finish(ck[s], piece(j), acc) : b2d_crc32_dev_finish(ck[s], piece(j), acc);
+        return B2D_OK;
+    };
+    for (uint64_t j = 0; j < nb; ++j) {
+        const int s = (int)(j % B2D_NSLOT);
+        const uint64_t off = j * c->max_batch, m = piece(j);
+        if (j >= B2D_NSLOT) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));
+        if (pinned) { CU(cudaMemcpyAsync(d_in[s], data + off, m, cudaMemcpyHostToDevice, c->st_in)); }
+        else {
+            par_memcpy(c->h_in_s[s], data + off, m);
+            CU(cudaMemcpyAsync(d_in[s], c->h_in_s[s], m, cudaMemcpyHostToDevice, c->st_in));
+        }
+        CU(cudaEventRecord(c->ev_in[s], c->st_in));
+        CU(cudaStreamWaitEvent(c->st, c->ev_in[s], 0));
+        if (adler) { CU(b2d_adler32_dev_launch(ck[s], d_in[s], m, c->st)); c->launches += 2; }
+        else { CU(b2d_crc32_dev_launch(ck[s], d_in[s], m, c->st)); c->launches += crc_launches(d_in[s], m); }
+        CU(cudaEventRecord(c->ev_comp[s], c->st));
+        if (j >= 2 && (rc = finish(j - 2))) { cudaDeviceSynchronize(); return rc; }
+    }
+    if (nb >= 2 && (rc = finish(nb - 2))) { cudaDeviceSynchronize(); return rc; }
+    if ((rc = finish(nb - 1))) { cudaDeviceSynchronize(); return rc; }
+    *out = acc;
     return B2D_OK;
 }
 
@@ -482,13 +588,14 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         cudaPointerAttributes ot;
         const bool opinned = out && cudaPointerGetAttributes(&ot, out) == cudaSuccess && ot.type == cudaMemoryTypeHost;
         cudaGetLastError();
-        if (pinned && opinned && !adler && n > c->max_batch) {
+        if (n > c->max_batch) {
             int rc = deflate_host_pipelined(c, level, max_dist, data, n, dict, dict_n, out, out_cap, final ? 2 : 0, &produced,
-                                            crc ? &crc_acc : nullptr);
+                                            crc ? &crc_acc : nullptr, adler ? &adler_acc : nullptr, pinned, opinned);
             if (rc) return rc;
             if (final) { out[produced++] = 0x03; out[produced++] = 0x00; }
             *out_n = produced;
             if (crc) *crc = crc_acc;
+            if (adler) *adler = adler_acc;
             return B2D_OK;
         }
     }

@@ -213,6 +213,7 @@ struct b2d_cksum_ws {
     uint32_t *d_tabA, *d_xp32, *d_tab8, *d_raw;
     uint32_t *h_raw;                  /* pinned */
     adler_part *d_parts, *h_parts;
+    uint32_t adler_g;                 /* partial sums the last adler launch wrote */
     /* description of the last launch, for finish() */
     uint64_t seg_len[CK_MAX_SEG + 2];
     uint32_t nseg;
@@ -316,8 +317,9 @@ cudaError_t b2d_crc32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint32_
     return cudaSuccess;
 }
 
-cudaError_t b2d_adler32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint32_t start, uint32_t *out, cudaStream_t st) {
-    if (n == 0) { *out = start; return cudaSuccess; }
+cudaError_t b2d_adler32_dev_launch(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, cudaStream_t st) {
+    w->adler_g = 0;
+    if (n == 0) return cudaSuccess;
     uint64_t head = (16 - ((uintptr_t)d & 15)) & 15;
     if (head > n) head = n;
     const uint64_t npieces = (n - head) / 16;
@@ -334,12 +336,15 @@ cudaError_t b2d_adler32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint3
     k_adler_edges<<<1, 2, 0, st>>>(r0, 0, r1, head + npieces * 16, n, w->d_parts);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    e = cudaMemcpyAsync(w->h_parts, w->d_parts, (2 + G) * sizeof(adler_part), cudaMemcpyDeviceToHost, st);
-    if (e != cudaSuccess) return e;
-    e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) return e;
+    w->adler_g = 2 + G;
+    return cudaMemcpyAsync(w->h_parts, w->d_parts, (2 + G) * sizeof(adler_part), cudaMemcpyDeviceToHost, st);
+}
+
+/* after the stream has passed the launch: fold the partial sums into adler32(start, data[0..n)) */
+uint32_t b2d_adler32_dev_finish(b2d_cksum_ws *w, uint64_t n, uint32_t start) {
+    if (n == 0) return start;
     uint64_t S1 = 0, P = 0, Q = 0;
-    for (uint32_t i = 0; i < 2 + G; ++i) {
+    for (uint32_t i = 0; i < w->adler_g; ++i) {
         S1 = (S1 + w->h_parts[i].s1 % ADLER_BASE) % ADLER_BASE;
         P = (P + w->h_parts[i].p) % ADLER_BASE;
         Q = (Q + w->h_parts[i].q % ADLER_BASE) % ADLER_BASE;
@@ -347,6 +352,15 @@ cudaError_t b2d_adler32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint3
     const uint64_t a = start & 0xffffu, b = (start >> 16) & 0xffffu;
     const uint64_t s1 = (a + S1) % ADLER_BASE;
     const uint64_t s2 = (b + (n % ADLER_BASE) * a % ADLER_BASE + P + ADLER_BASE - Q) % ADLER_BASE;
-    *out = (uint32_t)(s1 | (s2 << 16));
+    return (uint32_t)(s1 | (s2 << 16));
+}
+
+cudaError_t b2d_adler32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint32_t start, uint32_t *out, cudaStream_t st) {
+    if (n == 0) { *out = start; return cudaSuccess; }
+    cudaError_t e = b2d_adler32_dev_launch(w, d, n, st);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    *out = b2d_adler32_dev_finish(w, n, start);
     return cudaSuccess;
 }

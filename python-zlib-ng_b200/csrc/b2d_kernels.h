@@ -41,6 +41,8 @@ cudaError_t b2d_adler32_dev(b2d_cksum_ws *ws, const uint8_t *d, uint64_t n, uint
 /* asynchronous halves, for callers that overlap them with the deflate kernels */
 cudaError_t b2d_crc32_dev_launch(b2d_cksum_ws *ws, const uint8_t *d, uint64_t n, cudaStream_t st);
 uint32_t b2d_crc32_dev_finish(b2d_cksum_ws *ws, uint64_t n, uint32_t start);
+cudaError_t b2d_adler32_dev_launch(b2d_cksum_ws *ws, const uint8_t *d, uint64_t n, cudaStream_t st);
+uint32_t b2d_adler32_dev_finish(b2d_cksum_ws *ws, uint64_t n, uint32_t start);
 
 /* host GF(2) helpers (b2d_checksum.cu) */
 uint32_t b2d_host_crc32_combine(uint32_t crc1, uint32_t crc2, uint64_t len2);

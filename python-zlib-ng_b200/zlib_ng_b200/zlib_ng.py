@@ -63,7 +63,7 @@ error = _stdzlib.error            # one exception type for both halves of the mo
 
 _WINDOW = 32768
 _BLOCK = 131072                   # device block; streaming cuts happen on multiples of it
-_STREAM_THRESHOLD = 4 << 20       # compressobj submits to the GPU once this much input is pending
+_STREAM_THRESHOLD = 32 << 20      # compressobj submits to the GPU once this much input is pending
 _UINT32_MAX = 0xFFFFFFFF
 
 
@@ -128,22 +128,69 @@ def crc32_combine(crc1, crc2, crc2_length, /):
 
 
 # ------------------------------------------------------------------ raw deflate call
-def _deflate(data_addr, n, zdict: bytes, level: int, wbits_abs: int, final: bool, crc=None, adler=None):
-    """-> (raw deflate bytes, crc or None, adler or None)"""
+_api = ctypes.pythonapi
+_api.PyBytes_FromStringAndSize.restype = ctypes.c_void_p
+_api.PyBytes_FromStringAndSize.argtypes = [ctypes.c_void_p, ctypes.c_ssize_t]
+_api.PyBytes_AsString.restype = ctypes.c_void_p
+_api.PyBytes_AsString.argtypes = [ctypes.c_void_p]
+_api._PyBytes_Resize.restype = ctypes.c_int
+_api._PyBytes_Resize.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_ssize_t]
+_api.Py_DecRef.restype = None
+_api.Py_DecRef.argtypes = [ctypes.c_void_p]
+
+
+class _OutBytes:
+    """An uninitialised bytes object the library writes into, trimmed in place afterwards: what
+    arrange_output_buffer does in the reference (zlib_ngmodule.c:149-197) — no zero fill of the
+    worst-case size and no copy of the result."""
+
+    def __init__(self, cap: int):
+        self._p = _api.PyBytes_FromStringAndSize(None, cap)
+        if not self._p:
+            raise MemoryError
+        self.addr = _api.PyBytes_AsString(self._p)
+        self.cap = cap
+
+    def finish(self, size: int) -> bytes:
+        pp = ctypes.c_void_p(self._p)
+        self._p = None
+        if _api._PyBytes_Resize(ctypes.byref(pp), size) != 0:      # frees the object on failure
+            raise MemoryError
+        obj = ctypes.cast(pp, ctypes.py_object).value              # takes a second reference
+        _api.Py_DecRef(pp)                                         # drop ours
+        return obj
+
+    def __del__(self):
+        if getattr(self, "_p", None):
+            _api.Py_DecRef(ctypes.c_void_p(self._p))
+            self._p = None
+
+
+def _deflate(data_addr, n, zdict: bytes, level: int, wbits_abs: int, final: bool, crc=None, adler=None,
+             head: bytes = b"", tail_fn=None):
+    """-> (head + raw deflate bytes + tail_fn(crc, adler), crc or None, adler or None) in one bytes object"""
     L = _native.lib()
     cap = int(L.b2d_deflate_bound(n)) + 8
-    out = ctypes.create_string_buffer(cap)
+    out = _OutBytes(len(head) + cap + 16)
     out_n = ctypes.c_uint64(0)
     c_crc = ctypes.c_uint32(crc) if crc is not None else None
     c_ad = ctypes.c_uint32(adler) if adler is not None else None
     rc = L.b2d_deflate_host(_ctx().handle, level, wbits_abs, data_addr, n, zdict if zdict else None, len(zdict),
-                            1 if final else 0, ctypes.cast(out, ctypes.c_void_p), cap, ctypes.byref(out_n),
+                            1 if final else 0, ctypes.c_void_p(out.addr + len(head)), cap, ctypes.byref(out_n),
                             ctypes.byref(c_crc) if c_crc is not None else None,
                             ctypes.byref(c_ad) if c_ad is not None else None)
     if rc:
         _raise(rc, "while compressing data")
-    return (ctypes.string_at(out, out_n.value), c_crc.value if c_crc is not None else None,
-            c_ad.value if c_ad is not None else None)
+    r_crc = c_crc.value if c_crc is not None else None
+    r_ad = c_ad.value if c_ad is not None else None
+    size = len(head) + out_n.value
+    if head:
+        ctypes.memmove(out.addr, head, len(head))
+    if tail_fn is not None:
+        tail = tail_fn(r_crc, r_ad)
+        ctypes.memmove(out.addr + size, tail, len(tail))
+        size += len(tail)
+    return out.finish(size), r_crc, r_ad
 
 
 def _wrapper(wbits: int):
@@ -191,11 +238,11 @@ def compress(data, /, level=Z_DEFAULT_COMPRESSION, wbits=MAX_WBITS):
     lvl = _level(level)
     addr, n, keep = _native._addr(data)
     if kind == "zlib":
-        body, _, ad = _deflate(addr, n, b"", lvl, wb, True, adler=1)
-        return _zlib_header(lvl, wb, b"") + body + struct.pack(">I", ad)
+        return _deflate(addr, n, b"", lvl, wb, True, adler=1, head=_zlib_header(lvl, wb, b""),
+                        tail_fn=lambda c, a: struct.pack(">I", a))[0]
     if kind == "gzip":
-        body, crc, _ = _deflate(addr, n, b"", lvl, wb, True, crc=0)
-        return _gzip_header(lvl) + body + struct.pack("<II", crc, n & _UINT32_MAX)
+        return _deflate(addr, n, b"", lvl, wb, True, crc=0, head=_gzip_header(lvl),
+                        tail_fn=lambda c, a: struct.pack("<II", c, n & _UINT32_MAX))[0]
     body, _, _ = _deflate(addr, n, b"", lvl, wb, True)
     del keep
     return body
@@ -231,12 +278,8 @@ class _Compress:
             return _gzip_header(self._level)
         return b""
 
-    def _submit(self, nbytes: int, final: bool) -> bytes:
-        chunk = bytes(self._pending[:nbytes])
-        del self._pending[:nbytes]
-        addr, n, keep = _native._addr(chunk)
-        if n == 0 and not final and not self._flush_empty:
-            return b""
+    def _run(self, addr: int, n: int, final: bool) -> bytes:
+        """n bytes at addr -> raw deflate bytes primed with the stream's last 32 KiB; updates checksums and tail"""
         body, crc, ad = _deflate(addr, n, self._tail, self._level, self._wb, final,
                                  crc=self._crc if (self._kind == "gzip" or self._kind_crc) else None,
                                  adler=self._adler if self._kind == "zlib" else None)
@@ -245,7 +288,24 @@ class _Compress:
         if ad is not None:
             self._adler = ad
         self._total += n
-        self._tail = (self._tail + chunk)[-_WINDOW:] if n < _WINDOW else chunk[-_WINDOW:]
+        if n >= _WINDOW:
+            self._tail = ctypes.string_at(addr + n - _WINDOW, _WINDOW)
+        elif n:
+            self._tail = (self._tail + ctypes.string_at(addr, n))[-_WINDOW:]
+        return body
+
+    def _submit(self, nbytes: int, final: bool) -> bytes:
+        """the first nbytes of the pending buffer, in place (no copy of the input on the Python side)"""
+        if nbytes == 0:
+            if not final and not self._flush_empty:
+                return b""
+            return self._run(0, 0, final)
+        hold = (ctypes.c_char * len(self._pending)).from_buffer(self._pending)
+        try:
+            body = self._run(ctypes.addressof(hold), nbytes, final)
+        finally:
+            del hold                      # releases the export so that the bytearray can shrink again
+        del self._pending[:nbytes]
         return body
 
     _flush_empty = False
@@ -256,10 +316,18 @@ class _Compress:
             if self._finished:
                 raise error("Error -2 while compressing data: inconsistent stream state")
             mv = memoryview(data)
-            self._pending += mv.cast("B") if mv.ndim == 1 and mv.c_contiguous else bytes(mv)
+            mv = mv.cast("B") if mv.ndim == 1 and mv.c_contiguous else memoryview(bytes(mv))
             out = b""
+            if not self._pending and mv.nbytes >= _STREAM_THRESHOLD:
+                # a large write on an empty buffer: its whole blocks go straight from the caller's memory
+                k = mv.nbytes // _BLOCK * _BLOCK
+                addr, _, keep = _native._addr(mv)
+                out = self._header() + self._run(addr, k, False)
+                del keep
+                mv = mv[k:]
+            self._pending += mv
             if len(self._pending) >= _STREAM_THRESHOLD:
-                out = self._header() + self._submit(len(self._pending) // _BLOCK * _BLOCK, False)
+                out += self._header() + self._submit(len(self._pending) // _BLOCK * _BLOCK, False)
             return out
 
     def flush(self, mode=Z_FINISH, /):

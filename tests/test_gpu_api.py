@@ -156,13 +156,20 @@ def test_pair_compress_equals_compressobj(zng, fastq):
             assert b"".join(parts) + co.flush() == one
 
 
-def test_compressobj_streams_large_input_incrementally(zng):
+def test_compressobj_streams_large_input_incrementally(zng, monkeypatch):
+    monkeypatch.setattr(zng, "_STREAM_THRESHOLD", 4 << 20)
     data = synthdata.make("mixed", 12_000_000, 4).tobytes()
     co = zng.compressobj(6)
     pieces = [co.compress(data[i:i + 1_000_000]) for i in range(0, len(data), 1_000_000)]
     assert sum(1 for p in pieces if p) >= 2          # output appears before flush
     out = b"".join(pieces) + co.flush()
     assert zlib.decompress(out) == data
+    assert out == zng.compress(data, 6)              # however the writes were sliced
+    # one write larger than the threshold goes to the GPU straight from the caller's buffer
+    co = zng.compressobj(6)
+    first = co.compress(memoryview(data)[:9_000_001])
+    assert first
+    assert first + co.compress(data[9_000_001:]) + co.flush() == out
     with pytest.raises(zng.error):
         co.compress(b"more")
 

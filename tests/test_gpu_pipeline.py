@@ -156,6 +156,35 @@ def _adler(nat, ctx, data, start=1):
     return v.value
 
 
+def test_checksums_and_deflate_over_many_pieces_pageable_and_pinned(nat):
+    """Host buffers larger than one batch take the overlapped path (pinned staging slots for pageable
+    memory, direct DMA for pinned): same values / bytes as one piece, for crc32, adler32 and deflate with
+    either checksum."""
+    data = synthdata.make("mixed", 5_300_001, 41).tobytes()
+    small = nat.Context(0, 1 << 20)
+    big = nat.Context(0, 16 << 20)
+    try:
+        for start in (0, 0xDEADBEEF):
+            assert _crc(nat, small, data, start) == zlib.crc32(data, start)
+            assert _adler(nat, small, data, start) == zlib.adler32(data, start)
+        want = deflate_host(nat, big, data, 6, final=True)
+        got = deflate_host(nat, small, data, 6, final=True)
+        assert got == want
+        assert got[1] == zlib.crc32(data) and got[2] == zlib.adler32(data)
+        # pinned source
+        p = small.host_alloc(len(data))
+        ctypes.memmove(p, data, len(data))
+        v = ctypes.c_uint32(0)
+        nat.check(nat.lib().b2d_crc32(small.handle, 7, ctypes.c_void_p(p), len(data), ctypes.byref(v)))
+        assert v.value == zlib.crc32(data, 7)
+        nat.check(nat.lib().b2d_adler32(small.handle, 7, ctypes.c_void_p(p), len(data), ctypes.byref(v)))
+        assert v.value == zlib.adler32(data, 7)
+        small.host_free(p)
+    finally:
+        small.close()
+        big.close()
+
+
 def test_checksum_kat_rows(nat, ctx):
     from helpers import b64
     kat = golden("checksum_kat.json")
