@@ -57,7 +57,12 @@ int b2d_compress_and_crc(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t 
  * same stream as above; `final` != 0 appends the BFINAL empty fixed block 03 00
  * (what gzip_ng_threaded.py:333 appends).  window_bits (9..15) caps match
  * distances at 2^window_bits for the small-wbits forms.  crc / adler may be NULL; adler is the
- * Adler-32 of `data` continued from *adler's incoming value, crc likewise. */
+ * Adler-32 of `data` continued from *adler's incoming value, crc likewise.
+ * Every `level` argument of this library is 0..9, optionally with the zlib strategy in bits 8..11
+ * (B2D_LEVEL_STRATEGY): 1 Z_FILTERED (matches shorter than 6 are dropped), 2 Z_HUFFMAN_ONLY (no matches,
+ * deflate_huff.c), 3 Z_RLE (distance 1 only, deflate_rle.c), 4 Z_FIXED (no dynamic blocks, trees.c:677);
+ * what compressobj(strategy=...) passes (zlib_ngmodule.c:376-430). */
+#define B2D_LEVEL_STRATEGY(level, strategy) ((level) | ((strategy) << 8))
 int b2d_deflate_host(b2d_ctx *ctx, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
                      uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler);
 

@@ -59,7 +59,7 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
         uint32_t best = 0, bd = 0;
         if (maxl >= B2D_MIN_MATCH) {
             size_t cand = p;
-            uint32_t d = prevd[p];
+            uint32_t d = pol.search == B2D_SEARCH_RLE ? (p >= 1 ? 1u : 0u) : prevd[p];
             for (int step = 0; step < pol.depth && d != 0; step++) {
                 cand -= d;
                 size_t dist = p - cand;
@@ -67,7 +67,7 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
                 uint32_t l = 0;
                 while (l < maxl && buf[cand + l] == buf[p + l]) l++;
                 if (l > best) { best = l; bd = (uint32_t)dist; if (l >= (uint32_t)pol.nice || l == maxl) break; }
-                d = prevd[cand];
+                d = pol.search == B2D_SEARCH_RLE ? 0u : prevd[cand];
             }
         }
         match[p - D] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
@@ -93,6 +93,9 @@ static void twin_parse(const uint8_t *buf, size_t D, size_t n, size_t k, const u
             uint32_t l0 = b2d_match_len(m[i]);
             uint32_t l1 = i + 1 < len ? b2d_match_len(m[i + 1]) : 0;
             uint32_t l2 = i + 2 < len ? b2d_match_len(m[i + 2]) : 0;
+            if (l0 < (uint32_t)pol.min_take) l0 = 0;      /* Z_FILTERED: short matches count as none */
+            if (l1 < (uint32_t)pol.min_take) l1 = 0;
+            if (l2 < (uint32_t)pol.min_take) l2 = 0;
             uint32_t step = b2d_parse_step(l0, l1, l2, pol.lazy);
             if (step > 1) {
                 uint32_t dist = b2d_match_dist(m[i]);
@@ -152,9 +155,9 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     S->block_off = (uint64_t *)calloc(nb + 1, sizeof(uint64_t));
     uint16_t *head = (uint16_t *)malloc(sizeof(uint16_t) * B2D_HASH_SIZE_MAX);
     b2d_huff_scratch *scr = (b2d_huff_scratch *)malloc(sizeof *scr);
-    if (level > 0) {
+    if (pol.search != B2D_SEARCH_NONE) {
         for (size_t b = 0; b < nb; b++) {
-            twin_chains(buf, D, n, b, S->prevd, head, pol.hash_bits);
+            if (pol.search == B2D_SEARCH_CHAINS) twin_chains(buf, D, n, b, S->prevd, head, pol.hash_bits);
             twin_matches(buf, D, n, b, S->prevd, S->match, pol, max_dist);
         }
     }
@@ -162,7 +165,7 @@ size_t b2d_twin_deflate_ex(const uint8_t *buf, size_t D, size_t n, int level, ui
     for (size_t k = 0; k < nsub; k++) {
         if (!S->info[k].tok_count) continue;
         const uint32_t *H = S->hist + k * (size_t)B2D_HIST;
-        b2d_plan_subblock(H, H + B2D_LL_CODES, S->info[k].in_len, &S->plan[k], scr, level == 0);
+        b2d_plan_subblock(H, H + B2D_LL_CODES, S->info[k].in_len, &S->plan[k], scr, pol.blocks);
     }
     /* stage 5: sizes */
     uint64_t off = 0;

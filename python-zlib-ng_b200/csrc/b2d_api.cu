@@ -291,8 +291,15 @@ static int ensure_second_lane(b2d_ctx *c) {
     return B2D_OK;
 }
 
+/* kernels one batch launches at this level / strategy */
+static uint32_t pipeline_launches(int level) {
+    const b2d_policy pol = b2d_level_policy(level);
+    return 4u + (pol.search == B2D_SEARCH_CHAINS ? 1u : 0u) + (pol.search != B2D_SEARCH_NONE ? 1u : 0u);
+}
+
 /* fold the event pairs of `nb` profiled batches into the per-stage totals */
 static int prof_drain(b2d_ctx *c, int nb, int level) {
+    const b2d_policy pol = b2d_level_policy(level);
     CU(cudaStreamSynchronize(c->st));
     if (c->st2) CU(cudaStreamSynchronize(c->st2));
     for (int i = 0; i < nb; ++i)
@@ -300,7 +307,7 @@ static int prof_drain(b2d_ctx *c, int nb, int level) {
             float t = 0;
             CU(cudaEventElapsedTime(&t, c->pev[i][j], c->pev[i][j + 1]));
             c->stage_ms[j] += t;
-            if (level > 0 || j >= 2) c->stage_launches[j] += 1;
+            if (j >= 2 || (j == 0 && pol.search == B2D_SEARCH_CHAINS) || (j == 1 && pol.search != B2D_SEARCH_NONE)) c->stage_launches[j] += 1;
         }
     return B2D_OK;
 }
@@ -328,7 +335,7 @@ extern "C" int b2d_profile_read(b2d_ctx *c, double *stage_ms, uint64_t *stage_la
 extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
                                   uint64_t out_cap, uint64_t *out_n, uint32_t *crc, float *ms) {
     if (!c || !out_n || (!d_buf && n) || !d_out) return fail(B2D_STREAM_ERROR, "null argument");
-    if (level < 0 || level > 9) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    if (!b2d_level_valid(level)) return fail(B2D_STREAM_ERROR, "Bad compression level");
     if (dict_n > B2D_WINDOW) return fail(B2D_STREAM_ERROR, "device dictionary longer than 32768 bytes");
     if (((uintptr_t)d_buf & 15) || ((uintptr_t)d_out & 3)) return fail(B2D_STREAM_ERROR, "misaligned device pointer");
     if (out_cap < b2d_deflate_bound(n)) return fail(B2D_BUF_ERROR, "out_cap below b2d_deflate_bound(n)");
@@ -362,7 +369,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
             pe = c->pev[nprof++];
         }
         CU(b2d_launch_pipeline(&J, lane ? c->st2 : c->st, pe));
-        c->launches += level > 0 ? 6 : 4;
+        c->launches += pipeline_launches(level);
     }
     if (two) { CU(cudaEventRecord(c->ev_join, c->st2)); CU(cudaStreamWaitEvent(c->st, c->ev_join, 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
@@ -509,7 +516,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         b2d_job J; fill_job(c, &J, d_in[s], D, m, c->d_in_cap, level, d_out[s], max_dist, ln);
         J.total = d_total[s];
         CU(b2d_launch_pipeline(&J, cs[ln], nullptr));
-        c->launches += level > 0 ? 6 : 4;
+        c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
         if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
         if (adler_acc) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
@@ -572,7 +579,7 @@ static int checksum_host_pipelined(b2d_ctx *c, const uint8_t *data, uint64_t n, 
 extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
                                 uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc, uint32_t *adler) {
     if (!c || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
-    if (level < 0 || level > 9) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    if (!b2d_level_valid(level)) return fail(B2D_STREAM_ERROR, "Bad compression level");
     if (window_bits < 9 || window_bits > 15) return fail(B2D_STREAM_ERROR, "window_bits outside 9..15");
     const uint32_t max_dist = 1u << window_bits;
     std::lock_guard<std::mutex> g(c->mu);
@@ -627,7 +634,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
         b2d_job J; fill_job(c, &J, c->d_in, D, m, c->d_in_cap, level, c->d_out, max_dist);
         CU(b2d_launch_pipeline(&J, c->st, nullptr));
-        c->launches += level > 0 ? 6 : 4;
+        c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
         if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_in + D, m, c->st)); c->launches += crc_launches(c->d_in + D, m); }
         CU(cudaStreamSynchronize(c->st));

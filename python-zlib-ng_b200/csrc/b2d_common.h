@@ -55,7 +55,21 @@ typedef struct {
     int nice;      /* stop searching once a match this long is found             */
     int hash_bits; /* log2 of the head-table size: a smaller table keeps more blocks   */
                    /* resident per SM in the chain stage, at a little ratio            */
+    int level;     /* 0..9                                                        */
+    int strategy;  /* Z_DEFAULT_STRATEGY 0, Z_FILTERED 1, Z_HUFFMAN_ONLY 2, Z_RLE 3, Z_FIXED 4 */
+    int search;    /* B2D_SEARCH_*: where match candidates come from              */
+    int min_take;  /* shortest match the parse accepts (Z_FILTERED: 6, zlib-ng deflate_slow.c "TOO_FAR"/filtered rule) */
+    int blocks;    /* B2D_BLOCKS_*: which block types the plan may choose         */
 } b2d_policy;
+#define B2D_SEARCH_NONE   0   /* literals only: level 0 (stored anyway) and Z_HUFFMAN_ONLY (deflate_huff.c) */
+#define B2D_SEARCH_CHAINS 1
+#define B2D_SEARCH_RLE    2   /* distance 1 only: Z_RLE (deflate_rle.c)                                      */
+#define B2D_BLOCKS_ANY    0
+#define B2D_BLOCKS_STORED 1   /* level 0 (deflate_stored.c)                                                  */
+#define B2D_BLOCKS_NO_DYN 2   /* Z_FIXED: stored or fixed Huffman only (trees.c:677)                         */
+/* the C ABI's `level` argument carries the strategy in bits 8..11 */
+#define B2D_LEVEL(level, strategy) ((level) | ((strategy) << 8))
+B2D_HD int b2d_level_valid(int x) { return x >= 0 && (x & 0xff) <= 9 && (x >> 8) <= 4; }
 
 #ifndef D_L6
 #define D_L5 5
@@ -66,8 +80,11 @@ typedef struct {
 #define HB_L23 13
 #define HB_L456 13
 #endif
-B2D_HD b2d_policy b2d_level_policy(int level) {
+B2D_HD b2d_policy b2d_level_policy(int level_and_strategy) {
     b2d_policy p;
+    const int level = level_and_strategy & 0xff;
+    p.level = level;
+    p.strategy = (level_and_strategy >> 8) & 0xf;
     switch (level) {
         case 1:  p.depth = 1;  p.lazy = 0; p.nice = 258; p.hash_bits = HB_L1; break;
         case 2:  p.depth = 2;  p.lazy = 0; p.nice = 258; p.hash_bits = HB_L23; break;
@@ -79,6 +96,12 @@ B2D_HD b2d_policy b2d_level_policy(int level) {
         case 8:  p.depth = 32; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break;
         default: p.depth = 64; p.lazy = 2; p.nice = 258; p.hash_bits = 14; break; /* 9, and 0 (unused there) */
     }
+    p.search = B2D_SEARCH_CHAINS; p.min_take = 4; p.blocks = B2D_BLOCKS_ANY;
+    if (p.strategy == 1) p.min_take = 6;
+    if (p.strategy == 2) p.search = B2D_SEARCH_NONE;
+    if (p.strategy == 3) { p.search = B2D_SEARCH_RLE; p.depth = 1; }
+    if (p.strategy == 4) p.blocks = B2D_BLOCKS_NO_DYN;
+    if (level == 0) { p.search = B2D_SEARCH_NONE; p.blocks = B2D_BLOCKS_STORED; }
     return p;
 }
 

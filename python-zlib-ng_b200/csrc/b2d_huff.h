@@ -138,7 +138,7 @@ B2D_HD uint32_t b2d_fixed_ll_len(uint32_t sym) { return sym < 144u ? 8u : sym < 
 /* Build the plan of one sub-block from its histograms.
  * ll_freq must already count the end-of-block symbol (ll_freq[256] == 1).
  * in_len = input bytes the sub-block covers (for the stored alternative).
- * force_stored = level 0 (deflate_stored.c in the reference). */
+ * blocks = B2D_BLOCKS_*: level 0 forces stored (deflate_stored.c in the reference), Z_FIXED forbids dynamic. */
 /* after ll_len / d_len: trailing-zero trimming, run-length coding of the length sequence, bl_freq */
 B2D_HDN void b2d_plan_mid(b2d_huff_scratch *S) {
     int hlit = B2D_LL_CODES; while (hlit > 257 && S->ll_len[hlit - 1] == 0) hlit--;
@@ -166,7 +166,8 @@ B2D_HDN void b2d_plan_mid(b2d_huff_scratch *S) {
 
 /* after bl_len: costs, stored / fixed / dynamic choice, codes and header bits */
 B2D_HDN void b2d_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
-                          b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
+                          b2d_plan *P, b2d_huff_scratch *S, int blocks) {
+    const int force_stored = blocks == B2D_BLOCKS_STORED, no_dyn = blocks == B2D_BLOCKS_NO_DYN;
     const uint8_t bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
     const int hlit = S->hlit, hdist = S->hdist, nseq = S->nseq;
     int hclen = B2D_BL_CODES; while (hclen > 4 && S->bl_len[bl_order[hclen - 1]] == 0) hclen--;
@@ -195,12 +196,12 @@ B2D_HDN void b2d_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint3
 
     for (int i = 0; i < B2D_HDR_WORDS; i++) P->hdr[i] = 0;
     P->hdr_bits = 0; P->pad = 0;
-    if ((force_stored || (sto_cost <= dyn_cost && sto_cost <= fix_cost)) && in_len <= 65535u) {
+    if ((force_stored || ((sto_cost <= dyn_cost || no_dyn) && sto_cost <= fix_cost)) && in_len <= 65535u) {
         P->type = 0; P->body_bits = 0;
         b2d_put_bits(P->hdr, &P->hdr_bits, 0u, 3);          /* BFINAL=0, BTYPE=00 */
         for (int i = 0; i < B2D_LL_CODES; i++) P->ll_code[i] = 0;
         for (int i = 0; i < B2D_D_CODES; i++) P->d_code[i] = 0;
-    } else if (fix_cost <= dyn_cost) {
+    } else if (fix_cost <= dyn_cost || no_dyn) {
         P->type = 1; P->body_bits = fix_body;
         b2d_put_bits(P->hdr, &P->hdr_bits, 2u, 3);          /* BFINAL=0, BTYPE=01 */
         for (int i = 0; i < B2D_LL_CODES; i++) {
@@ -231,12 +232,12 @@ B2D_HDN void b2d_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint3
 }
 
 B2D_HDN void b2d_plan_subblock(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
-                               b2d_plan *P, b2d_huff_scratch *S, int force_stored) {
+                               b2d_plan *P, b2d_huff_scratch *S, int blocks) {
     b2d_huff_lengths(ll_freq, B2D_LL_CODES, 15, S->ll_len, S);
     b2d_huff_lengths(d_freq, B2D_D_CODES, 15, S->d_len, S);
     b2d_plan_mid(S);
     b2d_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S);
-    b2d_plan_end(ll_freq, d_freq, in_len, P, S, force_stored);
+    b2d_plan_end(ll_freq, d_freq, in_len, P, S, blocks);
 }
 
 #endif /* B2D_HUFF_H */

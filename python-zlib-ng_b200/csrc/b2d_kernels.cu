@@ -157,7 +157,7 @@ __device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
         const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
-        uint32_t max_dist) {
+        uint32_t max_dist, int rle) {
     extern __shared__ __align__(16) uint8_t smem2[];
     uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES);       /* 2*(W+SUB)+16 */
@@ -185,7 +185,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         const uint64_t bstart = D + blk * (uint64_t)B2D_BLOCK;
         const uint64_t span_al = (bstart - (bstart < B2D_WINDOW ? bstart : B2D_WINDOW)) & ~(uint64_t)7;
         const uint4 *src = reinterpret_cast<const uint4 *>(prevd + blk * (uint64_t)B2D_LINKS + (wp_al - span_al));
-        for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
+        if (!rle) for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
     }
     __syncthreads();
     const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
@@ -201,7 +201,8 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         const uint32_t pr = tile_off + t;                   /* smem byte index of this position */
         /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
          * pushes the running distance past max_dist, so one compare ends the walk either way */
-        uint32_t dist = s_prev[pr - poff];
+        /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links exist */
+        uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : s_prev[pr - poff];
         if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
             /* the position's first 16 bytes stay in registers: most compares end inside them */
             uint32_t own[4];
@@ -270,7 +271,8 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
 
 __global__ void __launch_bounds__(K3_THREADS)
 k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict__ match,
-        uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy) {
+        uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy,
+        uint32_t min_take) {
     __shared__ __align__(16) uint8_t s_len[B2D_SUB + 16];
     __shared__ uint32_t s_reach[K3_WORDS], s_base[K3_WORDS];
     __shared__ uint32_t s_hist[B2D_HIST];
@@ -297,8 +299,9 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
             for (uint32_t j = 0; j < 8; ++j) {
                 const uint32_t i = i0 + j * K3_THREADS + tid;
                 const uint32_t l0 = v[j].x >> 16, l1 = v[j].y >> 16, l2 = v[j].z >> 16, l3 = v[j].w >> 16;
-                if (i < full)
-                    W[i] = (l0 ? l0 - 3u : 0u) | ((l1 ? l1 - 3u : 0u) << 8) | ((l2 ? l2 - 3u : 0u) << 16) | ((l3 ? l3 - 3u : 0u) << 24);
+                if (i < full)      /* matches below min_take (Z_FILTERED) count as none */
+                    W[i] = (l0 >= min_take ? l0 - 3u : 0u) | ((l1 >= min_take ? l1 - 3u : 0u) << 8) |
+                           ((l2 >= min_take ? l2 - 3u : 0u) << 16) | ((l3 >= min_take ? l3 - 3u : 0u) << 24);
             }
         }
         for (uint32_t i = full + tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
@@ -307,7 +310,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
             for (uint32_t j = 0; j < 4; ++j) {
                 const uint32_t pos = 4 * i + j;
                 const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
-                pk |= (l ? l - 3u : 0u) << (8 * j);
+                pk |= (l >= min_take ? l - 3u : 0u) << (8 * j);
             }
             W[i] = pk;
         }
@@ -518,7 +521,8 @@ __constant__ uint8_t c_bl_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 
 
 /* b2d_plan_end by the warp (same results): costs by reduction, code tables and header bits in parallel */
 __device__ __forceinline__ void warp_plan_end(const uint32_t *ll_freq, const uint32_t *d_freq, uint32_t in_len,
-                                              b2d_plan *P, b2d_huff_scratch *S, int force_stored, uint32_t lane) {
+                                              b2d_plan *P, b2d_huff_scratch *S, int blocks, uint32_t lane) {
+    const bool force_stored = blocks == B2D_BLOCKS_STORED, no_dyn = blocks == B2D_BLOCKS_NO_DYN;
     const int hlit = S->hlit, hdist = S->hdist, nseq = S->nseq;
     int hclen = B2D_BL_CODES;
     while (hclen > 4 && S->bl_len[c_bl_order[hclen - 1]] == 0) hclen--;
@@ -544,11 +548,11 @@ __device__ __forceinline__ void warp_plan_end(const uint32_t *ll_freq, const uin
     const uint32_t sto_cost = 3u + 7u + 32u + 8u * in_len;   /* worst-case alignment pad */
     for (uint32_t i = lane; i < B2D_HDR_WORDS; i += 32) P->hdr[i] = 0;
     __syncwarp();
-    if ((force_stored || (sto_cost <= dyn_cost && sto_cost <= fix_cost)) && in_len <= 65535u) {
+    if ((force_stored || ((sto_cost <= dyn_cost || no_dyn) && sto_cost <= fix_cost)) && in_len <= 65535u) {
         for (uint32_t i = lane; i < B2D_LL_CODES; i += 32) P->ll_code[i] = 0;
         if (lane < B2D_D_CODES) P->d_code[lane] = 0;
         if (lane == 0) { P->type = 0; P->body_bits = 0; P->pad = 0; P->hdr_bits = 3; }   /* BFINAL=0, BTYPE=00: three zero bits */
-    } else if (fix_cost <= dyn_cost) {
+    } else if (fix_cost <= dyn_cost || no_dyn) {
         for (uint32_t i = lane; i < B2D_LL_CODES; i += 32) {
             const uint32_t l = b2d_fixed_ll_len(i);
             const uint32_t c = i < 144u ? 0x30u + i : i < 256u ? 0x190u + (i - 144u) : i < 280u ? i - 256u : 0xC0u + (i - 280u);
@@ -597,7 +601,7 @@ __device__ __forceinline__ void warp_plan_end(const uint32_t *ll_freq, const uin
 
 __global__ void __launch_bounds__(K4_WARPS * 32)
 k_plan(const uint32_t *__restrict__ hist, const b2d_subinfo *__restrict__ info, b2d_plan *__restrict__ plan,
-       uint32_t nsub, int force_stored) {
+       uint32_t nsub, int blocks) {
     extern __shared__ __align__(16) uint8_t smem4[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t k = blockIdx.x * K4_WARPS + warp;
@@ -616,7 +620,7 @@ k_plan(const uint32_t *__restrict__ hist, const b2d_subinfo *__restrict__ info, 
     if (lane == 0) b2d_plan_mid(S);
     __syncwarp();
     warp_huff_lengths(S->bl_freq, B2D_BL_CODES, 7, S->bl_len, S, lane);
-    warp_plan_end(W->hist, W->hist + B2D_LL_CODES, info[k].in_len, &W->P, S, force_stored, lane);
+    warp_plan_end(W->hist, W->hist + B2D_LL_CODES, info[k].in_len, &W->P, S, blocks, lane);
     const uint32_t *src = reinterpret_cast<const uint32_t *>(&W->P);
     uint32_t *dst = reinterpret_cast<uint32_t *>(&plan[k]);
     for (uint32_t i = lane; i < sizeof(b2d_plan) / 4; i += 32) dst[i] = src[i];
@@ -855,7 +859,7 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     const uint8_t *data = J->buf + J->D;
 #define MARK(i) do { if (ev) { cudaError_t e_ = cudaEventRecord(ev[i], st); if (e_ != cudaSuccess) return e_; } } while (0)
     MARK(0);
-    if (J->level > 0) {
+    if (pol.search == B2D_SEARCH_CHAINS) {
         /* the head table is 2^hash_bits u16: the smaller it is the more blocks an SM keeps in flight */
         switch (pol.hash_bits) {
             case 11: k_chains<11><<<nblocks, 32, k1_smem(11), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd); break;
@@ -865,17 +869,17 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
         }
     }
     MARK(1);
-    if (J->level > 0) {
+    if (pol.search != B2D_SEARCH_NONE) {
         k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
-                                                    pol.depth, (uint32_t)pol.nice, J->max_dist);
+                                                    pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
         if (e != cudaSuccess) return e;
     }
     MARK(2);
-    k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy);
+    k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy, (uint32_t)pol.min_take);
     MARK(3);
-    k_plan<<<(nsub + K4_WARPS - 1) / K4_WARPS, K4_WARPS * 32, k4_smem(), st>>>(J->hist, J->info, J->plan, nsub, J->level == 0);
+    k_plan<<<(nsub + K4_WARPS - 1) / K4_WARPS, K4_WARPS * 32, k4_smem(), st>>>(J->hist, J->info, J->plan, nsub, pol.blocks);
     MARK(4);
     if (J->scan_wait) { cudaError_t e = cudaStreamWaitEvent(st, J->scan_wait, 0); if (e != cudaSuccess) return e; }
     k_scan<<<1, 1024, 0, st>>>(J->plan, J->info, nsub, nblocks, J->block_off, J->total);

@@ -255,8 +255,9 @@ class _Compress:
     not depend on how the caller sliced its writes (test_pair in the reference's
     tests/test_zlib_compliance.py:295-306 relies on compress() == compressobj())."""
 
-    def __init__(self, level, wbits, zdict):
+    def __init__(self, level, wbits, zdict, strategy=Z_DEFAULT_STRATEGY):
         self._level = level
+        self._strategy = strategy          # carried in bits 8..11 of the C ABI's level argument (B2D_LEVEL)
         self._kind, self._wb = _wrapper(wbits)
         self._zdict = bytes(zdict) if zdict is not None else b""
         self._tail = self._zdict[-(1 << self._wb):][-_WINDOW:]
@@ -280,7 +281,7 @@ class _Compress:
 
     def _run(self, addr: int, n: int, final: bool) -> bytes:
         """n bytes at addr -> raw deflate bytes primed with the stream's last 32 KiB; updates checksums and tail"""
-        body, crc, ad = _deflate(addr, n, self._tail, self._level, self._wb, final,
+        body, crc, ad = _deflate(addr, n, self._tail, self._level | (self._strategy << 8), self._wb, final,
                                  crc=self._crc if (self._kind == "gzip" or self._kind_crc) else None,
                                  adler=self._adler if self._kind == "zlib" else None)
         if crc is not None:
@@ -390,7 +391,7 @@ def compressobj(level=Z_DEFAULT_COMPRESSION, method=DEFLATED, wbits=MAX_WBITS, m
         raise ValueError("Invalid initialization option")
     _wrapper(wbits)
     _ctx()
-    return _Compress(_level(level), wbits, zdict)
+    return _Compress(_level(level), wbits, zdict, strategy)
 
 
 class _ParallelCompress:

@@ -174,6 +174,21 @@ def test_compressobj_streams_large_input_incrementally(zng, monkeypatch):
         co.compress(b"more")
 
 
+def test_compressobj_strategies_change_the_stream(zng):
+    """strategy is honoured, not just accepted (deflate_huff.c / deflate_rle.c / trees.c:677)"""
+    data = b"".join(bytes([i % 251]) * 900 for i in range(400)) + b"abcdefgh" * 20_000
+    size = {}
+    for strat in (zng.Z_DEFAULT_STRATEGY, zng.Z_FILTERED, zng.Z_HUFFMAN_ONLY, zng.Z_RLE, zng.Z_FIXED):
+        co = zng.compressobj(6, zng.DEFLATED, -15, 8, strat)
+        out = co.compress(data) + co.flush()
+        assert zlib.decompress(out, wbits=-15) == data
+        size[strat] = len(out)
+        if strat == zng.Z_FIXED:
+            assert (out[0] >> 1) & 3 in (0, 1)
+    assert size[zng.Z_HUFFMAN_ONLY] > 10 * size[zng.Z_DEFAULT_STRATEGY]
+    assert size[zng.Z_DEFAULT_STRATEGY] < size[zng.Z_RLE] < size[zng.Z_HUFFMAN_ONLY]
+
+
 @pytest.mark.parametrize("level", [0, 1, 6, 9])
 def test_flush_modes(zng, level):
     data = synthdata.make("fastq", 300_000, 8).tobytes()

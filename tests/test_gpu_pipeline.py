@@ -100,6 +100,19 @@ def test_blocks_are_independent_given_their_dictionary(nat, ctx, level):
     assert twin_deflate(data, level) == whole
 
 
+@pytest.mark.parametrize("strategy", [1, 2, 3, 4])
+@pytest.mark.parametrize("level", [1, 6])
+def test_strategies_match_twin(nat, ctx, level, strategy):
+    """level | strategy << 8 (B2D_LEVEL_STRATEGY): Z_FILTERED, Z_HUFFMAN_ONLY, Z_RLE, Z_FIXED"""
+    data = synthdata.make("mixed", 700_001, 21).tobytes() + b"\x07" * 70_000 + b"abcdefgh" * 9_000
+    lv = level | (strategy << 8)
+    out = deflate_host(nat, ctx, data, lv)[0]
+    assert zlib.decompressobj(-15).decompress(out) == data
+    assert out == twin_deflate(data, lv)
+    if strategy == 4:
+        assert (out[0] >> 1) & 3 in (0, 1)
+
+
 def test_empty_and_final(nat, ctx):
     out, crc, adler = deflate_host(nat, ctx, b"", 6)
     assert out == b"\x00\x00\x00\xff\xff" and crc == 0 and adler == 1

@@ -124,3 +124,25 @@ def test_ratio_vs_reference_golden(row):
     ours = len(twin_deflate(data, row["level"]))
     assert ours <= 1.03 * row["threaded_blocks"], (ours, row["threaded_blocks"], ours / row["threaded_blocks"])
     assert ours <= 1.03 * row["single_stream"]
+
+
+@pytest.mark.parametrize("level", [1, 6])
+def test_twin_strategies(level):
+    """compressobj(strategy=...) semantics of the reference (deflate_huff.c, deflate_rle.c, trees.c:677, the
+    Z_FILTERED rule of deflate_slow.c) in the CPU twin the GPU is compared with."""
+    text = synthdata.make("mixed", 300_000, 3).tobytes()
+    runs = b"".join(bytes([i % 251]) * 700 for i in range(300))
+    periodic = b"abcdefgh" * 30_000
+    size = {}
+    for name, data in (("text", text), ("runs", runs), ("periodic", periodic)):
+        for strat in range(5):
+            out = twin_deflate(data, level | (strat << 8))
+            assert zlib.decompressobj(-15).decompress(out) == data
+            size[name, strat] = len(out)
+            if strat == 4:        # Z_FIXED: first block is stored (00) or fixed (01), never dynamic (10)
+                assert (out[0] >> 1) & 3 in (0, 1)
+    assert size["runs", 2] > 20 * size["runs", 0]            # Huffman only: runs are not found
+    assert size["runs", 3] <= 1.1 * size["runs", 0]          # RLE finds them
+    assert size["periodic", 3] > 20 * size["periodic", 0]    # ... but not a period of 8
+    assert size["text", 1] != size["text", 0]                # filtered drops matches shorter than 6
+    assert size["text", 4] >= size["text", 0]
