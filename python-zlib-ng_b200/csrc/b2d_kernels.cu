@@ -277,6 +277,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     __shared__ uint32_t s_reach[K3_WORDS], s_base[K3_WORDS];
     __shared__ uint32_t s_hist[B2D_HIST];
     __shared__ uint32_t s_wsum[K3_THREADS / 32];
+    __shared__ uint8_t s_lsym[256], s_dsym[512];   /* length symbol of len-3; distance symbol of d-1 (d-1 < 256) or 256 + ((d-1) >> 7) */
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint64_t k = blockIdx.x;
     const uint64_t sub_start = k * (uint64_t)B2D_SUB;
@@ -317,6 +318,12 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     }
     for (uint32_t i = tid; i < B2D_HIST; i += K3_THREADS) s_hist[i] = 0;
     for (uint32_t i = tid; i < K3_WORDS; i += K3_THREADS) s_reach[i] = 0;
+    {   /* K3_THREADS == 256: one table row per thread */
+        uint32_t sy, eb, ev;
+        b2d_len_sym(tid, &sy, &eb, &ev); s_lsym[tid] = (uint8_t)sy;
+        b2d_dist_sym(tid, &sy, &eb, &ev); s_dsym[tid] = (uint8_t)sy;
+        b2d_dist_sym(tid << 7, &sy, &eb, &ev); s_dsym[256 + tid] = (uint8_t)sy;
+    }
     __syncthreads();
     /* lazy rule applied to every position at once (b2d_parse_step): a position keeps its length byte if
      * a match would be taken there, else 0.  Results sit in registers until every thread has read. */
@@ -381,9 +388,12 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     for (uint32_t j = 0; j < 4; ++j) { s_base[4 * tid + j] = run; run += c[j]; }
     __syncthreads();
     /* compaction: a warp takes 4 bitmap words per trip (lane = bit) and issues the global loads of
-     * all four before using any, so their latency overlaps */
-    uint32_t *t = tok + sub_start;
+     * all four before using any, so their latency overlaps.  Symbols come from small tables (the
+     * zlib-ng _length_code / _dist_code idea, trees_tbl.h:76-132); one store and one literal/length
+     * count per token, whatever its kind. */
+    const uint32_t tbase = (uint32_t)sub_start;           /* a batch is at most 2 GiB: token indices fit 32 bits */
     const uint8_t *src = data + sub_start;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     for (uint32_t w0 = warp * 4u; w0 < K3_WORDS; w0 += (K3_THREADS / 32) * 4u) {
         uint32_t rw[4], val[4];
         bool reached[4], take[4];
@@ -399,19 +409,16 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j) {
             if (!reached[j]) continue;
-            const uint32_t idx = s_base[w0 + j] + __popc(rw[j] & ((1u << lane) - 1u));
+            const uint32_t idx = s_base[w0 + j] + __popc(rw[j] & lt_mask);
+            uint32_t tv = val[j], sym = val[j];
             if (take[j]) {
-                const uint32_t ml = b2d_match_len(val[j]), md = b2d_match_dist(val[j]);
-                uint32_t ls, le, lv, ds, de, dv;
-                b2d_len_sym(ml - 3u, &ls, &le, &lv);
-                b2d_dist_sym(md - 1u, &ds, &de, &dv);
-                atomicAdd(&s_hist[257u + ls], 1u);
-                atomicAdd(&s_hist[B2D_LL_CODES + ds], 1u);
-                t[idx] = b2d_tok_match(ml, md);
-            } else {
-                atomicAdd(&s_hist[val[j]], 1u);
-                t[idx] = val[j];
+                const uint32_t ml = b2d_match_len(val[j]), d1 = b2d_match_dist(val[j]) - 1u;
+                sym = 257u + s_lsym[ml - 3u];
+                atomicAdd(&s_hist[B2D_LL_CODES + s_dsym[d1 < 256u ? d1 : 256u + (d1 >> 7)]], 1u);
+                tv = 0x80000000u | ((ml - 3u) << 15) | d1;      /* b2d_tok_match */
             }
+            atomicAdd(&s_hist[sym], 1u);
+            tok[tbase + idx] = tv;
         }
     }
     __syncthreads();
