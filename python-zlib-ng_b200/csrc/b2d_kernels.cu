@@ -268,8 +268,10 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
 /* ------------------------------------------------------------------------- */
 #define K3_THREADS 256
 #define K3_WORDS (B2D_SUB / 32u)      /* bitmap words per sub-block = 1024 */
+#define K3_SEGS 4u                    /* lanes chasing one parse unit speculatively */
+#define K3_SEG (B2D_UNIT / K3_SEGS)
 
-__global__ void __launch_bounds__(K3_THREADS)
+__global__ void __launch_bounds__(K3_THREADS, 5)
 k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict__ match,
         uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy,
         uint32_t min_take) {
@@ -277,6 +279,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     __shared__ uint32_t s_reach[K3_WORDS], s_base[K3_WORDS];
     __shared__ uint32_t s_hist[B2D_HIST];
     __shared__ uint32_t s_wsum[K3_THREADS / 32];
+    __shared__ uint32_t s_exit[K3_SEGS * 32];
     __shared__ uint8_t s_lsym[256], s_dsym[512];   /* length symbol of len-3; distance symbol of d-1 (d-1 < 256) or 256 + ((d-1) >> 7) */
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint64_t k = blockIdx.x;
@@ -352,22 +355,54 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
         for (uint32_t r = 0; r < B2D_SUB / 4 / K3_THREADS; ++r) W[r * K3_THREADS + tid] = outw[r];
     }
     __syncthreads();
-    /* chase: lane u of warp 0 walks unit u; one dependent shared load per token */
-    if (warp == 0) {
+    /* Chase.  A unit's parse is a chain i -> i + step(i); K3_SEGS lanes walk it at once, lane (u, g)
+     * starting at the g-th quarter of unit u as if that position were reached.  Two chains that ever meet
+     * stay together, so a quarter's speculative marks are right from the point where the true chain
+     * (entering from the previous quarter) first steps on one of them; the repair below fixes the rest. */
+    const uint64_t *L8 = reinterpret_cast<const uint64_t *>(s_len);
+    if (warp < K3_SEGS) {
         const uint32_t ustart = lane * B2D_UNIT;
         const uint32_t uend = ustart + B2D_UNIT < len ? ustart + B2D_UNIT : len;
-        uint32_t i = ustart;
-        const uint64_t *L8 = reinterpret_cast<const uint64_t *>(s_len);
-        while (i < uend) {
+        const uint32_t b = ustart + warp * K3_SEG;
+        const uint32_t e = b + K3_SEG < uend ? b + K3_SEG : uend;     /* marks stay below e */
+        uint32_t i = b;
+        while (i < e) {
             /* the 8-byte group holding i, shifted so that byte 0 is position i: if nothing is left in
              * it, every position up to the group's end is a literal (literal runs go 8 at a time) */
             const uint32_t o = i & 7u;
             const uint64_t g = L8[i >> 3] >> (8u * o);
             const uint32_t v = (uint32_t)g & 255u;
             uint32_t k = 1;                                   /* positions marked reached */
-            if (g == 0) { k = 8u - o; if (i + k > uend) k = uend - i; }
+            if (g == 0) { k = 8u - o; if (i + k > e) k = e - i; }
             atomicOr(&s_reach[i >> 5], ((1u << k) - 1u) << (i & 31u));
             i += v ? v + 3u : k;
+        }
+        s_exit[warp * 32u + lane] = i;                        /* first position at or past e the chain lands on */
+    }
+    __syncthreads();
+    if (warp == 0) {
+        /* repair, one lane per unit, quarter by quarter: `at` is where the true chain enters the quarter */
+        const uint32_t ustart = lane * B2D_UNIT;
+        const uint32_t uend = ustart + B2D_UNIT < len ? ustart + B2D_UNIT : len;
+        uint32_t at = s_exit[lane];
+        for (uint32_t q = 1; q < K3_SEGS; ++q) {
+            const uint32_t b = ustart + q * K3_SEG;
+            if (b >= uend) break;
+            const uint32_t e = b + K3_SEG < uend ? b + K3_SEG : uend;
+            if (at == b) { at = s_exit[q * 32u + lane]; continue; }          /* the guess was right */
+            /* where does the true chain meet the speculative one (or leave the quarter)? */
+            uint32_t j = at;
+            while (j < e && !((s_reach[j >> 5] >> (j & 31u)) & 1u)) { const uint32_t v = s_len[j]; j += v ? v + 3u : 1u; }
+            const uint32_t meet = j < e ? j : e;
+            /* speculative marks before the meeting point are wrong: clear [b, meet), then mark the true chain */
+            for (uint32_t w = b >> 5; w <= (meet - 1u) >> 5 && meet > b; ++w) {
+                const uint32_t lo = w == (b >> 5) ? (b & 31u) : 0u;
+                const uint32_t hi = w == ((meet - 1u) >> 5) ? ((meet - 1u) & 31u) : 31u;
+                s_reach[w] &= ~((0xffffffffu >> (31u - hi)) & (0xffffffffu << lo));
+            }
+            uint32_t t2 = at;
+            while (t2 < meet) { s_reach[t2 >> 5] |= 1u << (t2 & 31u); const uint32_t v = s_len[t2]; t2 += v ? v + 3u : 1u; }
+            at = j < e ? s_exit[q * 32u + lane] : j;
         }
     }
     __syncthreads();
