@@ -39,7 +39,10 @@ extern "C" uint64_t b2d_deflate_bound(uint64_t n) {
 }
 
 #define PROF_BATCHES 64
-#define B2D_NSLOT 3     /* input/output slots of the host pipeline: one more than compute lanes */
+#ifndef B2D_NLANE
+#define B2D_NLANE 2     /* batches of one call in flight on the device, each on its own stream with its own intermediates */
+#endif
+#define B2D_NSLOT (B2D_NLANE + 1)   /* input/output slots of the host pipeline: one more than compute lanes */
 /* per-batch intermediates of the kernel pipeline.  Two of them ("lanes") let consecutive batches of one
  * call run on two streams, so one batch's kernels fill the SMs the other's tail waves leave idle. */
 struct b2d_work {
@@ -73,9 +76,9 @@ struct b2d_ctx {
     /* work buffers for one batch */
     uint8_t *d_in;  uint64_t d_in_cap;      /* WINDOW + max_batch + pad (host-buffer calls)   */
     uint8_t *d_out; uint64_t d_out_cap;     /* bound(max_batch) rounded (host-buffer calls)   */
-    b2d_work wk[2];                         /* lane 1 is allocated on first use (ensure_second_lane) */
-    cudaStream_t st2;                       /* lane 1's stream (lane 0 runs on st)            */
-    cudaEvent_t ev_scan[2], ev_fork, ev_join;
+    b2d_work wk[B2D_NLANE];                 /* lanes 1.. are allocated on first use (ensure_second_lane) */
+    cudaStream_t stl[B2D_NLANE];            /* lane streams; stl[0] == st                      */
+    cudaEvent_t ev_scan[B2D_NLANE], ev_fork, ev_join[B2D_NLANE];
     uint64_t *d_total;                      /* running output byte offset of a call           */
     uint64_t *h_total;                      /* pinned                                         */
     uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
@@ -98,11 +101,10 @@ struct b2d_ctx {
 static void ctx_free(b2d_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_in); cudaFree(c->d_out); work_free(&c->wk[0]); work_free(&c->wk[1]);
-    for (int i = 0; i < 2; ++i) if (c->ev_scan[i]) cudaEventDestroy(c->ev_scan[i]);
+    cudaFree(c->d_in); cudaFree(c->d_out); for (int i = 0; i < B2D_NLANE; ++i) work_free(&c->wk[i]);
+    for (int i = 0; i < B2D_NLANE; ++i) { if (c->ev_scan[i]) cudaEventDestroy(c->ev_scan[i]); if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->ev_join) cudaEventDestroy(c->ev_join);
-    if (c->st2) cudaStreamDestroy(c->st2);
+    for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) cudaStreamDestroy(c->stl[i]);
     cudaFree(c->d_total);
     for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
     for (int i = 0; i < B2D_NSLOT; ++i) {
@@ -282,12 +284,14 @@ static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uin
 
 /* second set of intermediates + its stream: only multi-batch calls pay for them */
 static int ensure_second_lane(b2d_ctx *c) {
-    if (c->st2) return B2D_OK;
-    CU(work_alloc(&c->wk[1], c->max_batch));
-    for (int i = 0; i < 2; ++i) CU(cudaEventCreateWithFlags(&c->ev_scan[i], cudaEventDisableTiming));
+    if (c->ev_fork) return B2D_OK;
+    c->stl[0] = c->st;
+    for (int i = 1; i < B2D_NLANE; ++i) { CU(work_alloc(&c->wk[i], c->max_batch)); CU(cudaStreamCreateWithFlags(&c->stl[i], cudaStreamNonBlocking)); }
+    for (int i = 0; i < B2D_NLANE; ++i) {
+        CU(cudaEventCreateWithFlags(&c->ev_scan[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
+    }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
-    CU(cudaStreamCreateWithFlags(&c->st2, cudaStreamNonBlocking));
     return B2D_OK;
 }
 
@@ -301,7 +305,7 @@ static uint32_t pipeline_launches(int level) {
 static int prof_drain(b2d_ctx *c, int nb, int level) {
     const b2d_policy pol = b2d_level_policy(level);
     CU(cudaStreamSynchronize(c->st));
-    if (c->st2) CU(cudaStreamSynchronize(c->st2));
+    for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) CU(cudaStreamSynchronize(c->stl[i]));
     for (int i = 0; i < nb; ++i)
         for (int j = 0; j < B2D_NSTAGE; ++j) {
             float t = 0;
@@ -352,26 +356,26 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     if (two) {
         int rc = ensure_second_lane(c); if (rc) return rc;
         CU(cudaEventRecord(c->ev_fork, c->st));
-        CU(cudaStreamWaitEvent(c->st2, c->ev_fork, 0));
+        for (int i = 1; i < B2D_NLANE; ++i) CU(cudaStreamWaitEvent(c->stl[i], c->ev_fork, 0));
     }
     uint64_t jb = 0;
     for (uint64_t off = 0; off < n; off += c->max_batch, ++jb) {
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
-        const int lane = two ? (int)(jb & 1) : 0;
+        const int lane = two ? (int)(jb % B2D_NLANE) : 0;
         /* re-base so the work buffers are indexed from (at most) 32 KiB + 15 bytes before the batch */
         const uint64_t abs0 = dict_n + off;
         const uint64_t base = abs0 > B2D_WINDOW ? (abs0 - B2D_WINDOW) & ~(uint64_t)15 : 0;
         b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out, B2D_WINDOW, lane);
-        if (two) { J.scan_wait = jb ? c->ev_scan[lane ^ 1] : nullptr; J.scan_done = c->ev_scan[lane]; }
+        if (two) { J.scan_wait = jb ? c->ev_scan[(lane + B2D_NLANE - 1) % B2D_NLANE] : nullptr; J.scan_done = c->ev_scan[lane]; }
         cudaEvent_t *pe = nullptr;
         if (c->profiling) {
             if (nprof == PROF_BATCHES) { int rc = prof_drain(c, nprof, level); if (rc) return rc; nprof = 0; }
             pe = c->pev[nprof++];
         }
-        CU(b2d_launch_pipeline(&J, lane ? c->st2 : c->st, pe));
+        CU(b2d_launch_pipeline(&J, lane ? c->stl[lane] : c->st, pe));
         c->launches += pipeline_launches(level);
     }
-    if (two) { CU(cudaEventRecord(c->ev_join, c->st2)); CU(cudaStreamWaitEvent(c->st, c->ev_join, 0)); }
+    if (two) for (int i = 1; i < B2D_NLANE; ++i) { CU(cudaEventRecord(c->ev_join[i], c->stl[i])); CU(cudaStreamWaitEvent(c->st, c->ev_join[i], 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
     CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
@@ -433,8 +437,8 @@ static int ensure_staging(b2d_ctx *c, bool in, bool out) {
 }
 
 /* Pinned host input and output, more than one batch: three-stage software pipeline.
- *   st_in : H2D of batch j into slot j % 3 (waits until the kernels of batch j-3 released the slot)
- *   st/st2: kernels + CRC of batch j on lane j & 1 (waits for its H2D and for the D2H of batch j-3);
+ *   st_in : H2D of batch j into slot j % B2D_NSLOT (waits until the kernels of the slot's previous batch released it)
+ *   lanes : kernels + CRC of batch j on lane j % B2D_NLANE (waits for its H2D and for the D2H of the slot's previous batch);
  *           consecutive batches overlap, which fills the tail waves of each other's kernels
  *   st_out: D2H of batch j-1 (issued once the host knows its size)
  * The host only blocks on "kernels of batch j-2 done", by which time batches j-1 and j are already queued.
@@ -447,7 +451,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     if (rc) return rc;
     if ((rc = ensure_second_lane(c))) return rc;
     if ((rc = ensure_staging(c, !in_pinned, !out_pinned))) return rc;
-    cudaStream_t cs[2] = {c->st, c->st2};       /* batch j computes on lane j & 1 */
+    cudaStream_t *cs = c->stl;                  /* batch j computes on lane j % B2D_NLANE */
     uint8_t *d_in[B2D_NSLOT] = {c->d_in}, *d_out[B2D_NSLOT] = {c->d_out};
     uint64_t *d_total[B2D_NSLOT] = {c->d_total};
     b2d_cksum_ws *ck[B2D_NSLOT] = {c->ck};
@@ -486,7 +490,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     };
     for (uint64_t j = 0; j < nb; ++j) {
         const int s = (int)(j % B2D_NSLOT);
-        const int ln = (int)(j & 1);          /* compute lane */
+        const int ln = (int)(j % B2D_NLANE);  /* compute lane */
         const uint64_t off = j * c->max_batch;
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
         uint64_t D;
@@ -521,11 +525,11 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
         if (adler_acc) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
-        /* the host trails by two batches: j-1 and j stay queued on the two lanes while it waits for j-2 */
-        if (j >= 2 && (rc = finish(j - 2))) { cudaDeviceSynchronize(); return rc; }
+        /* the host trails by one batch per lane: the lanes stay busy while it waits for the oldest batch */
+        if (j >= B2D_NLANE && (rc = finish(j - B2D_NLANE))) { cudaDeviceSynchronize(); return rc; }
     }
-    if (nb >= 2 && (rc = finish(nb - 2))) { cudaDeviceSynchronize(); return rc; }
-    if ((rc = finish(nb - 1))) { cudaDeviceSynchronize(); return rc; }
+    for (uint64_t k = nb > B2D_NLANE ? nb - B2D_NLANE : 0; k < nb; ++k)
+        if ((rc = finish(k))) { cudaDeviceSynchronize(); return rc; }
     if ((rc = drain())) { cudaDeviceSynchronize(); return rc; }
     CU(cudaStreamSynchronize(c->st_out));
     *produced_out = produced;
