@@ -51,6 +51,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
+        self.ready = threading.Event()      # NVML is up and the first sample is in: the timed region may start
 
     def run(self):
         try:
@@ -69,14 +70,18 @@ class ClockSampler(threading.Thread):
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.1)
+                self.ready.set()
+                time.sleep(0.02)
         except Exception as e:  # pragma: no cover
             self.reasons.add(f"sampler_error:{type(e).__name__}")
+            self.ready.set()
 
     def stop(self):
         self._halt.set()
         self.join(timeout=2)
-        med = float(np.median(self.samples)) if self.samples else None
+        # the first sample predates the timed region (taken while waiting for `ready`)
+        under_load = self.samples[1:] if len(self.samples) > 1 else self.samples
+        med = float(np.median(under_load)) if under_load else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
@@ -294,6 +299,7 @@ def main():
     launches0 = ctx.launch_count()
     sampler = ClockSampler(local)
     sampler.start()
+    sampler.ready.wait(timeout=20)
     barrier(dist, local)
     ctx.sync()
     t_wall0 = time.perf_counter()

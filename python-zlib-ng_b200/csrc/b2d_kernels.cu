@@ -154,6 +154,86 @@ __device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off
     return __funnelshift_r(s32[wi], s32[wi + 1], (byte_off & 3u) << 3);
 }
 
+/* Best match of the position at shared byte index `pr` (at most `maxl` bytes, `depth` candidates).  Two codings of
+ * the same search, same result:
+ *   DENSE = false  quick reject on the byte at index `best` before a candidate is compared; cheapest where hardly any
+ *                  candidate is a match (incompressible data: the whole warp skips the compare code);
+ *   DENSE = true   the kernel is issue-bound, and on compressible data some lane of a warp needs the compare in nine
+ *                  steps of ten: every lane compares the candidate's first eight bytes straight-line, without the
+ *                  reject branch and without a break (a match that ends the walk sets the step counter instead). */
+template <bool DENSE>
+__device__ __forceinline__ uint32_t k2_search(const uint32_t *s_in, const uint16_t *s_prev, uint32_t pr, uint32_t poff,
+                                              uint32_t maxl, int depth, uint32_t nice, uint32_t max_dist, int rle) {
+    const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
+    uint32_t best = 3, bd = 0;
+    /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
+     * pushes the running distance past max_dist, so one compare ends the walk either way */
+    /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links exist */
+    uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : s_prev[pr - poff];
+    if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
+        /* the position's first 16 bytes stay in registers: most compares end inside them */
+        uint32_t own[4];
+        {
+            const uint32_t wi = pr >> 2, sh = (pr & 3u) << 3;
+            const uint32_t a0 = s_in[wi], a1 = s_in[wi + 1], a2 = s_in[wi + 2], a3 = s_in[wi + 3], a4 = s_in[wi + 4];
+            own[0] = __funnelshift_r(a0, a1, sh); own[1] = __funnelshift_r(a1, a2, sh);
+            own[2] = __funnelshift_r(a2, a3, sh); own[3] = __funnelshift_r(a3, a4, sh);
+        }
+        uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
+        int step = depth;
+        const uint32_t osh = (pr & 3u) << 3;
+        /* byte addresses inside the shared window, so that a step's loads are one subtract each */
+        const uint8_t *lpb = reinterpret_cast<const uint8_t *>(s_prev + (pr - poff));
+        const uint8_t *cbp = s_in8 + pr + best;         /* own_b's address; the candidate's is cbp - dist */
+        do {
+            const uint32_t nd = *reinterpret_cast<const uint16_t *>(lpb - 2u * dist);   /* next link: independent of the test below */
+            if (DENSE || *(cbp - dist) == own_b) {
+                const uint32_t cand = pr - dist;
+                uint32_t cw = cand >> 2;
+                const uint32_t csh = (cand & 3u) << 3;
+                const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
+                const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own[0];
+                const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own[1];
+                uint32_t x = x0 ? x0 : x1, l = x0 ? 0u : 4u;      /* most compares end in the first 8 bytes */
+                if ((x0 | x1) == 0u) {
+                    const uint32_t a3 = s_in[cw + 3], a4 = s_in[cw + 4];
+                    if ((x = __funnelshift_r(a2, a3, csh) ^ own[2]) != 0) l = 8;
+                    else if ((x = __funnelshift_r(a3, a4, csh) ^ own[3]) != 0) l = 12;
+                    else {
+                        /* long match: 8 bytes per trip, each aligned word of either side loaded once */
+                        l = 16;
+                        cw += 4;
+                        uint32_t ow = (pr >> 2) + 4u, cp = a4, op = s_in[ow];
+                        while (l < maxl) {
+                            const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], o1 = s_in[ow + 1], o2 = s_in[ow + 2];
+                            if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, o1, osh)) != 0) break;
+                            l += 4;
+                            if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(o1, o2, osh)) != 0) break;
+                            l += 4; cw += 2; ow += 2; cp = c2; op = o2;
+                        }
+                    }
+                }
+                if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
+                if (l > maxl) l = maxl;
+                if (l > best) {
+                    best = l; bd = dist;
+                    if (DENSE) {
+                        if (l >= nice || l == maxl) step = 1;
+                    } else {
+                        if (l >= nice || l == maxl) break;
+                        cbp = s_in8 + pr + best;
+                        own_b = *cbp;
+                    }
+                }
+            }
+            dist += nd;
+        } while (--step > 0 && dist <= max_dist);
+    }
+    return best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+}
+
+#define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
+
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
         const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
@@ -188,78 +268,30 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         if (!rle) for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
     }
     __syncthreads();
-    const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
     const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
     const uint32_t tile_off = (uint32_t)(tile_start - ws_al);
     uint32_t *mout = match + (tile_start - D);
-    for (uint32_t t = tid; t < tile_len; t += K2_THREADS) {
-        /* no match crosses a parse unit (tile starts are unit-aligned relative to the data) */
+    /* no match crosses a parse unit (tile starts are unit-aligned relative to the data) */
+    auto max_len = [&](uint32_t t) -> uint32_t {
         const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
-        uint32_t maxl = to_unit < to_end ? to_unit : to_end;
-        if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
-        uint32_t best = 3, bd = 0;
-        const uint32_t pr = tile_off + t;                   /* smem byte index of this position */
-        /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
-         * pushes the running distance past max_dist, so one compare ends the walk either way */
-        /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links exist */
-        uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : s_prev[pr - poff];
-        if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
-            /* the position's first 16 bytes stay in registers: most compares end inside them */
-            uint32_t own[4];
-            {
-                const uint32_t wi = pr >> 2, sh = (pr & 3u) << 3;
-                const uint32_t a0 = s_in[wi], a1 = s_in[wi + 1], a2 = s_in[wi + 2], a3 = s_in[wi + 3], a4 = s_in[wi + 4];
-                own[0] = __funnelshift_r(a0, a1, sh); own[1] = __funnelshift_r(a1, a2, sh);
-                own[2] = __funnelshift_r(a2, a3, sh); own[3] = __funnelshift_r(a3, a4, sh);
-            }
-            uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
-            int step = depth;
-            const uint32_t osh = (pr & 3u) << 3;
-            /* byte addresses inside the shared window, so that a step's two loads are one subtract each */
-            const uint8_t *lpb = reinterpret_cast<const uint8_t *>(s_prev + (pr - poff));
-            const uint8_t *cbp = s_in8 + pr + best;         /* own_b's address; the candidate's is cbp - dist */
-            do {
-                const uint32_t nd = *reinterpret_cast<const uint16_t *>(lpb - 2u * dist);   /* next link: independent of the test below */
-                if (*(cbp - dist) == own_b) {
-                    const uint32_t cand = pr - dist;
-                    uint32_t cw = cand >> 2;
-                    const uint32_t csh = (cand & 3u) << 3;
-                    const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
-                    const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own[0];
-                    const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own[1];
-                    uint32_t l, x;
-                    if (x0 | x1) { x = x0 ? x0 : x1; l = x0 ? 0u : 4u; }      /* most compares end in the first 8 bytes */
-                    else {
-                        const uint32_t a3 = s_in[cw + 3], a4 = s_in[cw + 4];
-                        if ((x = __funnelshift_r(a2, a3, csh) ^ own[2]) != 0) l = 8;
-                        else if ((x = __funnelshift_r(a3, a4, csh) ^ own[3]) != 0) l = 12;
-                        else {
-                            /* long match: 8 bytes per trip, each aligned word of either side loaded once */
-                            l = 16;
-                            cw += 4;
-                            uint32_t ow = (pr >> 2) + 4u, cp = a4, op = s_in[ow];
-                            while (l < maxl) {
-                                const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], o1 = s_in[ow + 1], o2 = s_in[ow + 2];
-                                if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, o1, osh)) != 0) break;
-                                l += 4;
-                                if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(o1, o2, osh)) != 0) break;
-                                l += 4; cw += 2; ow += 2; cp = c2; op = o2;
-                            }
-                        }
-                    }
-                    if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
-                    if (l > maxl) l = maxl;
-                    if (l > best) {
-                        best = l; bd = dist;
-                        if (l >= nice || l == maxl) break;
-                        cbp = s_in8 + pr + best;
-                        own_b = *cbp;
-                    }
-                }
-                dist += nd;
-            } while (--step > 0 && dist <= max_dist);
-        }
-        mout[t] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+        const uint32_t m = to_unit < to_end ? to_unit : to_end;
+        return m > B2D_MAX_MATCH ? B2D_MAX_MATCH : m;
+    };
+    /* the tile's first 1024 positions are searched with the quick-reject coding and tell which coding suits the rest */
+    uint32_t t = tid, hit = 0;
+    if (t < tile_len) {
+        const uint32_t m = k2_search<false>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+        mout[t] = m;
+        hit = m != 0u;
+    }
+    const bool dense = __syncthreads_count((int)hit) >= (int)K2_DENSE_HITS;
+    t += K2_THREADS;
+    if (dense) {
+        for (; t < tile_len; t += K2_THREADS)
+            mout[t] = k2_search<true>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+    } else {
+        for (; t < tile_len; t += K2_THREADS)
+            mout[t] = k2_search<false>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
     }
 }
 

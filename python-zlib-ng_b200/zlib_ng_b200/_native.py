@@ -13,7 +13,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2d.so")
+LIB_PATH = os.environ.get("B2D_LIB") or os.path.join(_HERE, "libb2d.so")   # B2D_LIB: another build of the same ABI (A/B runs)
 
 B2D_OK = 0
 B2D_STREAM_ERROR = -2
