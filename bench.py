@@ -35,6 +35,10 @@ GIB = 1 << 30
 MIB = 1 << 20
 METRIC = "gzip_compress_input_GBps_L6"
 STAGES = ["k_chains", "k_match", "k_parse", "k_plan", "k_scan", "k_emit"]
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per INPUT byte of a launch, from the one
+# `ncu --set full` capture of a 256 MiB level-6 batch of this workload (profiles/ncu_r1_e_summary.txt §2)
+NCU_DRAM_BYTES_PER_INPUT_BYTE = {"k_chains": 3.57, "k_match": 7.33, "k_parse": 9.32, "k_plan": 0.063,
+                                 "k_scan": 0.004, "k_emit": 2.01}
 
 
 def make_workload(kind, n, seed, base_mib):
@@ -338,7 +342,10 @@ def main():
     alg_bytes_per_launch = (1.0 + ratio) * n * a.steps / max(int(stage_n[top]), 1)
     achieved = alg_bytes_per_launch / (stage_ms[top] / max(int(stage_n[top]), 1) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None,
+                "frac": achieved / peak,
+                "traffic": NCU_DRAM_BYTES_PER_INPUT_BYTE[STAGES[top]] * n * a.steps / max(int(stage_n[top]), 1),
+                "traffic_source": "ncu --set full capture of one launch (profiles/ncu_r1_e_summary.txt), DRAM bytes per "
+                                  "input byte x input bytes per launch",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                 "kernel_ms_per_step": {k: v / a.steps for k, v in shares.items()},
