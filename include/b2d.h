@@ -92,6 +92,10 @@ int b2d_host_free(b2d_ctx *ctx, void *ptr);
 int b2d_copy_h2d(b2d_ctx *ctx, void *d_dst, const void *h_src, uint64_t bytes);
 int b2d_copy_d2h(b2d_ctx *ctx, void *h_dst, const void *d_src, uint64_t bytes);
 int b2d_device_sync(b2d_ctx *ctx);
+/* memcpy between host buffers split over `threads` native threads: how the writer behind
+ * gzip_ng_threaded.open fills its pinned batch from the caller's bytes (the reference copies every block once
+ * as well: `data = bytes(b)`, gzip_ng_threaded.py:315).  One thread moves ~14 GB/s on the test box, eight ~70. */
+int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads);
 /* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
  * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit.
  * enable = 1 times the kernels as they run in production (consecutive batches of a

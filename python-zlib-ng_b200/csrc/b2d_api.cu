@@ -414,18 +414,27 @@ static int ensure_second_slot(b2d_ctx *c) {
 }
 
 /* host copy in a few threads: one thread moves ~10 GB/s, the pipeline wants more */
-static void par_memcpy(void *dst, const void *src, uint64_t n) {
-    const uint64_t piece = 8ull << 20;
-    if (n < 2 * piece) { memcpy(dst, src, n); return; }
-    const unsigned nt = 4;
-    std::thread th[nt];
-    const uint64_t per = (n / nt + 63) & ~63ull;
-    for (unsigned i = 0; i < nt; ++i) {
+static void par_memcpy_n(void *dst, const void *src, uint64_t n, unsigned nt) {
+    const uint64_t piece = 4ull << 20;
+    if (nt > 32) nt = 32;
+    if (nt < 2 || n < 2 * piece) { memcpy(dst, src, n); return; }
+    if ((uint64_t)nt * piece > n) nt = (unsigned)(n / piece);
+    std::thread th[32];
+    const uint64_t per = (n / nt + 4095) & ~4095ull;
+    for (unsigned i = 1; i < nt; ++i) {
         const uint64_t o = (uint64_t)i * per;
         const uint64_t k = o >= n ? 0 : (n - o < per ? n - o : per);
         th[i] = std::thread([=] { if (k) memcpy((uint8_t *)dst + o, (const uint8_t *)src + o, k); });
     }
-    for (unsigned i = 0; i < nt; ++i) th[i].join();
+    memcpy(dst, src, per < n ? per : n);          /* the calling thread takes the first piece */
+    for (unsigned i = 1; i < nt; ++i) th[i].join();
+}
+static void par_memcpy(void *dst, const void *src, uint64_t n) { par_memcpy_n(dst, src, n, 4); }
+
+extern "C" int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads) {
+    if ((!dst || !src) && bytes) return B2D_STREAM_ERROR;
+    par_memcpy_n(dst, src, bytes, threads < 1 ? 1u : (unsigned)threads);
+    return B2D_OK;
 }
 
 static int ensure_staging(b2d_ctx *c, bool in, bool out) {

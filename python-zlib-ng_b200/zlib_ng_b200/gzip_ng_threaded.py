@@ -40,27 +40,16 @@ _STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
 # overlap batch j's kernels.  threads=N asks for min(N, this) of them.
 _STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "4")), 1)
 _COPY_CHUNK = 4 << 20
-_copy_pool = None
-_copy_pool_lock = threading.Lock()
+_COPY_THREADS = max(int(os.environ.get("B2D_COPY_THREADS", "8")), 1)
 
 
 def _parallel_copy(dst_addr: int, src, nbytes: int) -> None:
-    """memcpy into pinned memory; large copies are split over a few threads (ctypes.memmove drops the GIL)."""
+    """memcpy into pinned memory, split over native threads by the library (the GIL is dropped for the call)."""
     saddr, _, keep = _native._addr(src)
     if nbytes < 2 * _COPY_CHUNK:
         ctypes.memmove(dst_addr, saddr, nbytes)
-        return
-    global _copy_pool
-    if _copy_pool is None:
-        with _copy_pool_lock:
-            if _copy_pool is None:
-                from concurrent.futures import ThreadPoolExecutor
-                _copy_pool = ThreadPoolExecutor(max_workers=int(os.environ.get("B2D_COPY_THREADS", "8")),
-                                                thread_name_prefix="b2d-copy")
-    futs = [_copy_pool.submit(ctypes.memmove, dst_addr + o, saddr + o, min(_COPY_CHUNK, nbytes - o))
-            for o in range(0, nbytes, _COPY_CHUNK)]
-    for f in futs:
-        f.result()
+    else:
+        _native.check(_native.lib().b2d_host_copy(dst_addr, saddr, nbytes, _COPY_THREADS))
     del keep
 
 
@@ -261,6 +250,12 @@ class _ThreadedGzipWriter(io.RawIOBase):
     def stop(self):
         """Stop, but do not care for remaining work"""
         self.running = False
+        # the workers poll their queues like the reference's (50 ms time-outs); a sentinel ends them at once
+        for q in list(self.input_queues) + list(self.output_queues):
+            try:
+                q.put_nowait(None)
+            except queue.Full:
+                pass
         for w in self.compression_workers:
             w.join()
         self.output_worker.join()
@@ -422,6 +417,9 @@ class _ThreadedGzipWriter(io.RawIOBase):
                     if not self._alive():
                         return
                     continue
+                if job is None:
+                    in_queue.task_done()
+                    return
                 try:
                     compressed, crc, n = self._run_job(0, job, out_buf)
                     self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
@@ -453,6 +451,9 @@ class _ThreadedGzipWriter(io.RawIOBase):
                     if not self._alive():
                         return
                     continue
+                if job is None:
+                    in_queue.task_done()
+                    return
                 out_buf = None
                 while out_buf is None:
                     try:
@@ -485,11 +486,15 @@ class _ThreadedGzipWriter(io.RawIOBase):
         while True:
             q = self.output_queues[index % nq]
             try:
-                compressed, crc, n, spare, out_buf = q.get(timeout=0.05)
+                item = q.get(timeout=0.05)
             except queue.Empty:
                 if not self._alive():
                     return
                 continue
+            if item is None:
+                q.task_done()
+                return
+            compressed, crc, n, spare, out_buf = item
             try:
                 self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
                 self._size += n
@@ -512,7 +517,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
             while True:
                 try:
                     job = qq.get(timeout=0.05)
-                    if qq in self.input_queues:
+                    if qq in self.input_queues and job is not None:
                         self._release(job)
                     qq.task_done()
                 except queue.Empty:
