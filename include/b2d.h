@@ -96,6 +96,26 @@ int b2d_device_sync(b2d_ctx *ctx);
  * gzip_ng_threaded.open fills its pinned batch from the caller's bytes (the reference copies every block once
  * as well: `data = bytes(b)`, gzip_ng_threaded.py:315).  One thread moves ~14 GB/s on the test box, eight ~70. */
 int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads);
+/* ---- the other side of the wire: block-parallel inflate of streams written by this library ----
+ * (first version.  The reference decompresses with zng_inflate on one thread:
+ * zlib_ng.decompress, zlib_ngmodule.c:275-370; _GzipReader.read, :2426-2637; gzip_ng_threaded.py:90-167.)
+ *
+ * b2d_block_index: where every 128 KiB device block of the LAST b2d_deflate_device call on this context starts
+ * in its compressed output: *count = blocks + 1 entries (the last one is the stream length), copied to
+ * `offsets` when it is not NULL (B2D_BUF_ERROR if cap < *count).  Blocks start byte-aligned. */
+int b2d_block_index(b2d_ctx *ctx, uint64_t *offsets, uint64_t cap, uint64_t *count);
+/* Inflate `raw_n` bytes from the raw-DEFLATE stream d_in[0, in_n) given block_offsets[0, nblocks) (a host
+ * array; nblocks = ceil(raw_n / 128 KiB)) and the dictionary the stream was primed with (device pointer, at
+ * most 32 KiB, may be NULL/0).  Every block is decoded by its own warp; references into the preceding 32 KiB
+ * are carried as markers and resolved afterwards (b2d_inflate.cu).  Needs 2 * raw_n bytes of device scratch
+ * (owned by the context).  Returns -3 (Z_DATA_ERROR) if a block does not decode to its expected length. */
+int b2d_inflate_device(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
+                       uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
+                       float *ms);
+/* the same with host buffers (H2D, kernels, D2H; not overlapped in this version) */
+int b2d_inflate_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
+                     const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n);
+
 /* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
  * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit.
  * enable = 1 times the kernels as they run in production (consecutive batches of a

@@ -17,6 +17,7 @@
 
 #include "../../include/b2d.h"
 #include "b2d_kernels.h"
+#include "b2d_inflate.h"
 
 static thread_local char g_err[512];
 static int fail_cuda(cudaError_t e, const char *where) {
@@ -91,6 +92,12 @@ struct b2d_ctx {
     uint8_t *h_in_s[B2D_NSLOT], *h_out_s[B2D_NSLOT];   /* pinned staging per slot, for pageable callers (lazy) */
     cudaEvent_t ev_in[B2D_NSLOT], ev_comp[B2D_NSLOT], ev_out[B2D_NSLOT];
     uint64_t launches;
+    /* compressed start offset of every device block of the last b2d_deflate_device call (b2d_block_index) */
+    uint64_t *d_index; uint64_t index_cap, index_n;
+    /* inflate scratch: 16-bit symbols, block index, error word */
+    uint16_t *d_inf16; uint64_t inf16_cap;
+    uint64_t *d_inf_index; uint64_t inf_index_cap;
+    uint32_t *d_inf_err;
     /* optional per-stage timing of device-resident calls */
     int profiling;
     cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
@@ -106,6 +113,7 @@ static void ctx_free(b2d_ctx *c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) cudaStreamDestroy(c->stl[i]);
     cudaFree(c->d_total);
+    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err);
     for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
     for (int i = 0; i < B2D_NSLOT; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
@@ -350,6 +358,15 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
     const uint64_t readable = dict_n + n + B2D_DEVICE_PAD;
     int nprof = 0;
+    {   /* room for the block index of this call */
+        const uint64_t need = (n + B2D_BLOCK - 1) / B2D_BLOCK + 1;
+        if (need > c->index_cap) {
+            cudaFree(c->d_index); c->d_index = nullptr; c->index_cap = 0;
+            CU(cudaMalloc(&c->d_index, need * sizeof(uint64_t)));
+            c->index_cap = need;
+        }
+        c->index_n = 0;
+    }
     /* several batches alternate between two lanes (streams + intermediates); b2d_profile(ctx, 2) keeps
      * one lane so that the stage times are those of kernels running alone */
     const bool two = n > c->max_batch && c->profiling != 2;
@@ -374,6 +391,11 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
         }
         CU(b2d_launch_pipeline(&J, lane ? c->stl[lane] : c->st, pe));
         c->launches += pipeline_launches(level);
+        /* k_scan left the absolute output offset of each block of this batch (and the running total) in the lane's
+         * block_off: keep them, the inflate side needs them */
+        const uint64_t nb = (m + B2D_BLOCK - 1) / B2D_BLOCK;
+        CU(cudaMemcpyAsync(c->d_index + off / B2D_BLOCK, J.block_off, (nb + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
+                           lane ? c->stl[lane] : c->st));
     }
     if (two) for (int i = 1; i < B2D_NLANE; ++i) { CU(cudaEventRecord(c->ev_join[i], c->stl[i])); CU(cudaStreamWaitEvent(c->st, c->ev_join[i], 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
@@ -384,6 +406,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     if (nprof) { int rc = prof_drain(c, nprof, level); if (rc) return rc; }
     if (crc) *crc = n ? b2d_crc32_dev_finish(c->ck, n, 0) : 0;
     *out_n = *c->h_total;
+    c->index_n = n ? (n + B2D_BLOCK - 1) / B2D_BLOCK + 1 : 0;
     if (n == 0) {   /* the empty job is just the sync marker: 00 00 00 ff ff */
         static const uint8_t marker[5] = {0, 0, 0, 0xff, 0xff};
         CU(cudaMemcpyAsync(d_out, marker, 5, cudaMemcpyHostToDevice, c->st));
@@ -685,4 +708,94 @@ extern "C" int b2d_compress_and_crc(b2d_ctx *c, int level, const uint8_t *data, 
     if (!crc) return fail(B2D_STREAM_ERROR, "null argument");
     *crc = 0;
     return b2d_deflate_host(c, level, 15, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr);
+}
+
+
+/* ------------------------------------------------------------------------- */
+/* inflate side (first version): streams of this library + their block index */
+/* ------------------------------------------------------------------------- */
+extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint64_t *count) {
+    if (!c || !count) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::mutex> g(c->mu);
+    *count = c->index_n;
+    if (!offsets || c->index_n == 0) return B2D_OK;
+    if (cap < c->index_n) return fail(B2D_BUF_ERROR, "b2d_block_index: capacity below the number of entries");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(offsets, c->d_index, c->index_n * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return B2D_OK;
+}
+
+extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
+                                  uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
+                                  float *ms) {
+    if (!c || (!d_in && in_n) || (!d_out && raw_n) || (!block_offsets && nblocks) || (!d_dict && dict_n))
+        return fail(B2D_STREAM_ERROR, "null argument");
+    if (nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
+    if (nblocks > 0x0fffffffull) return fail(B2D_STREAM_ERROR, "too many blocks");
+    if (dict_n > B2D_WINDOW) return fail(B2D_STREAM_ERROR, "device dictionary longer than 32768 bytes");
+    if ((uintptr_t)d_out & 15) return fail(B2D_STREAM_ERROR, "misaligned device pointer");
+    for (uint64_t b = 0; b < nblocks; ++b)
+        if (block_offsets[b] >= in_n || (b && block_offsets[b] <= block_offsets[b - 1]))
+            return fail(B2D_STREAM_ERROR, "bad block index");
+    if (ms) *ms = 0.f;
+    if (raw_n == 0) return B2D_OK;
+    std::lock_guard<std::mutex> g(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (raw_n > c->inf16_cap) {
+        cudaFree(c->d_inf16); c->d_inf16 = nullptr; c->inf16_cap = 0;
+        cudaError_t e = cudaMalloc(&c->d_inf16, raw_n * sizeof(uint16_t));
+        if (e != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate scratch (2 bytes per output byte) does not fit"); }
+        c->inf16_cap = raw_n;
+    }
+    if (nblocks > c->inf_index_cap) {
+        cudaFree(c->d_inf_index); c->d_inf_index = nullptr; c->inf_index_cap = 0;
+        CU(cudaMalloc(&c->d_inf_index, nblocks * sizeof(uint64_t)));
+        c->inf_index_cap = nblocks;
+    }
+    if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, sizeof(uint32_t)));
+    CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
+    CU(cudaMemsetAsync(c->d_inf_err, 0, sizeof(uint32_t), c->st));
+    if (ms) CU(cudaEventRecord(c->ev0, c->st));
+    CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+                          c->d_inf_err, c->st));
+    c->launches += B2D_INF_LAUNCHES;
+    if (ms) CU(cudaEventRecord(c->ev1, c->st));
+    uint32_t err = 0;
+    CU(cudaMemcpyAsync(&err, c->d_inf_err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    if (err) {
+        static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code"};
+        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err >> 28) & 3], err & 0x0fffffffu);
+        return -3;   /* Z_DATA_ERROR */
+    }
+    return B2D_OK;
+}
+
+extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
+                                const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n) {
+    if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
+    if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
+    uint8_t *d_in = nullptr, *d_out = nullptr, *d_dict = nullptr;
+    {
+        std::lock_guard<std::mutex> g(c->mu);
+        CU(cudaSetDevice(c->device));
+        cudaError_t e = cudaMalloc(&d_in, in_n + 16);
+        if (e == cudaSuccess) e = cudaMalloc(&d_out, raw_n + 16);
+        if (e == cudaSuccess && dict_n) e = cudaMalloc(&d_dict, dict_n);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, in, in_n, cudaMemcpyHostToDevice, c->st);
+        if (e == cudaSuccess && dict_n) e = cudaMemcpyAsync(d_dict, dict, dict_n, cudaMemcpyHostToDevice, c->st);
+        if (e != cudaSuccess) { cudaFree(d_in); cudaFree(d_out); cudaFree(d_dict); cudaGetLastError(); return fail_cuda(e, "b2d_inflate_host: device buffers"); }
+    }
+    int rc = b2d_inflate_device(c, d_in, in_n, block_offsets, nblocks, d_dict, dict_n, d_out, raw_n, nullptr);
+    {
+        std::lock_guard<std::mutex> g(c->mu);
+        cudaError_t e = cudaSuccess;
+        if (rc == B2D_OK) { e = cudaMemcpyAsync(out, d_out, raw_n, cudaMemcpyDeviceToHost, c->st); if (e == cudaSuccess) e = cudaStreamSynchronize(c->st); }
+        cudaFree(d_in); cudaFree(d_out); cudaFree(d_dict);
+        if (e != cudaSuccess) return fail_cuda(e, "b2d_inflate_host: copy back");
+    }
+    return rc;
 }

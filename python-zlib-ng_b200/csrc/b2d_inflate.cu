@@ -1,0 +1,320 @@
+/* b2d_inflate.cu — block-parallel inflate of raw-DEFLATE streams written by this library
+ * (the step on the other side of the wire; first version).
+ *
+ * The writer cuts its input into 128 KiB device blocks, each byte-aligned in the output and primed with the
+ * previous 32 KiB of *input* (b2d_kernels.cu), and can report where every block starts in the compressed
+ * stream (b2d_block_index).  With that index every block can be entropy-decoded on its own; what a block
+ * cannot know is the content of its dictionary, i.e. the last 32 KiB its predecessor produces.  So decoding
+ * runs in three stages (the two-stage scheme of parallel gzip readers, restated for one warp per block):
+ *
+ *   k_inf_decode   one warp per device block.  Lane 0 parses the DEFLATE block headers (stored / fixed /
+ *                  dynamic: inflate.c's TYPE..CODELENS states, inftrees.c) and decodes symbols with a
+ *                  10-bit / 9-bit first-level table in shared memory and the canonical count/offset walk
+ *                  for longer codes; the warp executes every copy together.  Output is 16 bits per byte:
+ *                  0..255 = the byte, 256 + k = "byte k of the 32 KiB before this block" — copies move these
+ *                  markers around like bytes, so a block never waits for its predecessor.
+ *   k_inf_tails    one CTA walks the blocks in order and resolves the last 32 KiB of each (one gather per
+ *                  marker from the predecessor's resolved tail): the only serial part, ~1 us per block.
+ *   k_inf_finish   one CTA per block resolves the rest of the block against the now final tails.
+ *
+ * Reference code this stands in for: zng_inflate (zlib-ng/inflate.c:474-1150), inflate_table
+ * (inftrees.c:30-290), inflate_fast (inffast_tpl.h), as driven by zlib_ng.decompress / _GzipReader
+ * (zlib_ngmodule.c:275-370, 2426-2637).  Streams from other writers carry no block index and are not
+ * accepted.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b2d_common.h"
+#include "b2d_inflate.h"
+
+#define FULL 0xffffffffu
+#define INF_WARPS 4
+#define INF_LL_BITS 10
+#define INF_D_BITS 9
+#define INF_TOK_EOB 0x7fffffffu
+#define INF_TOK_ERR 0x7ffffffeu
+
+struct inf_warp {
+    uint16_t ll_tab[1 << INF_LL_BITS];   /* (symbol << 4) | code length, 0 = code longer than the table */
+    uint16_t d_tab[1 << INF_D_BITS];
+    uint16_t ll_sorted[288];             /* symbols ordered by (length, symbol): canonical order */
+    uint16_t d_sorted[32];
+    uint16_t ll_count[16];               /* codes per length */
+    uint16_t d_count[16];
+    uint8_t lens[288 + 32];
+};
+
+__constant__ uint16_t c_lbase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115,
+                                     131, 163, 195, 227, 258};
+__constant__ uint8_t c_lext[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+__constant__ uint16_t c_dbase[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537,
+                                     2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+__constant__ uint8_t c_dext[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+__constant__ uint8_t c_clorder[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+
+/* LSB-first bit reader over global memory (lane 0 only).  After refill() at least 33 bits are buffered: enough
+ * for a length code with its extra bits (20) or a distance code with its extra bits (28). */
+struct bitrd {
+    const uint8_t *in;
+    uint64_t pos, lim;       /* next unread byte, end of the stream (bytes beyond read as zero) */
+    uint64_t buf;
+    uint32_t cnt;
+};
+__device__ __forceinline__ void br_init(bitrd &r, const uint8_t *in, uint64_t pos, uint64_t lim) {
+    r.in = in; r.pos = pos; r.lim = lim; r.buf = 0; r.cnt = 0;
+    while ((reinterpret_cast<uintptr_t>(in + r.pos) & 3u) && r.cnt < 24u) {
+        const uint32_t b = r.pos < lim ? in[r.pos] : 0u;
+        r.buf |= (uint64_t)b << r.cnt; r.cnt += 8; r.pos++;
+    }
+}
+__device__ __forceinline__ void br_refill(bitrd &r) {
+    if (r.cnt <= 32u) {
+        uint32_t w;
+        if (r.pos + 4 <= r.lim) w = *reinterpret_cast<const uint32_t *>(r.in + r.pos);
+        else {
+            w = 0;
+            for (uint32_t i = 0; i < 4; ++i) if (r.pos + i < r.lim) w |= (uint32_t)r.in[r.pos + i] << (8 * i);
+        }
+        r.buf |= (uint64_t)w << r.cnt; r.cnt += 32; r.pos += 4;
+    }
+}
+__device__ __forceinline__ uint32_t br_take(bitrd &r, uint32_t n) {   /* n <= 16, bits already buffered */
+    const uint32_t v = (uint32_t)r.buf & ((1u << n) - 1u);
+    r.buf >>= n; r.cnt -= n;
+    return v;
+}
+
+/* canonical decode of the code at the low end of `bits` (at most maxlen bits): count / sorted as built by
+ * inf_sort; returns the symbol and its length, or -1 (puff-style walk; inftrees.c builds tables from the same
+ * counts and offsets) */
+__device__ __forceinline__ int inf_canon(uint32_t bits, const uint16_t *count, const uint16_t *sorted, int maxlen, uint32_t *len_out) {
+    int code = 0, first = 0, index = 0;
+    for (int len = 1; len <= maxlen; ++len) {
+        code |= (int)(bits & 1u); bits >>= 1;
+        const int c = count[len];
+        if (code - c < first) { *len_out = (uint32_t)len; return sorted[index + (code - first)]; }
+        index += c; first += c; first <<= 1; code <<= 1;
+    }
+    return -1;
+}
+/* count[] and sorted[] of n code lengths (lane 0) */
+__device__ __forceinline__ void inf_sort(const uint8_t *lens, int n, uint16_t *count, uint16_t *sorted) {
+    uint16_t offs[16];
+    for (int l = 0; l < 16; ++l) count[l] = 0;
+    for (int s = 0; s < n; ++s) count[lens[s]]++;
+    count[0] = 0;
+    offs[1] = 0;
+    for (int l = 1; l < 15; ++l) offs[l + 1] = (uint16_t)(offs[l] + count[l]);
+    for (int s = 0; s < n; ++s) if (lens[s]) sorted[offs[lens[s]]++] = (uint16_t)s;
+}
+/* first-level table by the whole warp: entry i = the symbol whose code is a prefix of i */
+__device__ __forceinline__ void inf_fill(uint16_t *tab, int tbits, const uint16_t *count, const uint16_t *sorted, uint32_t lane) {
+    for (uint32_t i = lane; i < (1u << tbits); i += 32) {
+        uint32_t len = 0;
+        const int s = inf_canon(i, count, sorted, tbits, &len);
+        tab[i] = s >= 0 ? (uint16_t)(((uint32_t)s << 4) | len) : (uint16_t)0;
+    }
+}
+
+__global__ void __launch_bounds__(INF_WARPS * 32)
+k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__restrict__ index, uint32_t nblocks,
+             uint64_t raw_n, uint32_t dict_n, uint16_t *out16, uint32_t *err) {
+    __shared__ inf_warp s_w[INF_WARPS];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t b = blockIdx.x * INF_WARPS + warp;
+    if (b >= nblocks) return;
+    inf_warp *T = &s_w[warp];
+    const uint64_t bs = (uint64_t)b * B2D_BLOCK;
+    const uint32_t expect = (uint32_t)(raw_n - bs < B2D_BLOCK ? raw_n - bs : B2D_BLOCK);
+    /* how far behind its own start this block may reach: 32 KiB, or the caller's dictionary for block 0 */
+    const uint32_t reach = b == 0 ? dict_n : B2D_WINDOW;
+    uint16_t *o16 = out16 + bs;
+    bitrd R;
+    br_init(R, in, index[b], in_n);
+    uint32_t produced = 0, fail = 0;
+
+    while (produced < expect && !fail) {
+        /* ---- block header (lane 0): type, and for dynamic blocks the code lengths into T->lens */
+        uint32_t type = 0, st_len = 0;
+        uint64_t st_off = 0;
+        if (lane == 0) {
+            br_refill(R);
+            br_take(R, 1);                                  /* BFINAL: our writer never sets it on data blocks */
+            type = br_take(R, 2);
+            if (type == 0) {
+                br_take(R, R.cnt & 7u);                     /* to the next byte boundary */
+                br_refill(R);
+                const uint32_t len = br_take(R, 16), nlen = br_take(R, 16);
+                if ((len ^ nlen) != 0xffffu) type = 4;
+                st_len = len;
+                st_off = R.pos - (R.cnt >> 3);
+            } else if (type == 2) {
+                br_refill(R);
+                const uint32_t hlit = br_take(R, 5) + 257u, hdist = br_take(R, 5) + 1u, hclen = br_take(R, 4) + 4u;
+                if (hlit > 286u || hdist > 30u) type = 4;
+                else {
+                    uint8_t *cl = T->lens + 288;            /* 19 code-length code lengths, parked in the distance area */
+                    for (uint32_t i = 0; i < 19; ++i) cl[i] = 0;
+                    for (uint32_t i = 0; i < hclen; ++i) { br_refill(R); cl[c_clorder[i]] = (uint8_t)br_take(R, 3); }
+                    inf_sort(cl, 19, T->d_count, T->d_sorted);
+                    uint32_t idx = 0;
+                    const uint32_t total = hlit + hdist;
+                    uint8_t *L = T->lens;                   /* lengths of both alphabets back to back (<= 316), split below;
+                                                             * the parked 19 bytes may be overwritten: inf_sort has read them */
+                    while (idx < total) {
+                        br_refill(R);
+                        uint32_t l = 0;
+                        const int s = inf_canon((uint32_t)R.buf & 0x7fu, T->d_count, T->d_sorted, 7, &l);
+                        if (s < 0) { type = 4; break; }
+                        br_take(R, l);
+                        if (s < 16) { L[idx++] = (uint8_t)s; continue; }
+                        uint32_t rep, val = 0;
+                        if (s == 16) { if (idx == 0) { type = 4; break; } val = L[idx - 1]; rep = 3u + br_take(R, 2); }
+                        else if (s == 17) rep = 3u + br_take(R, 3);
+                        else rep = 11u + br_take(R, 7);
+                        if (idx + rep > total) { type = 4; break; }
+                        for (uint32_t i = 0; i < rep; ++i) L[idx++] = (uint8_t)val;
+                    }
+                    if (type == 2) {
+                        /* move the distance lengths to their own area (backwards: the areas may overlap), pad both with zeros */
+                        for (int i = (int)hdist - 1; i >= 0; --i) L[288 + i] = L[hlit + (uint32_t)i];
+                        for (uint32_t i = hdist; i < 32; ++i) L[288 + i] = 0;
+                        for (uint32_t i = hlit; i < 288; ++i) L[i] = 0;
+                    }
+                }
+            } else if (type == 3) type = 4;
+        }
+        type = __shfl_sync(FULL, type, 0);
+        if (type == 4) { fail = 1; break; }
+        if (type == 0) {
+            st_len = __shfl_sync(FULL, st_len, 0);
+            st_off = __shfl_sync(FULL, st_off, 0);
+            if (produced + st_len > expect || st_off + st_len > in_n) { fail = 2; break; }
+            for (uint32_t i = lane; i < st_len; i += 32) o16[produced + i] = in[st_off + i];
+            produced += st_len;
+            if (lane == 0) br_init(R, in, st_off + st_len, in_n);
+            __syncwarp();
+            continue;
+        }
+        if (type == 1) {   /* fixed code: trees.c static_ltree / RFC 1951 3.2.6 */
+            for (uint32_t i = lane; i < 288; i += 32) T->lens[i] = i < 144 ? 8 : (i < 256 ? 9 : (i < 280 ? 7 : 8));
+            T->lens[288 + lane] = lane < 30 ? 5 : 0;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            inf_sort(T->lens, 288, T->ll_count, T->ll_sorted);
+            inf_sort(T->lens + 288, 32, T->d_count, T->d_sorted);
+        }
+        __syncwarp();
+        inf_fill(T->ll_tab, INF_LL_BITS, T->ll_count, T->ll_sorted, lane);
+        inf_fill(T->d_tab, INF_D_BITS, T->d_count, T->d_sorted, lane);
+        __syncwarp();
+
+        /* ---- symbols: lane 0 decodes, the warp copies */
+        for (;;) {
+            uint32_t tok = 0;
+            if (lane == 0) {
+                br_refill(R);
+                uint32_t e = T->ll_tab[(uint32_t)R.buf & ((1u << INF_LL_BITS) - 1u)], len = e & 15u;
+                int sym = (int)(e >> 4);
+                if (!e) sym = inf_canon((uint32_t)R.buf & 0x7fffu, T->ll_count, T->ll_sorted, 15, &len);
+                if (sym < 0) tok = INF_TOK_ERR;
+                else {
+                    br_take(R, len);
+                    if (sym < 256) tok = (uint32_t)sym;
+                    else if (sym == 256) tok = INF_TOK_EOB;
+                    else if (sym > 285) tok = INF_TOK_ERR;
+                    else {
+                        const uint32_t ls = (uint32_t)sym - 257u;
+                        const uint32_t mlen = c_lbase[ls] + br_take(R, c_lext[ls]);
+                        br_refill(R);
+                        e = T->d_tab[(uint32_t)R.buf & ((1u << INF_D_BITS) - 1u)]; len = e & 15u;
+                        int ds = (int)(e >> 4);
+                        if (!e) ds = inf_canon((uint32_t)R.buf & 0x7fffu, T->d_count, T->d_sorted, 15, &len);
+                        if (ds < 0 || ds > 29) tok = INF_TOK_ERR;
+                        else {
+                            br_take(R, len);
+                            const uint32_t dist = c_dbase[ds] + br_take(R, c_dext[ds]);
+                            tok = 0x80000000u | (mlen << 16) | (dist - 1u);
+                        }
+                    }
+                }
+            }
+            tok = __shfl_sync(FULL, tok, 0);
+            if (tok == INF_TOK_EOB) break;
+            if (tok == INF_TOK_ERR) { fail = 3; break; }
+            if (!(tok >> 31)) {
+                if (produced >= expect) { fail = 2; break; }
+                if (lane == 0) o16[produced] = (uint16_t)tok;
+                produced += 1;
+            } else {
+                const uint32_t mlen = (tok >> 16) & 0x1ffu, dist = (tok & 0x7fffu) + 1u;
+                if (produced + mlen > expect || dist > produced + reach) { fail = 2; break; }
+                const int src0 = (int)produced - (int)dist;
+                for (uint32_t i = lane; i < mlen; i += 32) {
+                    const int rel = src0 + (int)(dist >= mlen ? i : i % dist);
+                    /* before the block: a marker for byte (32768 + rel) of the 32 KiB that precede it */
+                    const uint32_t v = rel < 0 ? 256u + (uint32_t)((int)B2D_WINDOW + rel) : (uint32_t)__ldcg(o16 + rel);
+                    o16[produced + i] = (uint16_t)v;
+                }
+                produced += mlen;
+            }
+            __syncwarp();    /* this symbol's stores are visible to the loads of the next copy */
+        }
+    }
+    if (!fail && produced != expect) fail = 2;
+    if (fail && lane == 0) atomicCAS(err, 0u, (fail << 28) | (b & 0x0fffffffu));
+}
+
+/* the byte a marker stands for: `k` indexes the 32 KiB that precede the block starting at output byte bs */
+__device__ __forceinline__ uint32_t inf_behind(const uint8_t *out8, const uint8_t *dict, uint32_t dict_n, uint64_t bs, uint32_t k) {
+    if (bs == 0) return dict[dict_n - B2D_WINDOW + k];      /* k >= 32768 - dict_n was checked by the decoder */
+    return __ldcg(out8 + (bs - B2D_WINDOW + k));
+}
+
+__global__ void __launch_bounds__(1024)
+k_inf_tails(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n,
+            uint32_t nblocks, uint64_t raw_n) {
+    for (uint32_t b = 0; b < nblocks; ++b) {
+        const uint64_t bs = (uint64_t)b * B2D_BLOCK;
+        const uint64_t be = raw_n - bs < B2D_BLOCK ? raw_n : bs + B2D_BLOCK;
+        const uint64_t ts = be - bs > B2D_WINDOW ? be - B2D_WINDOW : bs;
+        for (uint64_t p = ts + threadIdx.x; p < be; p += 1024) {
+            const uint32_t s = out16[p];
+            out8[p] = (uint8_t)(s < 256u ? s : inf_behind(out8, dict, dict_n, bs, s - 256u));
+        }
+        __syncthreads();     /* block b's tail is final before block b+1 reads it */
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n,
+             uint64_t raw_n) {
+    const uint64_t bs = (uint64_t)blockIdx.x * B2D_BLOCK;
+    const uint64_t be = raw_n - bs < B2D_BLOCK ? raw_n : bs + B2D_BLOCK;
+    const uint64_t ts = be - bs > B2D_WINDOW ? be - B2D_WINDOW : bs;      /* [ts, be) was written by k_inf_tails */
+    for (uint64_t p = bs + 8ull * threadIdx.x; p < ts; p += 8ull * 256) {
+        const uint4 q = *reinterpret_cast<const uint4 *>(out16 + p);     /* ts - bs is a multiple of 8 */
+        uint32_t s[8] = {q.x & 0xffffu, q.x >> 16, q.y & 0xffffu, q.y >> 16, q.z & 0xffffu, q.z >> 16, q.w & 0xffffu, q.w >> 16};
+        if ((q.x | q.y | q.z | q.w) & 0xff00ff00u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) if (s[i] >= 256u) s[i] = inf_behind(out8, dict, dict_n, bs, s[i] - 256u);
+        }
+        uint2 o;
+        o.x = s[0] | (s[1] << 8) | (s[2] << 16) | (s[3] << 24);
+        o.y = s[4] | (s[5] << 8) | (s[6] << 16) | (s[7] << 24);
+        *reinterpret_cast<uint2 *>(out8 + p) = o;
+    }
+}
+
+cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
+                               const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
+                               uint64_t raw_n, uint32_t *d_err, cudaStream_t st) {
+    if (nblocks == 0) return cudaSuccess;
+    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
+                                                                                d_out16, d_err);
+    k_inf_tails<<<1, 1024, 0, st>>>(d_out16, d_out, d_dict, dict_n, nblocks, raw_n);
+    k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
+    return cudaGetLastError();
+}

@@ -1,0 +1,14 @@
+/* b2d_inflate.h — launcher of the block-parallel inflate stages (b2d_inflate.cu). */
+#ifndef B2D_INFLATE_H
+#define B2D_INFLATE_H
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define B2D_INF_LAUNCHES 3   /* k_inf_decode, k_inf_tails, k_inf_finish */
+
+/* d_index[b] = byte offset of device block b in the compressed stream; d_out16 = 2 * raw_n bytes of scratch;
+ * *d_err (zeroed by the caller) receives (reason << 28) | block of the first block that failed to decode */
+cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
+                               const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
+                               uint64_t raw_n, uint32_t *d_err, cudaStream_t st);
+#endif

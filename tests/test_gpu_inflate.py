@@ -1,0 +1,131 @@
+"""GPU parity tests of the block-parallel inflate (b2d_inflate_device / b2d_inflate_host):
+streams written by this library's device-resident compressor, decoded with their block index, must give back
+the input byte for byte — and the very same streams must decode to the same bytes with the checkers (oracle
+inflate restated from inflate.c / inftrees.c, stdlib zlib).  All calls go through the C ABI."""
+import ctypes
+import zlib
+
+import numpy as np
+import pytest
+
+import synthdata
+from helpers import orc_inflate
+
+pytestmark = pytest.mark.gpu
+BLOCK = 131072
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from zlib_ng_b200 import _native
+    return _native
+
+
+@pytest.fixture(scope="module")
+def ctx(nat):
+    c = nat.Context(0, 8 << 20)      # 8 MiB batches: inputs above that exercise the index across batches
+    yield c
+    c.close()
+
+
+def deflate_indexed(nat, ctx, data: bytes, level: int, zdict: bytes = b""):
+    """device-resident compress of [zdict | data] -> (stream bytes, block offsets, device buffers)"""
+    L = nat.lib()
+    n, dn = len(data), len(zdict)
+    d_buf = ctx.device_alloc(dn + n + 64 + 16)
+    both = zdict + data
+    if both:
+        ctx.h2d(d_buf, both, len(both))
+    cap = (int(L.b2d_deflate_bound(n)) + 3) & ~3
+    d_out = ctx.device_alloc(cap + 16)
+    out_n, crc = ctypes.c_uint64(0), ctypes.c_uint32(0)
+    nat.check(L.b2d_deflate_device(ctx.handle, level, ctypes.c_void_p(d_buf), dn, n, ctypes.c_void_p(d_out), cap,
+                                   ctypes.byref(out_n), ctypes.byref(crc), None))
+    cnt = ctypes.c_uint64(0)
+    nat.check(L.b2d_block_index(ctx.handle, None, 0, ctypes.byref(cnt)))
+    offs = (ctypes.c_uint64 * max(cnt.value, 1))()
+    nat.check(L.b2d_block_index(ctx.handle, offs, cnt.value, ctypes.byref(cnt)))
+    stream = ctypes.create_string_buffer(max(out_n.value, 1))
+    ctx.d2h(stream, d_out, out_n.value)
+    return stream.raw[:out_n.value], list(offs)[:cnt.value], d_buf, d_out, crc.value
+
+
+def inflate_device(nat, ctx, d_stream, stream_n, offs, d_dict, dict_n, raw_n):
+    L = nat.lib()
+    nb = (raw_n + BLOCK - 1) // BLOCK
+    d_raw = ctx.device_alloc(raw_n + 64)
+    arr = (ctypes.c_uint64 * max(nb, 1))(*offs[:nb])
+    ms = ctypes.c_float(0)
+    try:
+        nat.check(L.b2d_inflate_device(ctx.handle, ctypes.c_void_p(d_stream), stream_n, arr, nb,
+                                       ctypes.c_void_p(d_dict) if dict_n else None, dict_n, ctypes.c_void_p(d_raw), raw_n,
+                                       ctypes.byref(ms)))
+        back = ctypes.create_string_buffer(max(raw_n, 1))
+        ctx.d2h(back, d_raw, raw_n)
+    finally:
+        ctx.device_free(d_raw)
+    return back.raw[:raw_n]
+
+
+CASES = [("fastq", 1_000_000, 5), ("mixed", 3_000_000, 6), ("fastq", 131072, 7), ("mixed", 131073, 8),
+         ("fastq", 32769, 10), ("mixed", 1023, 11), ("mixed", 1, 12), ("mixed", 20_000_000, 13)]
+
+
+@pytest.mark.parametrize("kind,n,seed", CASES)
+@pytest.mark.parametrize("level", [0, 1, 6, 9, 6 | (4 << 8)])     # stored, dynamic, and Z_FIXED -> fixed-Huffman blocks
+def test_round_trip_with_index(nat, ctx, kind, n, seed, level):
+    if n > 4_000_000 and level not in (1, 6):
+        pytest.skip("large case at two levels only")
+    data = synthdata.make(kind, n, seed).tobytes()
+    stream, offs, d_buf, d_out, crc = deflate_indexed(nat, ctx, data, level)
+    try:
+        assert len(offs) == (n + BLOCK - 1) // BLOCK + 1 and offs[0] == 0 and offs[-1] == len(stream)
+        assert offs == sorted(offs)
+        back = inflate_device(nat, ctx, d_out, len(stream), offs, 0, 0, n)
+    finally:
+        ctx.device_free(d_buf)
+        ctx.device_free(d_out)
+    assert back == data
+    assert crc == zlib.crc32(data)
+    # the checkers agree on what this stream holds
+    assert zlib.decompressobj(-15).decompress(stream) == data
+    if n <= 3_000_000:
+        assert orc_inflate(stream, n, need_final=False) == data
+
+
+@pytest.mark.parametrize("level", [1, 6])
+def test_dictionary_and_markers_across_many_blocks(nat, ctx, level):
+    # text that repeats with a period just under the window, runs of one byte, and a preset dictionary:
+    # most of every block depends (transitively) on the 32 KiB before it
+    rng = np.random.default_rng(3)
+    period = rng.integers(32, 127, 30_000, dtype=np.uint8).tobytes()
+    zdict = period[-20_000:]
+    data = period * 20 + b"\x00" * 700_000 + period[:5000] * 40 + b"ab" * 300_000
+    stream, offs, d_buf, d_out, _ = deflate_indexed(nat, ctx, data, level, zdict)
+    try:
+        back = inflate_device(nat, ctx, d_out, len(stream), offs, d_buf, len(zdict), len(data))
+    finally:
+        ctx.device_free(d_buf)
+        ctx.device_free(d_out)
+    assert back == data
+    assert zlib.decompressobj(-15, zdict=zdict).decompress(stream) == data
+
+
+def test_host_buffers_and_bad_index(nat, ctx):
+    L = nat.lib()
+    data = synthdata.make("fastq", 700_000, 21).tobytes()
+    stream, offs, d_buf, d_out, _ = deflate_indexed(nat, ctx, data, 6)
+    ctx.device_free(d_buf)
+    ctx.device_free(d_out)
+    nb = len(offs) - 1
+    arr = (ctypes.c_uint64 * nb)(*offs[:nb])
+    out = ctypes.create_string_buffer(len(data))
+    nat.check(L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb, None, 0, out, len(data)))
+    assert out.raw == data
+    # an index that does not match the size, or points into the middle of a block, is refused / detected
+    assert L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb - 1, None, 0, out, len(data)) == nat.B2D_STREAM_ERROR
+    bad = (ctypes.c_uint64 * nb)(*([offs[0]] + [o + 3 for o in offs[1:nb]]))
+    rc = L.b2d_inflate_host(ctx.handle, stream, len(stream), bad, nb, None, 0, out, len(data))
+    assert rc == -3 or out.raw != data
+    # empty
+    nat.check(L.b2d_inflate_host(ctx.handle, None, 0, None, 0, None, 0, None, 0))
