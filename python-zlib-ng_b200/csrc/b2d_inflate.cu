@@ -13,8 +13,8 @@
  *                  for longer codes; the warp executes every copy together.  Output is 16 bits per byte:
  *                  0..255 = the byte, 256 + k = "byte k of the 32 KiB before this block" — copies move these
  *                  markers around like bytes, so a block never waits for its predecessor.
- *   k_inf_tails    one CTA walks the blocks in order and resolves the last 32 KiB of each (one gather per
- *                  marker from the predecessor's resolved tail): the only serial part, ~1 us per block.
+ *   k_inf_tails    one cluster of 8 CTAs walks the blocks in order and resolves the last 32 KiB of each (one
+ *                  gather per marker from the predecessor's resolved tail): the only serial part.
  *   k_inf_finish   one CTA per block resolves the rest of the block against the now final tails.
  *
  * Reference code this stands in for: zng_inflate (zlib-ng/inflate.c:474-1150), inflate_table
@@ -22,11 +22,14 @@
  * (zlib_ngmodule.c:275-370, 2426-2637).  Streams from other writers carry no block index and are not
  * accepted.
  */
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "b2d_common.h"
 #include "b2d_inflate.h"
+
+namespace cg = cooperative_groups;
 
 #define FULL 0xffffffffu
 #define INF_WARPS 4
@@ -273,18 +276,48 @@ __device__ __forceinline__ uint32_t inf_behind(const uint8_t *out8, const uint8_
     return __ldcg(out8 + (bs - B2D_WINDOW + k));
 }
 
-__global__ void __launch_bounds__(1024)
+/* eight symbols -> eight bytes; markers are looked up in the resolved 32 KiB before the block at bs */
+__device__ __forceinline__ uint2 inf_resolve8(uint4 q, const uint8_t *out8, const uint8_t *dict, uint32_t dict_n, uint64_t bs) {
+    uint32_t s[8] = {q.x & 0xffffu, q.x >> 16, q.y & 0xffffu, q.y >> 16, q.z & 0xffffu, q.z >> 16, q.w & 0xffffu, q.w >> 16};
+    if ((q.x | q.y | q.z | q.w) & 0xff00ff00u) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) if (s[i] >= 256u) s[i] = inf_behind(out8, dict, dict_n, bs, s[i] - 256u);
+    }
+    uint2 o;
+    o.x = s[0] | (s[1] << 8) | (s[2] << 16) | (s[3] << 24);
+    o.y = s[4] | (s[5] << 8) | (s[6] << 16) | (s[7] << 24);
+    return o;
+}
+
+/* The chain over the blocks is serial, and one SM needs ~5 us of instruction issue to look 32768 symbols up.  A
+ * thread-block cluster spreads every step over INF_CLUSTER SMs: a thread owns eight symbols of each tail, the next
+ * block's symbols are loaded while this block's markers are looked up, and a step ends with one cluster barrier
+ * (release / acquire at cluster scope: block b's tail is final before block b+1 looks into it). */
+#define INF_CLUSTER 8
+#define INF_TAIL_THREADS (B2D_WINDOW / 8 / INF_CLUSTER)      /* 512 */
+__global__ void __launch_bounds__(INF_TAIL_THREADS)
 k_inf_tails(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n,
             uint32_t nblocks, uint64_t raw_n) {
-    for (uint32_t b = 0; b < nblocks; ++b) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const uint32_t t = blockIdx.x * INF_TAIL_THREADS + threadIdx.x;          /* 0 .. 4095: one group of 8 symbols */
+    const uint32_t nfull = (uint32_t)(raw_n / B2D_BLOCK);          /* blocks of 128 KiB: their tails are aligned */
+    const uint64_t toff = (B2D_BLOCK - B2D_WINDOW) + 8u * t;
+    uint4 cur = make_uint4(0, 0, 0, 0), nxt = cur;
+    if (nfull) cur = *reinterpret_cast<const uint4 *>(out16 + toff);
+    for (uint32_t b = 0; b < nfull; ++b) {
         const uint64_t bs = (uint64_t)b * B2D_BLOCK;
-        const uint64_t be = raw_n - bs < B2D_BLOCK ? raw_n : bs + B2D_BLOCK;
-        const uint64_t ts = be - bs > B2D_WINDOW ? be - B2D_WINDOW : bs;
-        for (uint64_t p = ts + threadIdx.x; p < be; p += 1024) {
+        if (b + 1 < nfull) nxt = *reinterpret_cast<const uint4 *>(out16 + bs + B2D_BLOCK + toff);
+        *reinterpret_cast<uint2 *>(out8 + bs + toff) = inf_resolve8(cur, out8, dict, dict_n, bs);
+        cluster.sync();
+        cur = nxt;
+    }
+    if (nfull < nblocks) {   /* the last, shorter block: nobody depends on it */
+        const uint64_t bs = (uint64_t)nfull * B2D_BLOCK;
+        const uint64_t ts = raw_n - bs > B2D_WINDOW ? raw_n - B2D_WINDOW : bs;
+        for (uint64_t p = ts + t; p < raw_n; p += INF_CLUSTER * INF_TAIL_THREADS) {
             const uint32_t s = out16[p];
             out8[p] = (uint8_t)(s < 256u ? s : inf_behind(out8, dict, dict_n, bs, s - 256u));
         }
-        __syncthreads();     /* block b's tail is final before block b+1 reads it */
     }
 }
 
@@ -295,16 +328,9 @@ k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *_
     const uint64_t be = raw_n - bs < B2D_BLOCK ? raw_n : bs + B2D_BLOCK;
     const uint64_t ts = be - bs > B2D_WINDOW ? be - B2D_WINDOW : bs;      /* [ts, be) was written by k_inf_tails */
     for (uint64_t p = bs + 8ull * threadIdx.x; p < ts; p += 8ull * 256) {
-        const uint4 q = *reinterpret_cast<const uint4 *>(out16 + p);     /* ts - bs is a multiple of 8 */
-        uint32_t s[8] = {q.x & 0xffffu, q.x >> 16, q.y & 0xffffu, q.y >> 16, q.z & 0xffffu, q.z >> 16, q.w & 0xffffu, q.w >> 16};
-        if ((q.x | q.y | q.z | q.w) & 0xff00ff00u) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) if (s[i] >= 256u) s[i] = inf_behind(out8, dict, dict_n, bs, s[i] - 256u);
-        }
-        uint2 o;
-        o.x = s[0] | (s[1] << 8) | (s[2] << 16) | (s[3] << 24);
-        o.y = s[4] | (s[5] << 8) | (s[6] << 16) | (s[7] << 24);
-        *reinterpret_cast<uint2 *>(out8 + p) = o;
+        /* a group of 8 that straddles ts rewrites a few tail bytes with the same values */
+        const uint4 q = *reinterpret_cast<const uint4 *>(out16 + p);
+        *reinterpret_cast<uint2 *>(out8 + p) = inf_resolve8(q, out8, dict, dict_n, bs);
     }
 }
 
@@ -314,7 +340,16 @@ cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_
     if (nblocks == 0) return cudaSuccess;
     k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
                                                                                 d_out16, d_err);
-    k_inf_tails<<<1, 1024, 0, st>>>(d_out16, d_out, d_dict, dict_n, nblocks, raw_n);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = INF_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, k_inf_tails, (const uint16_t *)d_out16, d_out, d_dict, dict_n, nblocks, raw_n);
+        if (e != cudaSuccess) return e;
+    }
     k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
     return cudaGetLastError();
 }

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--batch-mib", type=int, default=256)
     ap.add_argument("--crc-mib", type=int, default=0)
     ap.add_argument("--verify", action="store_true")
+    ap.add_argument("--inflate", action="store_true", help="also time b2d_inflate_device on each level's output")
     a = ap.parse_args()
     n = a.mib << 20
     t = time.time()
@@ -57,6 +58,22 @@ def main():
         L.b2d_profile_read(ctx.handle, sm, None, 1)
         nat.check(L.b2d_profile(ctx.handle, 0))
         print("   stage ms alone:", " ".join(f"{nm}={sm[i]:.2f}" for i, nm in enumerate(["chains", "match", "parse", "plan", "scan", "emit"])), flush=True)
+        if a.inflate:
+            cnt = ctypes.c_uint64(0)
+            nat.check(L.b2d_block_index(ctx.handle, None, 0, ctypes.byref(cnt)))
+            offs = (ctypes.c_uint64 * cnt.value)()
+            nat.check(L.b2d_block_index(ctx.handle, offs, cnt.value, ctypes.byref(cnt)))
+            d_back = ctx.device_alloc(n + 64)
+            for r in range(a.reps):
+                ims = ctypes.c_float(0)
+                nat.check(L.b2d_inflate_device(ctx.handle, ctypes.c_void_p(d_out), out_n.value, offs, cnt.value - 1, None, 0,
+                                               ctypes.c_void_p(d_back), n, ctypes.byref(ims)))
+                print(f"   inflate rep{r}: {ims.value:.2f} ms  {n / ims.value / 1e6:.2f} GB/s (output bytes)", flush=True)
+            v1, v2 = ctypes.c_uint32(0), ctypes.c_uint32(0)
+            nat.check(L.b2d_crc32_device(ctx.handle, 0, ctypes.c_void_p(d_back), n, ctypes.byref(v1), None))
+            nat.check(L.b2d_crc32_device(ctx.handle, 0, ctypes.c_void_p(d_in), n, ctypes.byref(v2), None))
+            print("   inflate crc matches input:", v1.value == v2.value, flush=True)
+            ctx.device_free(d_back)
         if a.verify:
             host = np.empty(out_n.value, dtype=np.uint8)
             ctx.d2h(host.ctypes.data_as(ctypes.c_void_p), d_out, out_n.value)
