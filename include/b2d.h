@@ -100,7 +100,8 @@ int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads);
  * (first version.  The reference decompresses with zng_inflate on one thread:
  * zlib_ng.decompress, zlib_ngmodule.c:275-370; _GzipReader.read, :2426-2637; gzip_ng_threaded.py:90-167.)
  *
- * b2d_block_index: where every 128 KiB device block of the LAST b2d_deflate_device call on this context starts
+ * b2d_block_index: where every 128 KiB device block of the LAST deflate call on this context (b2d_deflate_device,
+ * b2d_deflate_host, b2d_compress_and_crc) starts
  * in its compressed output: *count = blocks + 1 entries (the last one is the stream length), copied to
  * `offsets` when it is not NULL (B2D_BUF_ERROR if cap < *count).  Blocks start byte-aligned. */
 int b2d_block_index(b2d_ctx *ctx, uint64_t *offsets, uint64_t cap, uint64_t *count);

@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include <thread>
+#include <vector>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -94,6 +95,8 @@ struct b2d_ctx {
     uint64_t launches;
     /* compressed start offset of every device block of the last b2d_deflate_device call (b2d_block_index) */
     uint64_t *d_index; uint64_t index_cap, index_n;
+    /* host-buffer calls keep offsets relative to each batch's output: index_base[j] is where batch j's output starts */
+    std::vector<uint64_t> index_base; uint64_t index_total;
     /* inflate scratch: 16-bit symbols, block index, error word */
     uint16_t *d_inf16; uint64_t inf16_cap;
     uint64_t *d_inf_index; uint64_t inf_index_cap;
@@ -344,6 +347,20 @@ extern "C" int b2d_profile_read(b2d_ctx *c, double *stage_ms, uint64_t *stage_la
     return B2D_OK;
 }
 
+/* room for the block index of a call over n input bytes */
+static int ensure_index(b2d_ctx *c, uint64_t n) {
+    const uint64_t need = (n + B2D_BLOCK - 1) / B2D_BLOCK + 2;
+    if (need > c->index_cap) {
+        cudaFree(c->d_index); c->d_index = nullptr; c->index_cap = 0;
+        CU(cudaMalloc(&c->d_index, need * sizeof(uint64_t)));
+        c->index_cap = need;
+    }
+    c->index_n = 0;
+    c->index_base.clear();
+    c->index_total = 0;
+    return B2D_OK;
+}
+
 extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
                                   uint64_t out_cap, uint64_t *out_n, uint32_t *crc, float *ms) {
     if (!c || !out_n || (!d_buf && n) || !d_out) return fail(B2D_STREAM_ERROR, "null argument");
@@ -358,15 +375,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     CU(cudaMemsetAsync(c->d_total, 0, sizeof(uint64_t), c->st));
     const uint64_t readable = dict_n + n + B2D_DEVICE_PAD;
     int nprof = 0;
-    {   /* room for the block index of this call */
-        const uint64_t need = (n + B2D_BLOCK - 1) / B2D_BLOCK + 1;
-        if (need > c->index_cap) {
-            cudaFree(c->d_index); c->d_index = nullptr; c->index_cap = 0;
-            CU(cudaMalloc(&c->d_index, need * sizeof(uint64_t)));
-            c->index_cap = need;
-        }
-        c->index_n = 0;
-    }
+    { int rc = ensure_index(c, n); if (rc) return rc; }
     /* several batches alternate between two lanes (streams + intermediates); b2d_profile(ctx, 2) keeps
      * one lane so that the stage times are those of kernels running alone */
     const bool two = n > c->max_batch && c->profiling != 2;
@@ -489,6 +498,8 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     b2d_cksum_ws *ck[B2D_NSLOT] = {c->ck};
     for (int i = 1; i < B2D_NSLOT; ++i) { d_in[i] = c->d_inx[i - 1]; d_out[i] = c->d_outx[i - 1]; d_total[i] = c->d_totalx[i - 1]; ck[i] = c->ckx[i - 1]; }
     const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
+    if ((rc = ensure_index(c, n))) return rc;
+    c->index_base.assign(nb, 0);
     uint64_t produced = 0;
     uint64_t drained = 0;                 /* bytes of `out` final (staged output only) */
     uint64_t pend_off = 0, pend_n = 0; int pend_s = -1;
@@ -508,6 +519,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         if (adler_acc) *adler_acc = b2d_adler32_dev_finish(ck[s], m, *adler_acc);
         const uint64_t got = c->h_total[s];
         if (produced + got + reserve > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+        c->index_base[j] = produced;
         if (out_pinned) {
             CU(cudaMemcpyAsync(out + produced, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
             CU(cudaEventRecord(c->ev_out[s], c->st_out));
@@ -554,6 +566,8 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         CU(b2d_launch_pipeline(&J, cs[ln], nullptr));
         c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
+        CU(cudaMemcpyAsync(c->d_index + off / B2D_BLOCK, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK) * sizeof(uint64_t),
+                           cudaMemcpyDeviceToDevice, cs[ln]));
         if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
         if (adler_acc) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
@@ -565,6 +579,8 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     if ((rc = drain())) { cudaDeviceSynchronize(); return rc; }
     CU(cudaStreamSynchronize(c->st_out));
     *produced_out = produced;
+    c->index_total = produced;
+    c->index_n = (n + B2D_BLOCK - 1) / B2D_BLOCK + 1;
     return B2D_OK;
 }
 
@@ -653,7 +669,8 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         CU(cudaStreamSynchronize(c->st));
         return B2D_OK;
     };
-    for (uint64_t off = 0; off < n; off += c->max_batch) {
+    { int rc = ensure_index(c, n); if (rc) return rc; }
+    for (uint64_t off = 0; off < n; off += c->max_batch) {      /* one trip: longer inputs took the pipelined path */
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
         uint64_t D;
         int rc;
@@ -672,6 +689,8 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         CU(b2d_launch_pipeline(&J, c->st, nullptr));
         c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaMemcpyAsync(c->d_index, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c->st));
+        c->index_n = (m + B2D_BLOCK - 1) / B2D_BLOCK + 1;
         if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_in + D, m, c->st)); c->launches += crc_launches(c->d_in + D, m); }
         CU(cudaStreamSynchronize(c->st));
         if (crc) crc_acc = b2d_crc32_dev_finish(c->ck, m, crc_acc);
@@ -723,6 +742,11 @@ extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint
     CU(cudaSetDevice(c->device));
     CU(cudaMemcpyAsync(offsets, c->d_index, c->index_n * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
+    if (!c->index_base.empty()) {       /* multi-batch host call: offsets were relative to each batch's output */
+        const uint64_t bpb = c->max_batch / B2D_BLOCK;
+        for (uint64_t i = 0; i + 1 < c->index_n; ++i) offsets[i] += c->index_base[i / bpb];
+        offsets[c->index_n - 1] = c->index_total;
+    }
     return B2D_OK;
 }
 

@@ -40,6 +40,41 @@ _STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
 # overlap batch j's kernels.  threads=N asks for min(N, this) of them.
 _STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "4")), 1)
 _COPY_CHUNK = 4 << 20
+# Block index (for the GPU reader): one data member, then the empty member the reference's close() leaves
+# (gzip_ng_threaded.py:340-355), then empty members whose FEXTRA field ("B2" subfields, RFC 1952 2.3.1.1) lists
+# the compressed size of every 128 KiB device block, then a fixed-size locator member.  Other gzip readers skip
+# extra fields and empty members, so the file stays an ordinary multi-member gzip file.
+_WRITE_INDEX = os.environ.get("B2D_WRITE_INDEX", "1") != "0"
+_GPU_READ = os.environ.get("B2D_GPU_READ", "1") != "0"
+_DEVICE_BLOCK = 128 * 1024
+_INDEX_CHUNK = 16000                      # block sizes per index member (XLEN is 16 bits)
+_LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size, index offset, blocks
+_LOCATOR_MAGIC = b"B2DX"
+_LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
+_READ_WINDOW_BLOCKS = 1024                # device blocks (128 MiB of output) the reader decodes per GPU call
+
+
+def _extra_member(payload: bytes) -> bytes:
+    """An empty gzip member whose header carries one "B2" extra subfield."""
+    sub = b"B2" + struct.pack("<H", len(payload)) + payload
+    return (struct.pack("<BBBBIBB", 0x1F, 0x8B, 8, 4, 0, 0, 0xFF) + struct.pack("<H", len(sub)) + sub
+            + b"\x03\x00" + b"\x00" * 8)
+
+
+def _parse_extra_member(buf: bytes, off: int):
+    """(payload, next offset) of an empty "B2" member at buf[off:], or None."""
+    if len(buf) < off + 12 or buf[off:off + 4] != b"\x1f\x8b\x08\x04":
+        return None
+    xlen = struct.unpack_from("<H", buf, off + 10)[0]
+    end = off + 12 + xlen
+    if xlen < 4 or len(buf) < end + 10 or buf[off + 12:off + 14] != b"B2":
+        return None
+    n = struct.unpack_from("<H", buf, off + 14)[0]
+    if n + 4 != xlen or buf[end:end + 10] != b"\x03\x00" + b"\x00" * 8:
+        return None
+    return buf[off + 16:off + 16 + n], end + 10
+
+
 _COPY_THREADS = max(int(os.environ.get("B2D_COPY_THREADS", "8")), 1)
 
 
@@ -116,19 +151,127 @@ def open_as_binary_stream(filename, open_mode):
 
 
 class _ThreadedGzipReader(io.RawIOBase):
-    """Streamed gzip reader.  Inflate is outside the accelerated path; this wraps
-    CPython's GzipFile so that "rb" keeps working for callers of open()."""
+    """Streamed gzip reader.  Files written by this module's writer carry a block index (see _WRITE_INDEX): those
+    are inflated on the GPU, a window of device blocks per call (b2d_inflate_host: one warp per 128 KiB block),
+    with the member's CRC32 and size checked at the end like gzip does.  Everything else goes through CPython's
+    GzipFile — the reference reads with one zng_inflate thread as well (gzip_ng_threaded.py:90-167)."""
 
     def __init__(self, filename, queue_size=2, block_size=1024 * 1024):
         self.raw, self.closefd = open_as_binary_stream(filename, "rb")
-        self.fileobj = _stdgzip.GzipFile(fileobj=self.raw, mode="rb")
         self.pos = 0
         self._closed = False
+        self._gpu = None
+        if _GPU_READ:
+            try:
+                self._gpu = self._find_index()
+            except Exception:
+                self._gpu = None
+        self.fileobj = None if self._gpu else _stdgzip.GzipFile(fileobj=self.raw, mode="rb")
+
+    # ---- GPU path
+    def _find_index(self):
+        raw = self.raw
+        if not (hasattr(raw, "seekable") and raw.seekable()):
+            return None
+        here = raw.tell()
+        try:
+            end = raw.seek(0, io.SEEK_END)
+            if end - here < _LOCATOR_MEMBER + 20:
+                return None
+            raw.seek(end - _LOCATOR_MEMBER)
+            got = _parse_extra_member(raw.read(_LOCATOR_MEMBER), 0)
+            if not got or len(got[0]) != _LOCATOR.size:
+                return None
+            magic, version, start, raw_n, index_off, nblocks = _LOCATOR.unpack(got[0])
+            if (magic != _LOCATOR_MAGIC or version != 1 or start != here or not here < index_off < end
+                    or nblocks != (raw_n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK or nblocks == 0):
+                return None
+            raw.seek(index_off)
+            buf = raw.read(end - _LOCATOR_MEMBER - index_off)
+            sizes, off = [], 0
+            while len(sizes) < nblocks:
+                got = _parse_extra_member(buf, off)
+                if not got:
+                    return None
+                payload, off = got
+                kind, _, _, cnt = struct.unpack_from("<BBHI", payload, 0)
+                if kind != 1 or len(payload) != 8 + 4 * cnt:
+                    return None
+                sizes.extend(struct.unpack_from(f"<{cnt}I", payload, 8))
+            if len(sizes) != nblocks or off != len(buf):
+                return None
+            raw.seek(here)
+            if raw.read(4) != b"\x1f\x8b\x08\x00":
+                return None
+            # data member: 10-byte header, the blocks, 03 00, CRC32, ISIZE; then the empty member of close()
+            if here + 10 + sum(sizes) + 2 + 8 > index_off:
+                return None
+            _native.default_context()      # no usable GPU: the CPU reader takes over (raises here)
+            return {"sizes": sizes, "raw_n": raw_n, "next": 0, "cpos": here + 10, "tail": b"", "buf": None, "off": 0,
+                    "crc": 0, "done": False, "end": end}
+        finally:
+            if self._gpu is None:
+                raw.seek(here)
+
+    def _gpu_fill(self):
+        g = self._gpu
+        sizes, nb_all = g["sizes"], len(g["sizes"])
+        if g["next"] >= nb_all:
+            if not g["done"]:
+                self.raw.seek(g["cpos"])
+                tail = self.raw.read(10)
+                crc, isize = struct.unpack("<II", tail[2:10]) if len(tail) == 10 else (None, None)
+                if tail[:2] != b"\x03\x00" or crc != g["crc"] or isize != (g["raw_n"] & 0xFFFFFFFF):
+                    raise _stdgzip.BadGzipFile("CRC check failed" if tail[:2] == b"\x03\x00" else "Bad stream end")
+                g["done"] = True
+            return False
+        first = g["next"]
+        nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
+        part = sizes[first:first + nb]
+        comp_n = sum(part)
+        self.raw.seek(g["cpos"])
+        comp = self.raw.read(comp_n)
+        if len(comp) != comp_n:
+            raise EOFError("Compressed file ended before the end-of-stream marker was reached")
+        raw_n = min(nb * _DEVICE_BLOCK, g["raw_n"] - first * _DEVICE_BLOCK)
+        offs = (ctypes.c_uint64 * nb)()
+        acc = 0
+        for i, sz in enumerate(part):
+            offs[i] = acc
+            acc += sz
+        out = bytearray(raw_n)
+        caddr, _, k1 = _native._addr(comp)
+        oaddr, _, k2 = _native._addr(out)
+        tail = g["tail"]
+        taddr, tn, k3 = _native._addr(tail) if tail else (None, 0, None)
+        ctx = _native.default_context()
+        rc = _native.lib().b2d_inflate_host(ctx.handle, caddr, comp_n, offs, nb, taddr, tn, oaddr, raw_n)
+        del k1, k2, k3
+        if rc:
+            raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
+        g["crc"] = zlib_ng.crc32(out, g["crc"])
+        g["tail"] = bytes(out[-DEFLATE_WINDOW_SIZE:]) if raw_n >= DEFLATE_WINDOW_SIZE else (tail + bytes(out))[-DEFLATE_WINDOW_SIZE:]
+        g["buf"], g["off"] = out, 0
+        g["next"] = first + nb
+        g["cpos"] += comp_n
+        return True
 
     def readinto(self, b):
         if self._closed:
             raise ValueError("I/O operation on closed file")
-        n = self.fileobj.readinto(b)
+        if self._gpu is None:
+            n = self.fileobj.readinto(b)
+            self.pos += n
+            return n
+        g = self._gpu
+        if g["buf"] is None or g["off"] >= len(g["buf"]):
+            g["buf"] = None
+            if not self._gpu_fill():
+                return 0
+        mv = memoryview(b).cast("B")
+        n = min(len(mv), len(g["buf"]) - g["off"])
+        mv[:n] = memoryview(g["buf"])[g["off"]:g["off"] + n]
+        g["off"] += n
         self.pos += n
         return n
 
@@ -143,7 +286,8 @@ class _ThreadedGzipReader(io.RawIOBase):
     def close(self) -> None:
         if self._closed:
             return
-        self.fileobj.close()
+        if self.fileobj is not None:
+            self.fileobj.close()
         if self.closefd:
             self.raw.close()
         self._closed = True
@@ -214,6 +358,10 @@ class _ThreadedGzipWriter(io.RawIOBase):
         self.index = 0
         self._crc = 0
         self._size = 0
+        # block index: only for a file this writer starts itself and fills with whole device blocks
+        self._indexing = _WRITE_INDEX and "a" not in mode and "+" not in mode and self.batch % _DEVICE_BLOCK == 0
+        self._blk_sizes = []          # compressed size of every device block of the current member
+        self._members = []            # (start offset, raw size, block sizes) of finished members that hold data
         self.running = False
         if nw > 1:
             self.compression_workers = [threading.Thread(target=self._compress, args=(i,)) for i in range(nw)]
@@ -223,6 +371,12 @@ class _ThreadedGzipWriter(io.RawIOBase):
             self.output_worker = threading.Thread(target=self._compress_and_write)
         self.raw, self.closefd = open_as_binary_stream(filename, mode)
         self._closed = False
+        self._member_start = None
+        if self._indexing:
+            try:
+                self._member_start = self.raw.tell()
+            except Exception:
+                self._indexing = False
         self._write_gzip_header()
         self.start()
 
@@ -236,6 +390,26 @@ class _ThreadedGzipWriter(io.RawIOBase):
             xfl = 0
         # the reference packs (…, mtime, os=0xff, xfl): byte 8 = 0xff, byte 9 = xfl
         self.raw.write(struct.pack("<BBBBIBB", 0x1F, 0x8B, 8, 0, 0, 0xFF, xfl))
+
+    def _note_blocks(self, sizes):
+        if sizes is None:
+            self._indexing = False
+        elif self._indexing:
+            self._blk_sizes.extend(sizes)
+
+    def _write_index(self):
+        """After the last member: the block index of a file that holds exactly one data member (see _WRITE_INDEX)."""
+        if not self._indexing or len(self._members) != 1:
+            return
+        start, raw_n, sizes = self._members[0]
+        if len(sizes) != (raw_n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK or max(sizes) >= 1 << 32:
+            return
+        index_off = self.raw.tell()
+        for i in range(0, len(sizes), _INDEX_CHUNK):
+            part = sizes[i:i + _INDEX_CHUNK]
+            self.raw.write(_extra_member(struct.pack("<BBHI", 1, 0, 0, len(part)) + struct.pack(f"<{len(part)}I", *part)))
+        self.raw.write(_extra_member(_LOCATOR.pack(_LOCATOR_MAGIC, 1, start, raw_n, index_off, len(sizes))))
+        self.raw.flush()
 
     def _check_closed(self, msg=None):
         if self._closed:
@@ -340,6 +514,9 @@ class _ThreadedGzipWriter(io.RawIOBase):
                 return
         self.raw.write(b"\x03\x00")          # = zlib_ng.compress(b"", wbits=-15): BFINAL fixed block with only EOB
         self.raw.write(struct.pack("<II", self._crc, self._size & 0xFFFFFFFF))
+        if self._indexing and self._size:
+            self._members.append((self._member_start, self._size, self._blk_sizes))
+        self._blk_sizes = []
         self._crc = 0
         self._size = 0
         self._last_tail = b""
@@ -358,6 +535,8 @@ class _ThreadedGzipWriter(io.RawIOBase):
         with self.lock:
             if self.exception:
                 raise self.exception
+        if self._indexing:
+            self._member_start = self.raw.tell()
         self._write_gzip_header()
 
     def close(self) -> None:
@@ -365,6 +544,8 @@ class _ThreadedGzipWriter(io.RawIOBase):
             return
         try:
             self._end_gzip_stream()
+            if not self.exception:
+                self._write_index()
         finally:
             self.stop()
         if self.exception:
@@ -400,7 +581,14 @@ class _ThreadedGzipWriter(io.RawIOBase):
             raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}")
         if rc:
             zlib_ng._raise(rc, "while compressing data")
-        return out_buf.view[:out_n.value], crc.value, n
+        sizes = None
+        if self._indexing:
+            nb = (n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK
+            offs = (ctypes.c_uint64 * (nb + 1))()
+            cnt = ctypes.c_uint64(0)
+            if _native.lib().b2d_block_index(ctx.handle, offs, nb + 1, ctypes.byref(cnt)) == 0 and cnt.value == nb + 1:
+                sizes = [offs[i + 1] - offs[i] for i in range(nb)]
+        return out_buf.view[:out_n.value], crc.value, n, sizes
 
     def _release(self, job):
         if len(job) > 2 and job[2] is not None:
@@ -421,9 +609,10 @@ class _ThreadedGzipWriter(io.RawIOBase):
                     in_queue.task_done()
                     return
                 try:
-                    compressed, crc, n = self._run_job(0, job, out_buf)
+                    compressed, crc, n, sizes = self._run_job(0, job, out_buf)
                     self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
                     self._size += n
+                    self._note_blocks(sizes)
                     self.raw.write(compressed)
                 except Exception as e:
                     self._release(job)
@@ -464,14 +653,14 @@ class _ThreadedGzipWriter(io.RawIOBase):
                             in_queue.task_done()
                             return
                 try:
-                    compressed, crc, n = self._run_job(index, job, out_buf)
+                    compressed, crc, n, sizes = self._run_job(index, job, out_buf)
                 except Exception as e:
                     self._release(job)
                     in_queue.task_done()
                     self._set_error_and_empty_queue(e, in_queue)
                     return
                 self._release(job)
-                out_queue.put((compressed, crc, n, spare, out_buf))
+                out_queue.put((compressed, crc, n, spare, out_buf, sizes))
                 in_queue.task_done()
         finally:
             # the writer thread may still be writing from one of these: let it drain before they go back to the pool
@@ -494,10 +683,11 @@ class _ThreadedGzipWriter(io.RawIOBase):
             if item is None:
                 q.task_done()
                 return
-            compressed, crc, n, spare, out_buf = item
+            compressed, crc, n, spare, out_buf, sizes = item
             try:
                 self._crc = zlib_ng.crc32_combine(self._crc, crc, n)
                 self._size += n
+                self._note_blocks(sizes)
                 self.raw.write(compressed)
             except Exception as e:
                 q.task_done()

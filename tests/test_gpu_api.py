@@ -284,8 +284,24 @@ def test_threaded_write_default_block_size_and_level1(gzt, tmp_path):
     blob = target.read_bytes()
     assert gzip.decompress(blob) == data
     assert blob[9] == 4
-    # 2-member file, the second one empty
-    assert blob.endswith(b"\x1f\x8b\x08\x00\x00\x00\x00\x00\xff\x04\x03\x00" + b"\x00" * 8)
+    # 2-member file, the second one empty; the block index for the GPU reader follows as further
+    # empty members (extra fields only), located by the fixed-size last member
+    empty = b"\x1f\x8b\x08\x00\x00\x00\x00\x00\xff\x04\x03\x00" + b"\x00" * 8
+    magic, version, start, raw_n, index_off, nblocks = gzt._LOCATOR.unpack(
+        gzt._parse_extra_member(blob[-gzt._LOCATOR_MEMBER:], 0)[0])
+    assert (magic, version, start, raw_n, nblocks) == (b"B2DX", 1, 0, len(data), (len(data) + 131071) // 131072)
+    assert blob[:index_off].endswith(empty)
+
+
+def test_threaded_write_without_index_ends_like_the_reference(gzt, tmp_path, monkeypatch):
+    monkeypatch.setattr(gzt, "_WRITE_INDEX", False)
+    data = synthdata.make("fastq", 1_000_000, 5).tobytes()
+    target = tmp_path / "plain.gz"
+    with gzt.open(target, "wb", compresslevel=6, threads=2) as f:
+        f.write(data)
+    blob = target.read_bytes()
+    assert gzip.decompress(blob) == data
+    assert blob.endswith(b"\x1f\x8b\x08\x00\x00\x00\x00\x00\xff\x00\x03\x00" + b"\x00" * 8)
 
 
 def test_threaded_open_no_threads(gzt, tmp_path):

@@ -129,3 +129,63 @@ def test_host_buffers_and_bad_index(nat, ctx):
     assert rc == -3 or out.raw != data
     # empty
     nat.check(L.b2d_inflate_host(ctx.handle, None, 0, None, 0, None, 0, None, 0))
+
+
+# ---- the user-facing side: gzip_ng_threaded.open(..., "rb") of files written by gzip_ng_threaded.open(..., "wb")
+@pytest.fixture(scope="module")
+def gzt():
+    from zlib_ng_b200 import gzip_ng_threaded
+    return gzip_ng_threaded
+
+
+def test_reader_uses_the_block_index(gzt, tmp_path, monkeypatch):
+    import gzip
+    data = synthdata.make("mixed", 9_000_000, 31).tobytes()
+    path = tmp_path / "indexed.gz"
+    with gzt.open(path, "wb", compresslevel=6, threads=4) as f:
+        for off in range(0, len(data), 1_000_003):
+            f.write(data[off:off + 1_000_003])
+    blob = path.read_bytes()
+    assert gzip.decompress(blob) == data                   # index members are empty gzip members to everyone else
+    monkeypatch.setattr(gzt, "_READ_WINDOW_BLOCKS", 8)      # several GPU calls, dictionary carried between them
+    with gzt.open(path, "rb") as f:
+        assert f.raw._gpu is not None
+        back = f.read()
+    assert back == data
+    with gzt.open(path, "rt", encoding="latin-1") as f:
+        assert f.read(100) == data[:100].decode("latin-1")
+    # a flipped bit in the compressed data is caught (decode error or CRC mismatch), like gzip does
+    bad = bytearray(blob)
+    bad[len(blob) // 3] ^= 0x10
+    (tmp_path / "bad.gz").write_bytes(bytes(bad))
+    with pytest.raises((gzip.BadGzipFile, EOFError, OSError)):
+        with gzt.open(tmp_path / "bad.gz", "rb") as f:
+            f.read()
+
+
+def test_reader_without_index_and_small_files(gzt, tmp_path):
+    import gzip
+    data = synthdata.make("fastq", 300_000, 32).tobytes()
+    (tmp_path / "plain.gz").write_bytes(gzip.compress(data))
+    with gzt.open(tmp_path / "plain.gz", "rb") as f:
+        assert f.raw._gpu is None
+        assert f.read() == data
+    for n in (1, 131072, 131073):
+        with gzt.open(tmp_path / "s.gz", "wb", threads=2) as f:
+            f.write(data[:n])
+        with gzt.open(tmp_path / "s.gz", "rb") as f:
+            assert f.raw._gpu is not None
+            assert f.read() == data[:n]
+    # flush() starts a new member: such files carry no index and are read the ordinary way
+    with gzt.open(tmp_path / "two.gz", "wb", threads=2) as f:
+        f.write(data)
+        f.flush()
+        f.write(data)
+    with gzt.open(tmp_path / "two.gz", "rb") as f:
+        assert f.raw._gpu is None
+        assert f.read() == data + data
+    # empty file
+    with gzt.open(tmp_path / "e.gz", "wb", threads=2) as f:
+        pass
+    with gzt.open(tmp_path / "e.gz", "rb") as f:
+        assert f.read() == b""
