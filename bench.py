@@ -420,6 +420,38 @@ def main():
         want = np.tile(base, (head_n + base.size - 1) // base.size)[:head_n].tobytes()
         extra["roundtrip_64MiB_ok"] = zlib.decompressobj(-15).decompress(host.tobytes()) == want
         extra["crc_ok"] = c1 == zlib.crc32(want)
+        # the other side of the wire: block-parallel inflate of this run's own output,
+        # device-resident, checked with the CRC kernel; beside it the reference's inflate (one thread, as its
+        # reader runs it) on the first 256 MiB worth of the same stream
+        try:
+            _, o_full, c_full = device_pass()
+            cnt = ctypes.c_uint64(0)
+            nat.check(L.b2d_block_index(ctx.handle, None, 0, ctypes.byref(cnt)))
+            offs = (ctypes.c_uint64 * cnt.value)()
+            nat.check(L.b2d_block_index(ctx.handle, offs, cnt.value, ctypes.byref(cnt)))
+            d_back = ctx.device_alloc(n + 64)
+            best = 1e9
+            for _ in range(3):
+                ims = ctypes.c_float(0)
+                nat.check(L.b2d_inflate_device(ctx.handle, ctypes.c_void_p(d_out), o_full, offs, cnt.value - 1, None, 0,
+                                               ctypes.c_void_p(d_back), n, ctypes.byref(ims)))
+                best = min(best, ims.value)
+            v = ctypes.c_uint32(0)
+            nat.check(L.b2d_crc32_device(ctx.handle, 0, ctypes.c_void_p(d_back), n, ctypes.byref(v), None))
+            ctx.device_free(d_back)
+            extra["inflate_GBps"] = n / best / 1e6
+            extra["inflate_crc_ok"] = v.value == c_full
+            ref = reference_module()
+            nblk = min(2048, cnt.value - 1)
+            comp = np.empty(offs[nblk], dtype=np.uint8)
+            ctx.d2h(comp.ctypes.data_as(ctypes.c_void_p), d_out, int(offs[nblk]))
+            zmod = ref[0] if ref is not None else zlib
+            t0 = time.perf_counter()
+            back_n = len(zmod.decompressobj(-15).decompress(comp.tobytes()))
+            extra["inflate_reference_1thread_GBps"] = back_n / (time.perf_counter() - t0) / 1e9
+            extra["inflate_reference_kind"] = "reference zlib_ng.decompressobj" if ref is not None else "stdlib zlib"
+        except Exception as e:  # report, never fake
+            extra["inflate_error"] = f"{type(e).__name__}: {e}"
         ms1 = min(device_pass(level=1)[0] for _ in range(3))
         extra["L1_mixed_GBps"] = n / ms1 / 1e6
         for name, fn, start in (("crc32", L.b2d_crc32_device, 0), ("adler32", L.b2d_adler32_device, 1)):

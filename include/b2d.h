@@ -113,9 +113,10 @@ int b2d_block_index(b2d_ctx *ctx, uint64_t *offsets, uint64_t cap, uint64_t *cou
 int b2d_inflate_device(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
                        uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
                        float *ms);
-/* the same with host buffers (H2D, kernels, D2H; not overlapped in this version) */
+/* the same with host buffers (H2D, kernels, D2H; callers overlap consecutive calls on two contexts).  `crc`
+ * (optional) is continued over the output: *crc = crc32(out[0, raw_n), *crc), computed on the device. */
 int b2d_inflate_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
-                     const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n);
+                     const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc);
 
 /* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
  * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit.

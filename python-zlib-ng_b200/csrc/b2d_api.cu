@@ -101,6 +101,7 @@ struct b2d_ctx {
     uint16_t *d_inf16; uint64_t inf16_cap;
     uint64_t *d_inf_index; uint64_t inf_index_cap;
     uint32_t *d_inf_err;
+    uint8_t *d_inf_in, *d_inf_out; uint64_t inf_in_cap, inf_out_cap;     /* device copies for b2d_inflate_host */
     /* optional per-stage timing of device-resident calls */
     int profiling;
     cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
@@ -116,7 +117,7 @@ static void ctx_free(b2d_ctx *c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) cudaStreamDestroy(c->stl[i]);
     cudaFree(c->d_total);
-    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err);
+    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out);
     for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
     for (int i = 0; i < B2D_NSLOT; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
@@ -798,28 +799,35 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
 }
 
 extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
-                                const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n) {
+                                const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
     if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
     if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
     if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
-    uint8_t *d_in = nullptr, *d_out = nullptr, *d_dict = nullptr;
     {
+        /* device copies of the stream (+ dictionary in front of it) and of the output: kept by the context, grown on demand */
         std::lock_guard<std::mutex> g(c->mu);
         CU(cudaSetDevice(c->device));
-        cudaError_t e = cudaMalloc(&d_in, in_n + 16);
-        if (e == cudaSuccess) e = cudaMalloc(&d_out, raw_n + 16);
-        if (e == cudaSuccess && dict_n) e = cudaMalloc(&d_dict, dict_n);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, in, in_n, cudaMemcpyHostToDevice, c->st);
-        if (e == cudaSuccess && dict_n) e = cudaMemcpyAsync(d_dict, dict, dict_n, cudaMemcpyHostToDevice, c->st);
-        if (e != cudaSuccess) { cudaFree(d_in); cudaFree(d_out); cudaFree(d_dict); cudaGetLastError(); return fail_cuda(e, "b2d_inflate_host: device buffers"); }
+        const uint64_t need_in = B2D_WINDOW + in_n + 64, need_out = raw_n + 64;
+        if (need_in > c->inf_in_cap) {
+            cudaFree(c->d_inf_in); c->d_inf_in = nullptr; c->inf_in_cap = 0;
+            if (cudaMalloc(&c->d_inf_in, need_in) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate input buffer does not fit"); }
+            c->inf_in_cap = need_in;
+        }
+        if (need_out > c->inf_out_cap) {
+            cudaFree(c->d_inf_out); c->d_inf_out = nullptr; c->inf_out_cap = 0;
+            if (cudaMalloc(&c->d_inf_out, need_out) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate output buffer does not fit"); }
+            c->inf_out_cap = need_out;
+        }
+        if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, c->st));
+        CU(cudaMemcpyAsync(c->d_inf_in + B2D_WINDOW, in, in_n, cudaMemcpyHostToDevice, c->st));
     }
-    int rc = b2d_inflate_device(c, d_in, in_n, block_offsets, nblocks, d_dict, dict_n, d_out, raw_n, nullptr);
-    {
-        std::lock_guard<std::mutex> g(c->mu);
-        cudaError_t e = cudaSuccess;
-        if (rc == B2D_OK) { e = cudaMemcpyAsync(out, d_out, raw_n, cudaMemcpyDeviceToHost, c->st); if (e == cudaSuccess) e = cudaStreamSynchronize(c->st); }
-        cudaFree(d_in); cudaFree(d_out); cudaFree(d_dict);
-        if (e != cudaSuccess) return fail_cuda(e, "b2d_inflate_host: copy back");
-    }
-    return rc;
+    int rc = b2d_inflate_device(c, c->d_inf_in + B2D_WINDOW, in_n, block_offsets, nblocks, dict_n ? c->d_inf_in : nullptr, dict_n,
+                                c->d_inf_out, raw_n, nullptr);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, c->st)); c->launches += crc_launches(c->d_inf_out, raw_n); }
+    CU(cudaMemcpyAsync(out, c->d_inf_out, raw_n, cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (crc) *crc = b2d_crc32_dev_finish(c->ck, raw_n, *crc);
+    return B2D_OK;
 }

@@ -57,7 +57,7 @@ SIGNATURES = {
     "b2d_block_index": (ctypes.c_int, [ctypes.c_void_p, _P(_u64), _u64, _P(_u64)]),
     "b2d_inflate_device": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64,
                                           _P(ctypes.c_float)]),
-    "b2d_inflate_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64]),
+    "b2d_inflate_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64, _P(_u32)]),
     "b2d_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "b2d_profile_read": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_double), _P(_u64), ctypes.c_int]),
 }

@@ -51,7 +51,7 @@ _INDEX_CHUNK = 16000                      # block sizes per index member (XLEN i
 _LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size, index offset, blocks
 _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
-_READ_WINDOW_BLOCKS = 1024                # device blocks (128 MiB of output) the reader decodes per GPU call
+_READ_WINDOW_BLOCKS = 2048                # device blocks (256 MiB of output) the reader decodes per GPU call
 
 
 def _extra_member(payload: bytes) -> bytes:
@@ -207,54 +207,101 @@ class _ThreadedGzipReader(io.RawIOBase):
             if here + 10 + sum(sizes) + 2 + 8 > index_off:
                 return None
             _native.default_context()      # no usable GPU: the CPU reader takes over (raises here)
-            return {"sizes": sizes, "raw_n": raw_n, "next": 0, "cpos": here + 10, "tail": b"", "buf": None, "off": 0,
-                    "crc": 0, "done": False, "end": end}
+            return {"sizes": sizes, "raw_n": raw_n, "cpos": here + 10}
         finally:
             if self._gpu is None:
                 raw.seek(here)
 
-    def _gpu_fill(self):
+    def _gpu_worker(self):
+        """Decodes window after window into pinned buffers, one window ahead of the consumer."""
         g = self._gpu
         sizes, nb_all = g["sizes"], len(g["sizes"])
-        if g["next"] >= nb_all:
-            if not g["done"]:
-                self.raw.seek(g["cpos"])
-                tail = self.raw.read(10)
-                crc, isize = struct.unpack("<II", tail[2:10]) if len(tail) == 10 else (None, None)
-                if tail[:2] != b"\x03\x00" or crc != g["crc"] or isize != (g["raw_n"] & 0xFFFFFFFF):
-                    raise _stdgzip.BadGzipFile("CRC check failed" if tail[:2] == b"\x03\x00" else "Bad stream end")
-                g["done"] = True
-            return False
-        first = g["next"]
-        nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
-        part = sizes[first:first + nb]
-        comp_n = sum(part)
-        self.raw.seek(g["cpos"])
-        comp = self.raw.read(comp_n)
-        if len(comp) != comp_n:
-            raise EOFError("Compressed file ended before the end-of-stream marker was reached")
-        raw_n = min(nb * _DEVICE_BLOCK, g["raw_n"] - first * _DEVICE_BLOCK)
-        offs = (ctypes.c_uint64 * nb)()
-        acc = 0
-        for i, sz in enumerate(part):
-            offs[i] = acc
-            acc += sz
-        out = bytearray(raw_n)
-        caddr, _, k1 = _native._addr(comp)
-        oaddr, _, k2 = _native._addr(out)
-        tail = g["tail"]
-        taddr, tn, k3 = _native._addr(tail) if tail else (None, 0, None)
         ctx = _native.default_context()
-        rc = _native.lib().b2d_inflate_host(ctx.handle, caddr, comp_n, offs, nb, taddr, tn, oaddr, raw_n)
-        del k1, k2, k3
-        if rc:
-            raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
-        g["crc"] = zlib_ng.crc32(out, g["crc"])
-        g["tail"] = bytes(out[-DEFLATE_WINDOW_SIZE:]) if raw_n >= DEFLATE_WINDOW_SIZE else (tail + bytes(out))[-DEFLATE_WINDOW_SIZE:]
-        g["buf"], g["off"] = out, 0
-        g["next"] = first + nb
-        g["cpos"] += comp_n
-        return True
+        L = _native.lib()
+        try:
+            comp_ptr, comp_view = g["comp"]
+            first, cpos, tail, crc = 0, g["cpos"], b"", ctypes.c_uint32(0)
+            while first < nb_all and not g["stop"]:
+                nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
+                part = sizes[first:first + nb]
+                comp_n = sum(part)
+                self.raw.seek(cpos)
+                got = self.raw.readinto(comp_view[:comp_n])
+                while got is not None and 0 < got < comp_n:      # raw streams may return short reads
+                    more = self.raw.readinto(comp_view[got:comp_n])
+                    if not more:
+                        break
+                    got += more
+                if got != comp_n:
+                    raise EOFError("Compressed file ended before the end-of-stream marker was reached")
+                raw_n = min(nb * _DEVICE_BLOCK, g["raw_n"] - first * _DEVICE_BLOCK)
+                offs = (ctypes.c_uint64 * nb)()
+                acc = 0
+                for i, sz in enumerate(part):
+                    offs[i] = acc
+                    acc += sz
+                out = None
+                while out is None:
+                    try:
+                        out = g["free"].get(timeout=0.05)
+                    except queue.Empty:
+                        if g["stop"]:
+                            return
+                out_ptr, out_view = out
+                rc = L.b2d_inflate_host(ctx.handle, comp_ptr, comp_n, offs, nb, tail if tail else None, len(tail),
+                                        out_ptr, raw_n, ctypes.byref(crc))
+                if rc:
+                    g["free"].put(out)
+                    raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
+                tail = (tail + bytes(out_view[max(raw_n - DEFLATE_WINDOW_SIZE, 0):raw_n]))[-DEFLATE_WINDOW_SIZE:]
+                g["ready"].put((out, raw_n))
+                first += nb
+                cpos += comp_n
+            if not g["stop"]:
+                self.raw.seek(cpos)
+                end = self.raw.read(10)
+                want_crc, isize = struct.unpack("<II", end[2:10]) if len(end) == 10 else (None, None)
+                if end[:2] != b"\x03\x00":
+                    raise _stdgzip.BadGzipFile("Bad stream end")
+                if want_crc != crc.value:
+                    raise _stdgzip.BadGzipFile(f"CRC check failed {hex(want_crc)} != {hex(crc.value)}")
+                if isize != (g["raw_n"] & 0xFFFFFFFF):
+                    raise _stdgzip.BadGzipFile("Incorrect length of data produced")
+            g["ready"].put(None)
+        except BaseException as e:       # surfaces in the reading thread
+            g["ready"].put(e)
+
+    def _gpu_start(self):
+        g = self._gpu
+        ctx = _native.default_context()
+        sizes = g["sizes"]
+
+        def bucket(n):       # few distinct sizes, so that the pinned pool can hand buffers to the next reader
+            if n <= 32 << 20:
+                return max(1 << (n - 1).bit_length(), 1 << 20)
+            return (n + (32 << 20) - 1) // (32 << 20) * (32 << 20)
+        win_raw = bucket(min(_READ_WINDOW_BLOCKS * _DEVICE_BLOCK, g["raw_n"]))
+        win_comp = bucket(max(sum(sizes[i:i + _READ_WINDOW_BLOCKS]) for i in range(0, len(sizes), _READ_WINDOW_BLOCKS)))
+        g["pinned"] = [(ctx, win_comp + 16) + _pinned_pool.get(ctx, win_comp + 16)]
+        g["comp"] = g["pinned"][0][2:]
+        g["free"], g["ready"], g["stop"] = queue.Queue(), queue.Queue(), False
+        for _ in range(2 if len(sizes) > _READ_WINDOW_BLOCKS else 1):
+            ent = (ctx, win_raw + 16) + _pinned_pool.get(ctx, win_raw + 16)
+            g["pinned"].append(ent)
+            g["free"].put(ent[2:])
+        g["cur"], g["cur_n"], g["off"], g["eof"] = None, 0, 0, False
+        g["thread"] = threading.Thread(target=self._gpu_worker, daemon=True)
+        g["thread"].start()
+
+    def _gpu_stop(self):
+        g = self._gpu
+        if not g or "thread" not in g:
+            return
+        g["stop"] = True
+        g["thread"].join()
+        for ctx, size, ptr, view in g["pinned"]:
+            _pinned_pool.put(ctx, size, ptr, view)
+        g["pinned"] = []
 
     def readinto(self, b):
         if self._closed:
@@ -264,13 +311,26 @@ class _ThreadedGzipReader(io.RawIOBase):
             self.pos += n
             return n
         g = self._gpu
-        if g["buf"] is None or g["off"] >= len(g["buf"]):
-            g["buf"] = None
-            if not self._gpu_fill():
+        if "thread" not in g:
+            self._gpu_start()
+        if g["cur"] is None or g["off"] >= g["cur_n"]:
+            if g["cur"] is not None:
+                g["free"].put(g["cur"])
+                g["cur"] = None
+            if g["eof"]:
                 return 0
+            item = g["ready"].get()
+            if item is None:
+                g["eof"] = True
+                return 0
+            if isinstance(item, BaseException):
+                g["eof"] = True
+                raise item
+            g["cur"], g["cur_n"] = item
+            g["off"] = 0
         mv = memoryview(b).cast("B")
-        n = min(len(mv), len(g["buf"]) - g["off"])
-        mv[:n] = memoryview(g["buf"])[g["off"]:g["off"] + n]
+        n = min(len(mv), g["cur_n"] - g["off"])
+        mv[:n] = g["cur"][1][g["off"]:g["off"] + n]
         g["off"] += n
         self.pos += n
         return n
@@ -286,6 +346,7 @@ class _ThreadedGzipReader(io.RawIOBase):
     def close(self) -> None:
         if self._closed:
             return
+        self._gpu_stop()
         if self.fileobj is not None:
             self.fileobj.close()
         if self.closefd:

@@ -120,15 +120,16 @@ def test_host_buffers_and_bad_index(nat, ctx):
     nb = len(offs) - 1
     arr = (ctypes.c_uint64 * nb)(*offs[:nb])
     out = ctypes.create_string_buffer(len(data))
-    nat.check(L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb, None, 0, out, len(data)))
-    assert out.raw == data
+    crc = ctypes.c_uint32(0)
+    nat.check(L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb, None, 0, out, len(data), ctypes.byref(crc)))
+    assert out.raw == data and crc.value == zlib.crc32(data)
     # an index that does not match the size, or points into the middle of a block, is refused / detected
-    assert L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb - 1, None, 0, out, len(data)) == nat.B2D_STREAM_ERROR
+    assert L.b2d_inflate_host(ctx.handle, stream, len(stream), arr, nb - 1, None, 0, out, len(data), None) == nat.B2D_STREAM_ERROR
     bad = (ctypes.c_uint64 * nb)(*([offs[0]] + [o + 3 for o in offs[1:nb]]))
-    rc = L.b2d_inflate_host(ctx.handle, stream, len(stream), bad, nb, None, 0, out, len(data))
+    rc = L.b2d_inflate_host(ctx.handle, stream, len(stream), bad, nb, None, 0, out, len(data), None)
     assert rc == -3 or out.raw != data
     # empty
-    nat.check(L.b2d_inflate_host(ctx.handle, None, 0, None, 0, None, 0, None, 0))
+    nat.check(L.b2d_inflate_host(ctx.handle, None, 0, None, 0, None, 0, None, 0, None))
 
 
 # ---- the user-facing side: gzip_ng_threaded.open(..., "rb") of files written by gzip_ng_threaded.open(..., "wb")

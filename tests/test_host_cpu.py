@@ -146,3 +146,21 @@ def test_twin_strategies(level):
     assert size["periodic", 3] > 20 * size["periodic", 0]    # ... but not a period of 8
     assert size["text", 1] != size["text", 0]                # filtered drops matches shorter than 6
     assert size["text", 4] >= size["text", 0]
+
+
+def test_index_members_are_ordinary_empty_gzip_members():
+    """The block index the threaded writer appends (gzip_ng_threaded._extra_member): empty members whose header has
+    an extra field, so every gzip reader skips them; the fixed-size locator parses back."""
+    import gzip
+    import struct
+    from zlib_ng_b200 import gzip_ng_threaded as gzt
+    sizes = list(range(1000, 1300))
+    idx = gzt._extra_member(struct.pack("<BBHI", 1, 0, 0, len(sizes)) + struct.pack(f"<{len(sizes)}I", *sizes))
+    loc = gzt._extra_member(gzt._LOCATOR.pack(gzt._LOCATOR_MAGIC, 1, 0, 12345, 777, len(sizes)))
+    assert len(loc) == gzt._LOCATOR_MEMBER
+    blob = gzip.compress(b"payload") + idx + loc
+    assert gzip.decompress(blob) == b"payload"
+    payload, nxt = gzt._parse_extra_member(idx + loc, 0)
+    assert struct.unpack_from(f"<{len(sizes)}I", payload, 8) == tuple(sizes) and nxt == len(idx)
+    assert gzt._LOCATOR.unpack(gzt._parse_extra_member(loc, 0)[0])[3] == 12345
+    assert gzt._parse_extra_member(gzip.compress(b"x"), 0) is None

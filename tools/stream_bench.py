@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--ref", action="store_true")
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--read", action="store_true", help="write the file once (this repo's writer), then time open(..., 'rb') reads")
     a = ap.parse_args()
     n = int(a.gib * (1 << 30))
     base = synthdata.make(a.kind, min(n, 256 << 20), 2)
@@ -52,6 +53,44 @@ def main():
     else:
         from zlib_ng_b200 import gzip_ng_threaded as gt
     step = a.write_mib << 20
+    if a.read:
+        import tempfile
+        from zlib_ng_b200 import gzip_ng_threaded as ours
+        d = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+        path = os.path.join(d, "b2d_stream_bench.gz")
+        with ours.open(path, "wb", compresslevel=a.level, threads=a.threads) as f:
+            for off in range(0, n, step):
+                f.write(mv[off:off + step])
+        print(f"file {os.path.getsize(path) / n:.4f} of the input; reader = {'reference' if a.ref else 'this repo'}", flush=True)
+        import zlib
+        want = zlib.crc32(mv)
+        try:
+            for r in range(a.reps):
+                t0 = time.perf_counter()
+                crc, got = 0, 0
+                with gt.open(path, "rb") as f:
+                    if r == a.reps - 1 and a.reps > 1:          # last rep: readinto a reused buffer (no fresh pages)
+                        box = bytearray(64 << 20)
+                        while True:
+                            k = f.readinto(box)
+                            if not k:
+                                break
+                            got += k
+                    else:
+                        while True:
+                            chunk = f.read(64 << 20)
+                            if not chunk:
+                                break
+                            got += len(chunk)
+                            if r == 0:
+                                crc = zlib.crc32(chunk, crc)
+                dt = time.perf_counter() - t0
+                print(f"read rep{r}: {n / dt / 1e9:.2f} GB/s  ({dt * 1e3:.0f} ms)  bytes ok {got == n}" +
+                      (f"  crc ok {crc == want} (checked inside the timed loop)" if r == 0 else "") +
+                      ("  [readinto]" if r == a.reps - 1 and a.reps > 1 else ""), flush=True)
+        finally:
+            os.unlink(path)
+        return
     for r in range(a.reps):
         sink = io.BytesIO() if a.verify else NullSink()
         t0 = time.perf_counter()
