@@ -214,56 +214,57 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
         inf_fill(T->d_tab, INF_D_BITS, T->d_count, T->d_sorted, lane);
         __syncwarp();
 
-        /* ---- symbols: lane 0 decodes, the warp copies */
+        /* ---- symbols: lane 0 decodes — literals straight to the output, as many as follow each other — and
+         * hands the next length/distance pair (or the end of the block) to the warp, which copies together */
         for (;;) {
-            uint32_t tok = 0;
+            uint32_t tok = 0, nlit = 0;
             if (lane == 0) {
-                br_refill(R);
-                uint32_t e = T->ll_tab[(uint32_t)R.buf & ((1u << INF_LL_BITS) - 1u)], len = e & 15u;
-                int sym = (int)(e >> 4);
-                if (!e) sym = inf_canon((uint32_t)R.buf & 0x7fffu, T->ll_count, T->ll_sorted, 15, &len);
-                if (sym < 0) tok = INF_TOK_ERR;
-                else {
+                uint16_t *lp = o16 + produced;
+                const uint32_t room = expect - produced;
+                for (;;) {
+                    br_refill(R);
+                    uint32_t e = T->ll_tab[(uint32_t)R.buf & ((1u << INF_LL_BITS) - 1u)], len = e & 15u;
+                    int sym = (int)(e >> 4);
+                    if (!e) sym = inf_canon((uint32_t)R.buf & 0x7fffu, T->ll_count, T->ll_sorted, 15, &len);
+                    if (sym < 0) { tok = INF_TOK_ERR; break; }
                     br_take(R, len);
-                    if (sym < 256) tok = (uint32_t)sym;
-                    else if (sym == 256) tok = INF_TOK_EOB;
-                    else if (sym > 285) tok = INF_TOK_ERR;
-                    else {
-                        const uint32_t ls = (uint32_t)sym - 257u;
-                        const uint32_t mlen = c_lbase[ls] + br_take(R, c_lext[ls]);
-                        br_refill(R);
-                        e = T->d_tab[(uint32_t)R.buf & ((1u << INF_D_BITS) - 1u)]; len = e & 15u;
-                        int ds = (int)(e >> 4);
-                        if (!e) ds = inf_canon((uint32_t)R.buf & 0x7fffu, T->d_count, T->d_sorted, 15, &len);
-                        if (ds < 0 || ds > 29) tok = INF_TOK_ERR;
-                        else {
-                            br_take(R, len);
-                            const uint32_t dist = c_dbase[ds] + br_take(R, c_dext[ds]);
-                            tok = 0x80000000u | (mlen << 16) | (dist - 1u);
-                        }
+                    if (sym < 256) {
+                        if (nlit >= room) { tok = INF_TOK_ERR; break; }
+                        lp[nlit++] = (uint16_t)sym;
+                        continue;
                     }
+                    if (sym == 256) { tok = INF_TOK_EOB; break; }
+                    if (sym > 285) { tok = INF_TOK_ERR; break; }
+                    const uint32_t ls = (uint32_t)sym - 257u;
+                    const uint32_t mlen = c_lbase[ls] + br_take(R, c_lext[ls]);
+                    br_refill(R);
+                    e = T->d_tab[(uint32_t)R.buf & ((1u << INF_D_BITS) - 1u)]; len = e & 15u;
+                    int ds = (int)(e >> 4);
+                    if (!e) ds = inf_canon((uint32_t)R.buf & 0x7fffu, T->d_count, T->d_sorted, 15, &len);
+                    if (ds < 0 || ds > 29) { tok = INF_TOK_ERR; break; }
+                    br_take(R, len);
+                    const uint32_t dist = c_dbase[ds] + br_take(R, c_dext[ds]);
+                    tok = 0x80000000u | (mlen << 16) | (dist - 1u);
+                    break;
                 }
             }
             tok = __shfl_sync(FULL, tok, 0);
+            nlit = __shfl_sync(FULL, nlit, 0);
+            produced += nlit;
             if (tok == INF_TOK_EOB) break;
             if (tok == INF_TOK_ERR) { fail = 3; break; }
-            if (!(tok >> 31)) {
-                if (produced >= expect) { fail = 2; break; }
-                if (lane == 0) o16[produced] = (uint16_t)tok;
-                produced += 1;
-            } else {
-                const uint32_t mlen = (tok >> 16) & 0x1ffu, dist = (tok & 0x7fffu) + 1u;
-                if (produced + mlen > expect || dist > produced + reach) { fail = 2; break; }
-                const int src0 = (int)produced - (int)dist;
-                for (uint32_t i = lane; i < mlen; i += 32) {
-                    const int rel = src0 + (int)(dist >= mlen ? i : i % dist);
-                    /* before the block: a marker for byte (32768 + rel) of the 32 KiB that precede it */
-                    const uint32_t v = rel < 0 ? 256u + (uint32_t)((int)B2D_WINDOW + rel) : (uint32_t)__ldcg(o16 + rel);
-                    o16[produced + i] = (uint16_t)v;
-                }
-                produced += mlen;
+            const uint32_t mlen = (tok >> 16) & 0x1ffu, dist = (tok & 0x7fffu) + 1u;
+            if (produced + mlen > expect || dist > produced + reach) { fail = 2; break; }
+            __syncwarp();    /* lane 0's literals and the previous copy are visible to this copy's loads */
+            const int src0 = (int)produced - (int)dist;
+            for (uint32_t i = lane; i < mlen; i += 32) {
+                const int rel = src0 + (int)(dist >= mlen ? i : i % dist);
+                /* before the block: a marker for byte (32768 + rel) of the 32 KiB that precede it */
+                const uint32_t v = rel < 0 ? 256u + (uint32_t)((int)B2D_WINDOW + rel) : (uint32_t)__ldcg(o16 + rel);
+                o16[produced + i] = (uint16_t)v;
             }
-            __syncwarp();    /* this symbol's stores are visible to the loads of the next copy */
+            produced += mlen;
+            __syncwarp();
         }
     }
     if (!fail && produced != expect) fail = 2;

@@ -1,2 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_inflate.py tests/test_gpu_api.py tests/test_gpu_pipeline.py -m gpu -x -q 2>&1 | tail -15 | tee gpurun_out/inf_pytest.log
+timeout 600 python -m pytest tests/test_gpu_inflate.py -m gpu -x -q 2>&1 | tail -3 | tee gpurun_out/inf_pytest.log
+timeout 300 python tools/probe.py --kind mixed --mib 256 --levels 6 --reps 2 --inflate 2>&1 | grep -E "inflate" | tee gpurun_out/inf_probe.log
+timeout 300 python tools/probe.py --kind mixed --mib 4096 --levels 6 --reps 2 --inflate 2>&1 | grep -E "inflate" | tee -a gpurun_out/inf_probe.log
