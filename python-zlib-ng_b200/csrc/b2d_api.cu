@@ -102,6 +102,8 @@ struct b2d_ctx {
     uint64_t *d_inf_index; uint64_t inf_index_cap;
     uint32_t *d_inf_err;
     uint8_t *d_inf_in, *d_inf_out; uint64_t inf_in_cap, inf_out_cap;     /* device copies for b2d_inflate_host */
+    uint32_t *d_inf_flags; uint64_t inf_flags_cap;                       /* one ready flag per block */
+    cudaStream_t st_inf; cudaEvent_t ev_inf_fork, ev_inf_join;           /* the serial pass runs beside the decode */
     /* optional per-stage timing of device-resident calls */
     int profiling;
     cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
@@ -117,7 +119,10 @@ static void ctx_free(b2d_ctx *c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) cudaStreamDestroy(c->stl[i]);
     cudaFree(c->d_total);
-    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out);
+    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out); cudaFree(c->d_inf_flags);
+    if (c->st_inf) cudaStreamDestroy(c->st_inf);
+    if (c->ev_inf_fork) cudaEventDestroy(c->ev_inf_fork);
+    if (c->ev_inf_join) cudaEventDestroy(c->ev_inf_join);
     for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
     for (int i = 0; i < B2D_NSLOT; ++i) {
         if (c->ev_in[i]) cudaEventDestroy(c->ev_in[i]);
@@ -779,11 +784,21 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         c->inf_index_cap = nblocks;
     }
     if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, sizeof(uint32_t)));
+    if (nblocks > c->inf_flags_cap) {
+        cudaFree(c->d_inf_flags); c->d_inf_flags = nullptr; c->inf_flags_cap = 0;
+        CU(cudaMalloc(&c->d_inf_flags, nblocks * sizeof(uint32_t)));
+        c->inf_flags_cap = nblocks;
+    }
+    if (!c->st_inf) {
+        CU(cudaStreamCreateWithFlags(&c->st_inf, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&c->ev_inf_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_inf_join, cudaEventDisableTiming));
+    }
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
     CU(cudaMemsetAsync(c->d_inf_err, 0, sizeof(uint32_t), c->st));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
-                          c->d_inf_err, c->st));
+                          c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join));
     c->launches += B2D_INF_LAUNCHES;
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
     uint32_t err = 0;
@@ -791,8 +806,9 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
     CU(cudaStreamSynchronize(c->st));
     if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
     if (err) {
-        static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code"};
-        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err >> 28) & 3], err & 0x0fffffffu);
+        static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code",
+                                    "decode did not arrive", "", "", ""};
+        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err >> 28) & 7], err & 0x0fffffffu);
         return -3;   /* Z_DATA_ERROR */
     }
     return B2D_OK;

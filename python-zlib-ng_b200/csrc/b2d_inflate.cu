@@ -14,7 +14,8 @@
  *                  0..255 = the byte, 256 + k = "byte k of the 32 KiB before this block" — copies move these
  *                  markers around like bytes, so a block never waits for its predecessor.
  *   k_inf_tails    one cluster of 8 CTAs walks the blocks in order and resolves the last 32 KiB of each (one
- *                  gather per marker from the predecessor's resolved tail): the only serial part.
+ *                  gather per marker from the predecessor's resolved tail): the only serial part.  It is launched
+ *                  first, on its own stream, and follows the decode through one ready flag per block.
  *   k_inf_finish   one CTA per block resolves the rest of the block against the now final tails.
  *
  * Reference code this stands in for: zng_inflate (zlib-ng/inflate.c:474-1150), inflate_table
@@ -122,7 +123,7 @@ __device__ __forceinline__ void inf_fill(uint16_t *tab, int tbits, const uint16_
 
 __global__ void __launch_bounds__(INF_WARPS * 32)
 k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__restrict__ index, uint32_t nblocks,
-             uint64_t raw_n, uint32_t dict_n, uint16_t *out16, uint32_t *err) {
+             uint64_t raw_n, uint32_t dict_n, uint16_t *out16, uint32_t *flags, uint32_t *err) {
     __shared__ inf_warp s_w[INF_WARPS];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t b = blockIdx.x * INF_WARPS + warp;
@@ -269,6 +270,9 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
     }
     if (!fail && produced != expect) fail = 2;
     if (fail && lane == 0) atomicCAS(err, 0u, (fail << 28) | (b & 0x0fffffffu));
+    /* the block's symbols are in memory: k_inf_tails (running beside this kernel) may pick its tail up */
+    __syncwarp();
+    if (lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = 1u; }
 }
 
 /* the byte a marker stands for: `k` indexes the 32 KiB that precede the block starting at output byte bs */
@@ -296,27 +300,52 @@ __device__ __forceinline__ uint2 inf_resolve8(uint4 q, const uint8_t *out8, cons
  * (release / acquire at cluster scope: block b's tail is final before block b+1 looks into it). */
 #define INF_CLUSTER 8
 #define INF_TAIL_THREADS (B2D_WINDOW / 8 / INF_CLUSTER)      /* 512 */
+#define INF_READY_GROUP 32u                                  /* decode flags are polled for this many blocks at a time */
 __global__ void __launch_bounds__(INF_TAIL_THREADS)
-k_inf_tails(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n,
-            uint32_t nblocks, uint64_t raw_n) {
+k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n, uint32_t nblocks,
+            uint64_t raw_n, const uint32_t *flags, uint32_t *err) {
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t t = blockIdx.x * INF_TAIL_THREADS + threadIdx.x;          /* 0 .. 4095: one group of 8 symbols */
     const uint32_t nfull = (uint32_t)(raw_n / B2D_BLOCK);          /* blocks of 128 KiB: their tails are aligned */
     const uint64_t toff = (B2D_BLOCK - B2D_WINDOW) + 8u * t;
+    /* This kernel starts before k_inf_decode and follows it block by block: blocks [first, last) must have been
+     * decoded before their symbols are read.  One thread per flag polls (bounded: a decode that never arrives
+     * is reported, not waited for). */
+    auto wait_ready = [&](uint32_t first, uint32_t last) {
+        bool ok = true;
+        if (threadIdx.x < last - first && *reinterpret_cast<volatile uint32_t *>(err) == 0u) {
+            const volatile uint32_t *f = flags + first + threadIdx.x;
+            uint32_t spins = 0;
+            while (*f == 0u) {
+                __nanosleep(1000);
+                if (++spins > 3000000u) { ok = false; break; }
+            }
+        }
+        if (!__syncthreads_and(ok) && threadIdx.x == 0) atomicCAS(err, 0u, (4u << 28) | (first & 0x0fffffffu));
+        __threadfence();
+    };
+    auto load = [&](uint32_t b) { return __ldcg(reinterpret_cast<const uint4 *>(out16 + (uint64_t)b * B2D_BLOCK + toff)); };
     uint4 cur = make_uint4(0, 0, 0, 0), nxt = cur;
-    if (nfull) cur = *reinterpret_cast<const uint4 *>(out16 + toff);
+    if (nfull) {
+        wait_ready(0, nfull < INF_READY_GROUP ? nfull : INF_READY_GROUP);
+        cur = load(0);
+    }
     for (uint32_t b = 0; b < nfull; ++b) {
         const uint64_t bs = (uint64_t)b * B2D_BLOCK;
-        if (b + 1 < nfull) nxt = *reinterpret_cast<const uint4 *>(out16 + bs + B2D_BLOCK + toff);
+        if (b + 1 < nfull) {
+            if ((b + 1) % INF_READY_GROUP == 0) wait_ready(b + 1, b + 1 + INF_READY_GROUP < nfull ? b + 1 + INF_READY_GROUP : nfull);
+            nxt = load(b + 1);
+        }
         *reinterpret_cast<uint2 *>(out8 + bs + toff) = inf_resolve8(cur, out8, dict, dict_n, bs);
         cluster.sync();
         cur = nxt;
     }
     if (nfull < nblocks) {   /* the last, shorter block: nobody depends on it */
+        wait_ready(nfull, nblocks);
         const uint64_t bs = (uint64_t)nfull * B2D_BLOCK;
         const uint64_t ts = raw_n - bs > B2D_WINDOW ? raw_n - B2D_WINDOW : bs;
         for (uint64_t p = ts + t; p < raw_n; p += INF_CLUSTER * INF_TAIL_THREADS) {
-            const uint32_t s = out16[p];
+            const uint32_t s = __ldcg(out16 + p);
             out8[p] = (uint8_t)(s < 256u ? s : inf_behind(out8, dict, dict_n, bs, s - 256u));
         }
     }
@@ -337,20 +366,36 @@ k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *_
 
 cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
                                const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
-                               uint64_t raw_n, uint32_t *d_err, cudaStream_t st) {
+                               uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st, cudaStream_t st_tails,
+                               cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     if (nblocks == 0) return cudaSuccess;
-    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
-                                                                                d_out16, d_err);
+    cudaError_t e;
+    {   /* With lazy module loading the first launch of a kernel loads it, which can wait for running kernels to end:
+         * k_inf_decode must be resident in the driver before k_inf_tails starts waiting for it. */
+        cudaFuncAttributes fa;
+        if ((e = cudaFuncGetAttributes(&fa, k_inf_decode)) != cudaSuccess) return e;
+        if ((e = cudaFuncGetAttributes(&fa, k_inf_tails)) != cudaSuccess) return e;
+        if ((e = cudaFuncGetAttributes(&fa, k_inf_finish)) != cudaSuccess) return e;
+    }
+    /* the serial pass over the tails goes first, on its own stream, and follows the decode through d_flags */
+    if ((e = cudaMemsetAsync(d_flags, 0, nblocks * sizeof(uint32_t), st)) != cudaSuccess) return e;
+    if ((e = cudaEventRecord(ev_fork, st)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(st_tails, ev_fork, 0)) != cudaSuccess) return e;
     {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st_tails;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = INF_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, k_inf_tails, (const uint16_t *)d_out16, d_out, d_dict, dict_n, nblocks, raw_n);
+        e = cudaLaunchKernelEx(&cfg, k_inf_tails, (const uint16_t *)d_out16, d_out, d_dict, dict_n, nblocks, raw_n,
+                               (const uint32_t *)d_flags, d_err);
         if (e != cudaSuccess) return e;
     }
+    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
+                                                                                d_out16, d_flags, d_err);
+    if ((e = cudaEventRecord(ev_join, st_tails)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(st, ev_join, 0)) != cudaSuccess) return e;
     k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
     return cudaGetLastError();
 }

@@ -7,8 +7,11 @@
 #define B2D_INF_LAUNCHES 3   /* k_inf_decode, k_inf_tails, k_inf_finish */
 
 /* d_index[b] = byte offset of device block b in the compressed stream; d_out16 = 2 * raw_n bytes of scratch;
- * *d_err (zeroed by the caller) receives (reason << 28) | block of the first block that failed to decode */
+ * d_flags = nblocks words of scratch; *d_err (zeroed by the caller) receives (reason << 28) | block of the first
+ * block that failed to decode.  st_tails / ev_fork / ev_join: a second stream and two events, so that the serial
+ * pass runs beside the decode. */
 cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
                                const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
-                               uint64_t raw_n, uint32_t *d_err, cudaStream_t st);
+                               uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st, cudaStream_t st_tails,
+                               cudaEvent_t ev_fork, cudaEvent_t ev_join);
 #endif
