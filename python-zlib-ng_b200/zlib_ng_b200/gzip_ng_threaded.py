@@ -212,34 +212,69 @@ class _ThreadedGzipReader(io.RawIOBase):
             if self._gpu is None:
                 raw.seek(here)
 
+    def _gpu_file_reader(self):
+        """Compressed bytes of window after window into pinned buffers (the file is only touched by this thread)."""
+        g = self._gpu
+        sizes, nb_all = g["sizes"], len(g["sizes"])
+        try:
+            first, cpos = 0, g["cpos"]
+            self.raw.seek(cpos)
+            while first < nb_all and not g["stop"]:
+                nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
+                comp_n = sum(sizes[first:first + nb])
+                comp = None
+                while comp is None:
+                    try:
+                        comp = g["comp_free"].get(timeout=0.05)
+                    except queue.Empty:
+                        if g["stop"]:
+                            return
+                view = comp[1]
+                got = 0
+                while got < comp_n:                               # raw streams may return short reads
+                    more = self.raw.readinto(view[got:comp_n])
+                    if not more:
+                        raise EOFError("Compressed file ended before the end-of-stream marker was reached")
+                    got += more
+                g["comp_ready"].put((comp, comp_n, first, nb))
+                first += nb
+            if not g["stop"]:
+                g["comp_ready"].put(self.raw.read(10))            # 03 00, CRC32, ISIZE
+        except BaseException as e:
+            g["comp_ready"].put(e)
+
     def _gpu_worker(self):
         """Decodes window after window into pinned buffers, one window ahead of the consumer."""
         g = self._gpu
-        sizes, nb_all = g["sizes"], len(g["sizes"])
+        sizes = g["sizes"]
         ctx = _native.default_context()
         L = _native.lib()
         try:
-            comp_ptr, comp_view = g["comp"]
-            first, cpos, tail, crc = 0, g["cpos"], b"", ctypes.c_uint32(0)
-            while first < nb_all and not g["stop"]:
-                nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
-                part = sizes[first:first + nb]
-                comp_n = sum(part)
-                self.raw.seek(cpos)
-                got = self.raw.readinto(comp_view[:comp_n])
-                while got is not None and 0 < got < comp_n:      # raw streams may return short reads
-                    more = self.raw.readinto(comp_view[got:comp_n])
-                    if not more:
-                        break
-                    got += more
-                if got != comp_n:
-                    raise EOFError("Compressed file ended before the end-of-stream marker was reached")
+            tail, crc = b"", ctypes.c_uint32(0)
+            while not g["stop"]:
+                try:
+                    item = g["comp_ready"].get(timeout=0.05)
+                except queue.Empty:
+                    continue
+                if isinstance(item, BaseException):
+                    raise item
+                if isinstance(item, bytes):                       # the member's end
+                    want_crc, isize = struct.unpack("<II", item[2:10]) if len(item) == 10 else (None, None)
+                    if item[:2] != b"\x03\x00":
+                        raise _stdgzip.BadGzipFile("Bad stream end")
+                    if want_crc != crc.value:
+                        raise _stdgzip.BadGzipFile(f"CRC check failed {hex(want_crc)} != {hex(crc.value)}")
+                    if isize != (g["raw_n"] & 0xFFFFFFFF):
+                        raise _stdgzip.BadGzipFile("Incorrect length of data produced")
+                    g["ready"].put(None)
+                    return
+                comp, comp_n, first, nb = item
                 raw_n = min(nb * _DEVICE_BLOCK, g["raw_n"] - first * _DEVICE_BLOCK)
                 offs = (ctypes.c_uint64 * nb)()
                 acc = 0
-                for i, sz in enumerate(part):
+                for i in range(nb):
                     offs[i] = acc
-                    acc += sz
+                    acc += sizes[first + i]
                 out = None
                 while out is None:
                     try:
@@ -248,26 +283,14 @@ class _ThreadedGzipReader(io.RawIOBase):
                         if g["stop"]:
                             return
                 out_ptr, out_view = out
-                rc = L.b2d_inflate_host(ctx.handle, comp_ptr, comp_n, offs, nb, tail if tail else None, len(tail),
+                rc = L.b2d_inflate_host(ctx.handle, comp[0], comp_n, offs, nb, tail if tail else None, len(tail),
                                         out_ptr, raw_n, ctypes.byref(crc))
+                g["comp_free"].put(comp)
                 if rc:
                     g["free"].put(out)
                     raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
                 tail = (tail + bytes(out_view[max(raw_n - DEFLATE_WINDOW_SIZE, 0):raw_n]))[-DEFLATE_WINDOW_SIZE:]
                 g["ready"].put((out, raw_n))
-                first += nb
-                cpos += comp_n
-            if not g["stop"]:
-                self.raw.seek(cpos)
-                end = self.raw.read(10)
-                want_crc, isize = struct.unpack("<II", end[2:10]) if len(end) == 10 else (None, None)
-                if end[:2] != b"\x03\x00":
-                    raise _stdgzip.BadGzipFile("Bad stream end")
-                if want_crc != crc.value:
-                    raise _stdgzip.BadGzipFile(f"CRC check failed {hex(want_crc)} != {hex(crc.value)}")
-                if isize != (g["raw_n"] & 0xFFFFFFFF):
-                    raise _stdgzip.BadGzipFile("Incorrect length of data produced")
-            g["ready"].put(None)
         except BaseException as e:       # surfaces in the reading thread
             g["ready"].put(e)
 
@@ -282,23 +305,29 @@ class _ThreadedGzipReader(io.RawIOBase):
             return (n + (32 << 20) - 1) // (32 << 20) * (32 << 20)
         win_raw = bucket(min(_READ_WINDOW_BLOCKS * _DEVICE_BLOCK, g["raw_n"]))
         win_comp = bucket(max(sum(sizes[i:i + _READ_WINDOW_BLOCKS]) for i in range(0, len(sizes), _READ_WINDOW_BLOCKS)))
-        g["pinned"] = [(ctx, win_comp + 16) + _pinned_pool.get(ctx, win_comp + 16)]
-        g["comp"] = g["pinned"][0][2:]
-        g["free"], g["ready"], g["stop"] = queue.Queue(), queue.Queue(), False
-        for _ in range(2 if len(sizes) > _READ_WINDOW_BLOCKS else 1):
+        several = len(sizes) > _READ_WINDOW_BLOCKS
+        g["pinned"] = []
+        g["free"], g["ready"], g["comp_free"], g["comp_ready"], g["stop"] = queue.Queue(), queue.Queue(), queue.Queue(), queue.Queue(), False
+        for _ in range(2 if several else 1):
+            ent = (ctx, win_comp + 16) + _pinned_pool.get(ctx, win_comp + 16)
+            g["pinned"].append(ent)
+            g["comp_free"].put(ent[2:])
             ent = (ctx, win_raw + 16) + _pinned_pool.get(ctx, win_raw + 16)
             g["pinned"].append(ent)
             g["free"].put(ent[2:])
         g["cur"], g["cur_n"], g["off"], g["eof"] = None, 0, 0, False
-        g["thread"] = threading.Thread(target=self._gpu_worker, daemon=True)
-        g["thread"].start()
+        g["threads"] = [threading.Thread(target=self._gpu_file_reader, daemon=True),
+                        threading.Thread(target=self._gpu_worker, daemon=True)]
+        for t in g["threads"]:
+            t.start()
 
     def _gpu_stop(self):
         g = self._gpu
-        if not g or "thread" not in g:
+        if not g or "threads" not in g:
             return
         g["stop"] = True
-        g["thread"].join()
+        for t in g["threads"]:
+            t.join()
         for ctx, size, ptr, view in g["pinned"]:
             _pinned_pool.put(ctx, size, ptr, view)
         g["pinned"] = []
@@ -311,7 +340,7 @@ class _ThreadedGzipReader(io.RawIOBase):
             self.pos += n
             return n
         g = self._gpu
-        if "thread" not in g:
+        if "threads" not in g:
             self._gpu_start()
         if g["cur"] is None or g["off"] >= g["cur_n"]:
             if g["cur"] is not None:
