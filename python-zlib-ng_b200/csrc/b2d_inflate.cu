@@ -26,6 +26,7 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "b2d_common.h"
 #include "b2d_inflate.h"
@@ -377,8 +378,15 @@ cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_
         if ((e = cudaFuncGetAttributes(&fa, k_inf_tails)) != cudaSuccess) return e;
         if ((e = cudaFuncGetAttributes(&fa, k_inf_finish)) != cudaSuccess) return e;
     }
-    /* the serial pass over the tails goes first, on its own stream, and follows the decode through d_flags */
     if ((e = cudaMemsetAsync(d_flags, 0, nblocks * sizeof(uint32_t), st)) != cudaSuccess) return e;
+    /* B2D_INF_SERIAL=1: one stream, decode before the tails (profilers serialise kernels: the concurrent form
+     * would have the tails pass wait for a decode that cannot start) */
+    static const bool serial = getenv("B2D_INF_SERIAL") && getenv("B2D_INF_SERIAL")[0] == '1';
+    if (serial) st_tails = st;
+    if (serial)
+        k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
+                                                                                    d_out16, d_flags, d_err);
+    /* otherwise the serial pass over the tails goes first, on its own stream, and follows the decode through d_flags */
     if ((e = cudaEventRecord(ev_fork, st)) != cudaSuccess) return e;
     if ((e = cudaStreamWaitEvent(st_tails, ev_fork, 0)) != cudaSuccess) return e;
     {
@@ -392,8 +400,9 @@ cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_
                                (const uint32_t *)d_flags, d_err);
         if (e != cudaSuccess) return e;
     }
-    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
-                                                                                d_out16, d_flags, d_err);
+    if (!serial)
+        k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
+                                                                                    d_out16, d_flags, d_err);
     if ((e = cudaEventRecord(ev_join, st_tails)) != cudaSuccess) return e;
     if ((e = cudaStreamWaitEvent(st, ev_join, 0)) != cudaSuccess) return e;
     k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
