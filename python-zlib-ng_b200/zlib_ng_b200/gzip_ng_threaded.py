@@ -33,7 +33,7 @@ DEFLATE_WINDOW_SIZE = 2 ** 15
 _COMPRESS_LEVEL_TRADEOFF = 6
 _MIN_BATCH = 128 * 1024
 # What one GPU call covers.  The reference keeps threads * block_size bytes in flight; a GPU wants more
-# per launch, so batches grow to this size unless the caller asked for blocks below 1 MiB in total
+# per launch, so batches grow to this size unless the caller asked for less than one 128 KiB device block in total
 # (then the reference's sizes, and its OverflowError on oversized blocks, are kept as they are).
 _STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
 # workers (each with its own GPU context and stream) per device: batch j+1's H2D and batch j-1's D2H
@@ -436,7 +436,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
         nw = len(self._contexts)
         # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece
         nominal = max(block_size * threads // nw, 1)
-        self.batch = nominal if block_size * threads < (1 << 20) else max(nominal, _STREAM_BATCH)
+        self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, _STREAM_BATCH)
         self._out_cap = self.batch + max(self.batch // 10, 500)
         self.input_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)]
         self.output_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)] if nw > 1 else []
