@@ -319,7 +319,7 @@ k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ di
             uint32_t spins = 0;
             while (*f == 0u) {
                 __nanosleep(1000);
-                if (++spins > 3000000u) { ok = false; break; }
+                if (++spins > 20000000u) { ok = false; break; }   /* ~20 s: a hang guard, not a deadline */
             }
         }
         if (!__syncthreads_and(ok) && threadIdx.x == 0) atomicCAS(err, 0u, (4u << 28) | (first & 0x0fffffffu));
