@@ -190,3 +190,20 @@ def test_reader_without_index_and_small_files(gzt, tmp_path):
         pass
     with gzt.open(tmp_path / "e.gz", "rb") as f:
         assert f.read() == b""
+
+
+@pytest.mark.timeout(60)
+def test_reader_can_be_closed_early(gzt, tmp_path, monkeypatch):
+    import threading
+    data = synthdata.make("fastq", 6_000_000, 33).tobytes()
+    path = tmp_path / "early.gz"
+    with gzt.open(path, "wb", threads=2) as f:
+        f.write(data)
+    monkeypatch.setattr(gzt, "_READ_WINDOW_BLOCKS", 4)
+    before = threading.active_count()
+    f = gzt.open(path, "rb")
+    assert f.read(1000) == data[:1000]
+    f.close()                                   # the decoder threads are one window ahead: they must stop, not hang
+    assert f.closed and threading.active_count() <= before
+    with gzt.open(path, "rb") as f:             # and the pooled buffers serve the next reader
+        assert f.read() == data
