@@ -295,6 +295,79 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
     }
 }
 
+/* K2 at depth 1 (level 1, Z_RLE): a position has one candidate, so nothing walks the links and they need not be staged —
+ * each thread reads its own link from global memory (coalesced).  Only the input window sits in shared memory
+ * (65 KiB instead of 197), three CTAs share an SM and one tile's loads overlap the other's compares.  Same results as
+ * k_match with depth == 1. */
+#define K2D1_THREADS 512
+__global__ void __launch_bounds__(K2D1_THREADS, 3)
+k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
+           const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, uint32_t max_dist, int rle) {
+    extern __shared__ __align__(16) uint8_t smem2[];
+    uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
+    const uint32_t tid = threadIdx.x;
+    const uint64_t k = blockIdx.x;
+    const uint64_t job_end = D + n;
+    const uint64_t tile_start = D + k * (uint64_t)B2D_SUB;
+    const uint64_t tile_end = tile_start + B2D_SUB < job_end ? tile_start + B2D_SUB : job_end;
+    const uint64_t ws = tile_start >= B2D_WINDOW ? tile_start - B2D_WINDOW : 0;
+    const uint64_t ws_al = ws & ~(uint64_t)15;
+    const uint64_t rd_lim = buf_readable & ~(uint64_t)15;
+    {
+        uint4 *d4 = reinterpret_cast<uint4 *>(s_in);
+        const uint32_t n16 = (uint32_t)((tile_end + 272 - ws_al + 15) >> 4);
+        for (uint32_t i = tid; i < n16; i += K2D1_THREADS) {
+            uint64_t off = ws_al + 16ull * i;
+            d4[i] = (off + 16 <= rd_lim) ? __ldg(reinterpret_cast<const uint4 *>(buf + off)) : make_uint4(0, 0, 0, 0);
+        }
+    }
+    /* links of this tile's block: entry 0 = position (span_start & ~7) */
+    const uint64_t blk = k / B2D_NSUB;
+    const uint64_t bstart = D + blk * (uint64_t)B2D_BLOCK;
+    const uint64_t span_al = (bstart - (bstart < B2D_WINDOW ? bstart : B2D_WINDOW)) & ~(uint64_t)7;
+    const uint16_t *links = prevd + blk * (uint64_t)B2D_LINKS + (tile_start - span_al);
+    __syncthreads();
+    const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
+    const uint32_t tile_off = (uint32_t)(tile_start - ws_al);
+    uint32_t *mout = match + (tile_start - D);
+    for (uint32_t t = tid; t < tile_len; t += K2D1_THREADS) {
+        const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
+        uint32_t maxl = to_unit < to_end ? to_unit : to_end;
+        if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
+        const uint32_t pr = tile_off + t;
+        const uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : (uint32_t)__ldg(links + t);
+        uint32_t l = 0;
+        if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
+            const uint32_t wi = pr >> 2, osh = (pr & 3u) << 3;
+            const uint32_t cand = pr - dist;
+            uint32_t cw = cand >> 2;
+            const uint32_t csh = (cand & 3u) << 3;
+            const uint32_t o0 = s_in[wi], o1 = s_in[wi + 1], o2 = s_in[wi + 2];
+            const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
+            const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ __funnelshift_r(o0, o1, osh);
+            const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ __funnelshift_r(o1, o2, osh);
+            uint32_t x = x0 ? x0 : x1;
+            l = x0 ? 0u : 4u;
+            if ((x0 | x1) == 0u) {
+                /* longer than 8: 8 bytes per trip, each aligned word of either side loaded once */
+                l = 8;
+                cw += 2;
+                uint32_t ow = wi + 2u, cp = a2, op = o2;
+                while (l < maxl) {
+                    const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], p1 = s_in[ow + 1], p2 = s_in[ow + 2];
+                    if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, p1, osh)) != 0) break;
+                    l += 4;
+                    if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, osh)) != 0) break;
+                    l += 4; cw += 2; ow += 2; cp = c2; op = p2;
+                }
+            }
+            if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
+            if (l > maxl) l = maxl;
+        }
+        mout[t] = l >= B2D_MIN_MATCH ? b2d_pack_match(l, dist) : 0u;
+    }
+}
+
 /* ------------------------------------------------------------------------- */
 /* K3: parse + token compaction + histograms                                  */
 /* ------------------------------------------------------------------------- */
@@ -918,6 +991,8 @@ static size_t k2_smem() { return K2_IN_BYTES + 2u * (B2D_WINDOW + B2D_SUB) + 32u
 cudaError_t b2d_kernels_init(void) {
     cudaError_t e = cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_match_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
+    if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k4_smem());
     if (e != cudaSuccess) return e;
     return cudaSuccess;   /* k_chains needs at most 33 KiB: below the default dynamic limit */
@@ -944,8 +1019,12 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     }
     MARK(1);
     if (pol.search != B2D_SEARCH_NONE) {
-        k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
-                                                    pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
+        if (pol.depth == 1)
+            k_match_d1<<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist,
+                                                              pol.search == B2D_SEARCH_RLE);
+        else
+            k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
+                                                        pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
         if (e != cudaSuccess) return e;
