@@ -147,7 +147,11 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
 /* K2: all-position match search                                              */
 /* ------------------------------------------------------------------------- */
 #define K2_THREADS 1024
-#define K2_IN_BYTES (B2D_WINDOW + B2D_SUB + 16u + 288u)   /* +16 align slack, +258+pad look-ahead */
+#ifndef K2_TILE
+#define K2_TILE B2D_SUB     /* positions per k_match CTA (a divisor of B2D_BLOCK, a multiple of B2D_UNIT) */
+#endif
+#define K2_IN_BYTES (B2D_WINDOW + B2D_SUB + 16u + 288u)   /* +16 align slack, +258+pad look-ahead (k_match_d1: whole sub-blocks) */
+#define K2_IN_BYTES_T (B2D_WINDOW + K2_TILE + 16u + 288u)  /* k_match */
 
 __device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off) {
     const uint32_t wi = byte_off >> 2;
@@ -240,12 +244,12 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         uint32_t max_dist, int rle) {
     extern __shared__ __align__(16) uint8_t smem2[];
     uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
-    uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES);       /* 2*(W+SUB)+16 */
+    uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES_T);       /* 2*(W+SUB)+16 */
     const uint32_t tid = threadIdx.x;
     const uint64_t k = blockIdx.x;
     const uint64_t job_end = D + n;
-    const uint64_t tile_start = D + k * (uint64_t)B2D_SUB;
-    const uint64_t tile_end = tile_start + B2D_SUB < job_end ? tile_start + B2D_SUB : job_end;
+    const uint64_t tile_start = D + k * (uint64_t)K2_TILE;
+    const uint64_t tile_end = tile_start + K2_TILE < job_end ? tile_start + K2_TILE : job_end;
     const uint64_t ws = tile_start >= B2D_WINDOW ? tile_start - B2D_WINDOW : 0;
     const uint64_t ws_al = ws & ~(uint64_t)15;           /* smem byte 0 of s_in   */
     const uint64_t wp_al = ws & ~(uint64_t)7;            /* element 0 of s_prev   */
@@ -261,7 +265,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         uint4 *p4 = reinterpret_cast<uint4 *>(s_prev);
         const uint32_t np = (uint32_t)((tile_end - wp_al + 7) >> 3);
         /* links of this tile's block, entry 0 = position (span_start & ~7) */
-        const uint64_t blk = k / B2D_NSUB;
+        const uint64_t blk = k / (B2D_BLOCK / K2_TILE);
         const uint64_t bstart = D + blk * (uint64_t)B2D_BLOCK;
         const uint64_t span_al = (bstart - (bstart < B2D_WINDOW ? bstart : B2D_WINDOW)) & ~(uint64_t)7;
         const uint4 *src = reinterpret_cast<const uint4 *>(prevd + blk * (uint64_t)B2D_LINKS + (wp_al - span_al));
@@ -986,7 +990,7 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 /* ------------------------------------------------------------------------- */
 static size_t k1_smem(int hb) { return (2u << hb) + 2u * K1_BATCH; }
 static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
-static size_t k2_smem() { return K2_IN_BYTES + 2u * (B2D_WINDOW + B2D_SUB) + 32u; }
+static size_t k2_smem() { return K2_IN_BYTES_T + 2u * (B2D_WINDOW + K2_TILE) + 32u; }
 
 cudaError_t b2d_kernels_init(void) {
     cudaError_t e = cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
@@ -1023,7 +1027,7 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
             k_match_d1<<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist,
                                                               pol.search == B2D_SEARCH_RLE);
         else
-            k_match<<<nsub, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
+            k_match<<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
                                                         pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
