@@ -164,3 +164,17 @@ def test_index_members_are_ordinary_empty_gzip_members():
     assert struct.unpack_from(f"<{len(sizes)}I", payload, 8) == tuple(sizes) and nxt == len(idx)
     assert gzt._LOCATOR.unpack(gzt._parse_extra_member(loc, 0)[0])[3] == 12345
     assert gzt._parse_extra_member(gzip.compress(b"x"), 0) is None
+
+
+def test_host_copy_needs_no_device():
+    """b2d_host_copy is plain host code (the writer's copy into its pinned batch): any thread count, any size."""
+    import ctypes
+    import numpy as np
+    from zlib_ng_b200 import _native
+    L = _native.lib()
+    rng = np.random.default_rng(1)
+    for n, threads in ((0, 4), (1, 1), (4097, 8), (9 << 20, 3), (33 << 20, 8), (17 << 20, 64)):
+        src = rng.integers(0, 256, n, dtype=np.uint8)
+        dst = np.zeros(n + 8, dtype=np.uint8)
+        assert L.b2d_host_copy(dst.ctypes.data_as(ctypes.c_void_p), src.ctypes.data_as(ctypes.c_void_p), n, threads) == 0
+        assert (dst[:n] == src).all() and not dst[n:].any()
