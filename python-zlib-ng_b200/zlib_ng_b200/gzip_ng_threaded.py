@@ -364,6 +364,32 @@ class _ThreadedGzipReader(io.RawIOBase):
         self.pos += n
         return n
 
+    def readall(self):
+        """read() without a size: RawIOBase would collect 8 KiB pieces; the size is known here, so the windows are
+        copied straight into one (uninitialised) bytes object."""
+        if self._closed:
+            raise ValueError("I/O operation on closed file")
+        if self._gpu is None:
+            data = self.fileobj.read()
+            self.pos += len(data)
+            return data
+        left = self._gpu["raw_n"] - self.pos
+        if left <= 0:
+            self.readinto(bytearray(1))      # runs the end-of-member checks
+            return b""
+        out = zlib_ng._OutBytes(left)
+        view = memoryview((ctypes.c_char * left).from_address(out.addr)).cast("B")
+        got = 0
+        while got < left:
+            k = self.readinto(view[got:])
+            if not k:
+                break
+            got += k
+        if got == left:
+            self.readinto(bytearray(1))
+        view.release()
+        return out.finish(got)
+
     def readable(self) -> bool:
         return True
 
