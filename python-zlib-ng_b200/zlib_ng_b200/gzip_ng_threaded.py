@@ -51,7 +51,7 @@ _INDEX_CHUNK = 16000                      # block sizes per index member (XLEN i
 _LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size, index offset, blocks
 _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
-_READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "256")), 1) * 8    # device blocks the reader decodes per GPU call
+_READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "512")), 1) * 8    # device blocks the reader decodes per GPU call
 
 
 def _extra_member(payload: bytes) -> bytes:
