@@ -105,6 +105,11 @@ int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads);
  * in its compressed output: *count = blocks + 1 entries (the last one is the stream length), copied to
  * `offsets` when it is not NULL (B2D_BUF_ERROR if cap < *count).  Blocks start byte-aligned. */
 int b2d_block_index(b2d_ctx *ctx, uint64_t *offsets, uint64_t cap, uint64_t *count);
+/* b2d_compress_and_crc and b2d_block_index in one call: nothing else runs on the context between the two, so
+ * writers that share a context (several files open in one process) get their own block's index */
+int b2d_compress_and_crc_indexed(b2d_ctx *ctx, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                 uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                 uint64_t *offsets, uint64_t cap, uint64_t *count);
 /* Inflate `raw_n` bytes from the raw-DEFLATE stream d_in[0, in_n) given block_offsets[0, nblocks) (a host
  * array; nblocks = ceil(raw_n / 128 KiB)) and the dictionary the stream was primed with (device pointer, at
  * most 32 KiB, may be NULL/0).  Every block is decoded by its own warp; references into the preceding 32 KiB

@@ -74,7 +74,7 @@ struct b2d_ctx {
     uint64_t max_batch;
     cudaStream_t st;
     cudaEvent_t ev0, ev1;
-    std::mutex mu;
+    std::recursive_mutex mu;       /* recursive: the compound entry points (compress + index, host inflate) hold it across their parts */
     /* work buffers for one batch */
     uint8_t *d_in;  uint64_t d_in_cap;      /* WINDOW + max_batch + pad (host-buffer calls)   */
     uint8_t *d_out; uint64_t d_out_cap;     /* bound(max_batch) rounded (host-buffer calls)   */
@@ -210,7 +210,7 @@ static uint32_t crc_launches(const uint8_t *d, uint64_t n) {
 
 extern "C" int b2d_crc32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, uint64_t n, uint32_t *out, float *ms) {
     if (!c || !out) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(b2d_crc32_dev(c->ck, d, n, start, out, c->st));
@@ -220,7 +220,7 @@ extern "C" int b2d_crc32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, ui
 }
 extern "C" int b2d_adler32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, uint64_t n, uint32_t *out, float *ms) {
     if (!c || !out) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(b2d_adler32_dev(c->ck, d, n, start, out, c->st));
@@ -259,7 +259,7 @@ static int for_each_staged(b2d_ctx *c, const uint8_t *data, uint64_t n, F fn) {
 
 extern "C" int b2d_crc32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out) {
     if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (n > c->max_batch) return checksum_host_pipelined(c, data, n, start, false, out);
     uint32_t crc = start;
@@ -274,7 +274,7 @@ extern "C" int b2d_crc32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64
 }
 extern "C" int b2d_adler32(b2d_ctx *c, uint32_t start, const uint8_t *data, uint64_t n, uint32_t *out) {
     if (!c || !out || (!data && n)) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (n > c->max_batch) return checksum_host_pipelined(c, data, n, start, true, out);
     uint32_t a = start;
@@ -335,7 +335,7 @@ static int prof_drain(b2d_ctx *c, int nb, int level) {
 
 extern "C" int b2d_profile(b2d_ctx *c, int enable) {
     if (!c) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (enable && !c->pev[0][0])
         for (int i = 0; i < PROF_BATCHES; ++i) for (int j = 0; j <= B2D_NSTAGE; ++j) CU(cudaEventCreate(&c->pev[i][j]));
@@ -344,7 +344,7 @@ extern "C" int b2d_profile(b2d_ctx *c, int enable) {
 }
 extern "C" int b2d_profile_read(b2d_ctx *c, double *stage_ms, uint64_t *stage_launches, int reset) {
     if (!c) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     for (int j = 0; j < B2D_NSTAGE; ++j) {
         if (stage_ms) stage_ms[j] = c->stage_ms[j];
         if (stage_launches) stage_launches[j] = c->stage_launches[j];
@@ -374,7 +374,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     if (dict_n > B2D_WINDOW) return fail(B2D_STREAM_ERROR, "device dictionary longer than 32768 bytes");
     if (((uintptr_t)d_buf & 15) || ((uintptr_t)d_out & 3)) return fail(B2D_STREAM_ERROR, "misaligned device pointer");
     if (out_cap < b2d_deflate_bound(n)) return fail(B2D_BUF_ERROR, "out_cap below b2d_deflate_bound(n)");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(cudaMemsetAsync(d_out, 0, align_up(b2d_deflate_bound(n), 4) <= out_cap ? align_up(b2d_deflate_bound(n), 4) : out_cap, c->st));
@@ -640,7 +640,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
     if (!b2d_level_valid(level)) return fail(B2D_STREAM_ERROR, "Bad compression level");
     if (window_bits < 9 || window_bits > 15) return fail(B2D_STREAM_ERROR, "window_bits outside 9..15");
     const uint32_t max_dist = 1u << window_bits;
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (dict_n > max_dist) { dict += dict_n - max_dist; dict_n = max_dist; }
     if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
@@ -736,12 +736,22 @@ extern "C" int b2d_compress_and_crc(b2d_ctx *c, int level, const uint8_t *data, 
 }
 
 
+extern "C" int b2d_compress_and_crc_indexed(b2d_ctx *c, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                            uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                            uint64_t *offsets, uint64_t cap, uint64_t *count) {
+    if (!c || !count) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::recursive_mutex> g(c->mu);       /* no other call on this context between the two parts */
+    int rc = b2d_compress_and_crc(c, level, data, n, dict, dict_n, out, out_cap, out_n, crc);
+    if (rc) return rc;
+    return b2d_block_index(c, offsets, cap, count);
+}
+
 /* ------------------------------------------------------------------------- */
 /* inflate side (first version): streams of this library + their block index */
 /* ------------------------------------------------------------------------- */
 extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint64_t *count) {
     if (!c || !count) return fail(B2D_STREAM_ERROR, "null argument");
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     *count = c->index_n;
     if (!offsets || c->index_n == 0) return B2D_OK;
     if (cap < c->index_n) return fail(B2D_BUF_ERROR, "b2d_block_index: capacity below the number of entries");
@@ -770,7 +780,7 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
             return fail(B2D_STREAM_ERROR, "bad block index");
     if (ms) *ms = 0.f;
     if (raw_n == 0) return B2D_OK;
-    std::lock_guard<std::mutex> g(c->mu);
+    std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
     if (raw_n > c->inf16_cap) {
         cudaFree(c->d_inf16); c->d_inf16 = nullptr; c->inf16_cap = 0;
@@ -819,9 +829,9 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
     if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
     if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
     if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
+    std::lock_guard<std::recursive_mutex> whole(c->mu);      /* the device copies below belong to this call until it returns */
     {
         /* device copies of the stream (+ dictionary in front of it) and of the output: kept by the context, grown on demand */
-        std::lock_guard<std::mutex> g(c->mu);
         CU(cudaSetDevice(c->device));
         const uint64_t need_in = B2D_WINDOW + in_n + 64, need_out = raw_n + 64;
         if (need_in > c->inf_in_cap) {
@@ -840,7 +850,6 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
     int rc = b2d_inflate_device(c, c->d_inf_in + B2D_WINDOW, in_n, block_offsets, nblocks, dict_n ? c->d_inf_in : nullptr, dict_n,
                                 c->d_inf_out, raw_n, nullptr);
     if (rc) return rc;
-    std::lock_guard<std::mutex> g(c->mu);
     if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, c->st)); c->launches += crc_launches(c->d_inf_out, raw_n); }
     CU(cudaMemcpyAsync(out, c->d_inf_out, raw_n, cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));

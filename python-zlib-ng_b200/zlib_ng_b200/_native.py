@@ -55,6 +55,8 @@ SIGNATURES = {
     "b2d_host_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, _u64, ctypes.c_int]),
     "b2d_launch_count": (_u64, [ctypes.c_void_p]),
     "b2d_block_index": (ctypes.c_int, [ctypes.c_void_p, _P(_u64), _u64, _P(_u64)]),
+    "b2d_compress_and_crc_indexed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
+                                                    _P(_u64), _P(_u32), _P(_u64), _u64, _P(_u64)]),
     "b2d_inflate_device": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64,
                                           _P(ctypes.c_float)]),
     "b2d_inflate_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64, _P(_u32)]),

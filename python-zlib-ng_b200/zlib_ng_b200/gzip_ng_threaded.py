@@ -690,20 +690,25 @@ class _ThreadedGzipWriter(io.RawIOBase):
         out_n = ctypes.c_uint64(0)
         crc = ctypes.c_uint32(0)
         ctx = self._contexts[index]
-        rc = _native.lib().b2d_compress_and_crc(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
-                                                out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc))
+        nb = (n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK
+        offs, cnt = None, ctypes.c_uint64(0)
+        if self._indexing:
+            # compress and fetch the block offsets in one call: contexts are shared by every writer of the process
+            offs = (ctypes.c_uint64 * (nb + 1))()
+            rc = _native.lib().b2d_compress_and_crc_indexed(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
+                                                            out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc),
+                                                            offs, nb + 1, ctypes.byref(cnt))
+        else:
+            rc = _native.lib().b2d_compress_and_crc(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
+                                                    out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc))
         del k1, k2
         if rc == _native.B2D_BUF_ERROR:
             raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}")
         if rc:
             zlib_ng._raise(rc, "while compressing data")
         sizes = None
-        if self._indexing:
-            nb = (n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK
-            offs = (ctypes.c_uint64 * (nb + 1))()
-            cnt = ctypes.c_uint64(0)
-            if _native.lib().b2d_block_index(ctx.handle, offs, nb + 1, ctypes.byref(cnt)) == 0 and cnt.value == nb + 1:
-                sizes = [offs[i + 1] - offs[i] for i in range(nb)]
+        if offs is not None and cnt.value == nb + 1 and offs[nb] == out_n.value:
+            sizes = [offs[i + 1] - offs[i] for i in range(nb)]
         return out_buf.view[:out_n.value], crc.value, n, sizes
 
     def _release(self, job):

@@ -207,3 +207,37 @@ def test_reader_can_be_closed_early(gzt, tmp_path, monkeypatch):
     assert f.closed and threading.active_count() <= before
     with gzt.open(path, "rb") as f:             # and the pooled buffers serve the next reader
         assert f.read() == data
+
+
+@pytest.mark.timeout(120)
+def test_writers_and_readers_sharing_the_contexts(gzt, tmp_path, monkeypatch):
+    """Several files written, then read, at the same time in one process: the GPU contexts are shared, so every
+    block index has to come from its own compress call and every host inflate owns the context's buffers."""
+    import threading
+    monkeypatch.setattr(gzt, "_READ_WINDOW_BLOCKS", 16)
+    datas = [synthdata.make(kind, 5_000_000 + 70_001 * i, 40 + i).tobytes() for i, kind in enumerate(("fastq", "mixed", "fastq"))]
+    errors = []
+
+    def write(i):
+        try:
+            with gzt.open(tmp_path / f"w{i}.gz", "wb", threads=2) as f:
+                for off in range(0, len(datas[i]), 300_000):
+                    f.write(datas[i][off:off + 300_000])
+        except BaseException as e:
+            errors.append(e)
+
+    def read(i):
+        try:
+            with gzt.open(tmp_path / f"w{i}.gz", "rb") as f:
+                assert f.raw._gpu is not None
+                assert f.read() == datas[i]
+        except BaseException as e:
+            errors.append(e)
+
+    for fn in (write, read):
+        ts = [threading.Thread(target=fn, args=(i,)) for i in range(len(datas))]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        assert not errors, errors
