@@ -241,3 +241,41 @@ def test_writers_and_readers_sharing_the_contexts(gzt, tmp_path, monkeypatch):
         for t in ts:
             t.join()
         assert not errors, errors
+
+
+def test_reader_interface_on_indexed_files(gzt):
+    """The reference's reader tests (tests/test_gzip_ng_threaded.py:73-80,114-136,180-205) on the GPU path."""
+    import io
+    data = synthdata.make("fastq", 700_000, 50).tobytes()
+    sink = io.BytesIO()
+    with gzt.open(sink, "wb", threads=2) as f:
+        f.write(data)
+    assert not sink.closed                                  # streams passed in are not closed
+    blob = sink.getvalue()
+    stream = io.BytesIO(blob)
+    with gzt.open(stream, "rb") as f:
+        assert f.raw._gpu is not None
+        assert f.readable() and not f.writable()
+        assert f.read(10) == data[:10] and f.tell() == 10
+        assert f.read() == data[10:]
+        assert f.read() == b"" and f.tell() == len(data)
+    assert not stream.closed
+    r = gzt._ThreadedGzipReader(io.BytesIO(blob))
+    r.close()
+    assert r.closed
+    r.close()                                               # double close is fine
+    with pytest.raises(ValueError, match="closed"):
+        r.readinto(bytearray(10))
+    with gzt.open(io.BytesIO(blob[:-8]), "rb") as f:        # truncated: no locator any more, CPython's reader reports it
+        with pytest.raises(EOFError):
+            f.read()
+    # an index that no longer fits the data (trailer CRC changed) is reported like a damaged gzip file
+    import gzip
+    import struct
+    end = gzt._LOCATOR.unpack(gzt._parse_extra_member(blob[-gzt._LOCATOR_MEMBER:], 0)[0])[4]
+    empty = 10 + 2 + 8
+    pos = end - empty - 8
+    bad = blob[:pos] + struct.pack("<I", struct.unpack_from("<I", blob, pos)[0] ^ 1) + blob[pos + 4:]
+    with gzt.open(io.BytesIO(bad), "rb") as f:
+        with pytest.raises(gzip.BadGzipFile, match="CRC"):
+            f.read()
