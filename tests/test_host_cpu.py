@@ -178,3 +178,28 @@ def test_host_copy_needs_no_device():
         dst = np.zeros(n + 8, dtype=np.uint8)
         assert L.b2d_host_copy(dst.ctypes.data_as(ctypes.c_void_p), src.ctypes.data_as(ctypes.c_void_p), n, threads) == 0
         assert (dst[:n] == src).all() and not dst[n:].any()
+
+
+def test_reader_without_a_device_reads_indexed_files_through_cpython(tmp_path):
+    """An indexed file on a machine without a GPU: the reader finds the index, cannot open a device and reads the
+    file the ordinary way (reading was never the accelerated path: the reference reads on one thread too)."""
+    import gzip
+    import struct
+    from zlib_ng_b200 import _native, gzip_ng_threaded as gzt
+    if _native.lib().b2d_device_count() > 0:
+        pytest.skip("a CUDA device is present: the GPU tests cover the indexed path")
+    data = bytes(range(256)) * 300
+    member = gzip.compress(data, mtime=0)
+    assert member[:4] == b"\x1f\x8b\x08\x00"
+    empty = struct.pack("<BBBBIBB", 0x1F, 0x8B, 8, 0, 0, 0xFF, 0) + b"\x03\x00" + b"\x00" * 8
+    sizes = [len(member) - 10 - 8 - 2]
+    index_off = len(member) + len(empty)
+    blob = (member + empty
+            + gzt._extra_member(struct.pack("<BBHI", 1, 0, 0, 1) + struct.pack("<I", *sizes))
+            + gzt._extra_member(gzt._LOCATOR.pack(gzt._LOCATOR_MAGIC, 1, 0, len(data), index_off, 1)))
+    p = tmp_path / "indexed.gz"
+    p.write_bytes(blob)
+    assert gzip.decompress(blob) == data
+    with gzt.open(p, "rb") as f:
+        assert f.raw._gpu is None
+        assert f.read() == data
