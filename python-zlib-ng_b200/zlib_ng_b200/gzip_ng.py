@@ -109,4 +109,14 @@ def compress(data, compresslevel=_COMPRESS_LEVEL_BEST, *, mtime=None):
 
 
 def decompress(data):
+    """gzip_ng.decompress (reference gzip_ng.py:181-205).  Data written by gzip_ng_threaded's writer carries a block
+    index and is inflated on the GPU (gzip_ng_threaded._ThreadedGzipReader); anything else goes to CPython's gzip."""
+    from . import gzip_ng_threaded
+    if len(data) > gzip_ng_threaded._LOCATOR_MEMBER + 20:
+        reader = gzip_ng_threaded._ThreadedGzipReader(io.BytesIO(data))
+        try:
+            if reader._gpu is not None:
+                return reader.readall()
+        finally:
+            reader.close()
     return gzip.decompress(data)

@@ -279,3 +279,19 @@ def test_reader_interface_on_indexed_files(gzt):
     with gzt.open(io.BytesIO(bad), "rb") as f:
         with pytest.raises(gzip.BadGzipFile, match="CRC"):
             f.read()
+
+
+def test_gzip_ng_decompress_of_indexed_data(gzt):
+    import gzip
+    import io
+    from zlib_ng_b200 import gzip_ng
+    data = synthdata.make("mixed", 2_000_000, 51).tobytes()
+    sink = io.BytesIO()
+    with gzt.open(sink, "wb", threads=2) as f:
+        f.write(data)
+    blob = sink.getvalue()
+    r = gzt._ThreadedGzipReader(io.BytesIO(blob))
+    assert r._gpu is not None
+    r.close()
+    assert gzip_ng.decompress(blob) == data
+    assert gzip_ng.decompress(gzip.compress(data[:1000])) == data[:1000]        # no index: CPython
