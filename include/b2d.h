@@ -92,10 +92,41 @@ int b2d_host_free(b2d_ctx *ctx, void *ptr);
 int b2d_copy_h2d(b2d_ctx *ctx, void *d_dst, const void *h_src, uint64_t bytes);
 int b2d_copy_d2h(b2d_ctx *ctx, void *h_dst, const void *d_src, uint64_t bytes);
 int b2d_device_sync(b2d_ctx *ctx);
+/* page-locked host memory that needs no context (cudaHostAlloc, portable: every device can read and write it), and
+ * whether an address lies in page-locked memory — host-buffer calls move such memory by DMA directly, anything else
+ * through the context's pinned staging slots */
+int b2d_pinned_alloc(uint64_t bytes, void **ptr);
+int b2d_pinned_free(void *ptr);
+int b2d_host_is_pinned(const void *ptr);
 /* memcpy between host buffers split over `threads` native threads: how the writer behind
  * gzip_ng_threaded.open fills its pinned batch from the caller's bytes (the reference copies every block once
  * as well: `data = bytes(b)`, gzip_ng_threaded.py:315).  One thread moves ~14 GB/s on the test box, eight ~70. */
 int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads);
+/* ---- one stream over several GPUs ---------------------------------------------------------
+ * The reference runs N compression threads on ONE stream: blocks are dealt round-robin (gzip_ng_threaded.py:316-321),
+ * a writer thread emits the results in order and folds their CRCs with crc32_combine (:382-398, :394).  A multi-device
+ * context is that with one GPU per worker: the call cuts `data` into batches, batch j runs on device j % n_devices
+ * primed with the 32 KiB of input before it (one native thread per device, each with the H2D / kernels / D2H
+ * pipeline of b2d_deflate_host), every batch's output lands behind its predecessor's in `out`, and the host folds
+ * the checksums.  No device-to-device traffic, no collective.  The bytes produced are those of the single-device
+ * call on the same input (blocks are independent given the raw input).
+ * `devices` may name a device more than once (several contexts on one GPU): that is how a one-GPU box exercises
+ * the sharding. */
+typedef struct b2d_mctx b2d_mctx;
+int b2d_mctx_create(const int *devices, int n_devices, uint64_t max_batch, b2d_mctx **out);
+void b2d_mctx_destroy(b2d_mctx *m);
+int b2d_mctx_devices(b2d_mctx *m);
+uint64_t b2d_mctx_launch_count(b2d_mctx *m);
+/* b2d_deflate_host over all devices of `m`.  block_sizes (optional, `cap` entries) receives the compressed size of
+ * every 128 KiB device block, *count their number (what the writer stores as its block index). */
+int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                           uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                           uint32_t *adler, uint64_t *block_sizes, uint64_t cap, uint64_t *count);
+/* _ParallelCompress.compress_and_crc (zlib_ngmodule.c:1696-1782) over all devices of `m` */
+int b2d_compress_and_crc_multi(b2d_mctx *m, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                               uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                               uint64_t *block_sizes, uint64_t cap, uint64_t *count);
+
 /* ---- the other side of the wire: block-parallel inflate of streams written by this library ----
  * (first version.  The reference decompresses with zng_inflate on one thread:
  * zlib_ng.decompress, zlib_ngmodule.c:275-370; _GzipReader.read, :2426-2637; gzip_ng_threaded.py:90-167.)

@@ -8,6 +8,7 @@
  * independent given the raw input).
  */
 #include <cuda_runtime.h>
+#include <condition_variable>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -97,6 +98,7 @@ struct b2d_ctx {
     uint64_t *d_index; uint64_t index_cap, index_n;
     /* host-buffer calls keep offsets relative to each batch's output: index_base[j] is where batch j's output starts */
     std::vector<uint64_t> index_base; uint64_t index_total;
+    uint64_t index_bpb, index_local;        /* blocks per batch of that call; entries this context holds in d_index */
     /* inflate scratch: 16-bit symbols, block index, error word */
     uint16_t *d_inf16; uint64_t inf16_cap;
     uint64_t *d_inf_index; uint64_t inf_index_cap;
@@ -191,6 +193,20 @@ extern "C" int b2d_copy_h2d(b2d_ctx *c, void *d, const void *h, uint64_t n) {
 }
 extern "C" int b2d_copy_d2h(b2d_ctx *c, void *h, const void *d, uint64_t n) {
     CU(cudaSetDevice(c->device)); CU(cudaMemcpyAsync(h, d, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return B2D_OK;
+}
+/* page-locked host memory without a context (visible to every device: unified addressing), and the test the writers
+ * use to hand such memory to the GPU without staging it */
+extern "C" int b2d_pinned_alloc(uint64_t bytes, void **p) {
+    if (!p) return fail(B2D_STREAM_ERROR, "null argument");
+    CU(cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocPortable));
+    return B2D_OK;
+}
+extern "C" int b2d_pinned_free(void *p) { if (p) CU(cudaFreeHost(p)); return B2D_OK; }
+extern "C" int b2d_host_is_pinned(const void *p) {
+    cudaPointerAttributes at;
+    const bool pinned = p && cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return pinned ? 1 : 0;
 }
 extern "C" int b2d_device_sync(b2d_ctx *c) { CU(cudaSetDevice(c->device)); CU(cudaDeviceSynchronize()); return B2D_OK; }
 
@@ -483,68 +499,104 @@ static int ensure_staging(b2d_ctx *c, bool in, bool out) {
     return B2D_OK;
 }
 
-/* Pinned host input and output, more than one batch: three-stage software pipeline.
- *   st_in : H2D of batch j into slot j % B2D_NSLOT (waits until the kernels of the slot's previous batch released it)
- *   lanes : kernels + CRC of batch j on lane j % B2D_NLANE (waits for its H2D and for the D2H of the slot's previous batch);
+/* What the batches of one call share: where each batch's output starts.  With one context the batches finish in
+ * order anyway; with several (b2d_deflate_host_multi: batch j runs on device j % k) a context learns the offset of
+ * its batch j from the context that ran batch j - 1, as soon as that batch's kernels are done — its size is known
+ * then, its device-to-host copy need not be. */
+struct b2d_ledger {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<uint64_t> off;            /* off[j] = output bytes before batch j; valid for j <= known */
+    std::vector<uint32_t> crc, adler;     /* per batch, from the neutral start values (0 / 1) */
+    uint64_t known = 0;
+    int rc = B2D_OK;                      /* first failure of any context; the others stop waiting */
+    char err[512] = {0};
+    explicit b2d_ledger(uint64_t nb) : off(nb + 1, 0), crc(nb, 0), adler(nb, 1) {}
+    void fail_with(int code, const char *msg) {
+        std::lock_guard<std::mutex> g(mu);
+        if (rc == B2D_OK) { rc = code; snprintf(err, sizeof err, "%s", msg); }
+        cv.notify_all();
+    }
+};
+
+/* Host input and output, more than one batch: three-stage software pipeline over the batches
+ * j = first, first + stride, ... of the call (one context takes them all: first 0, stride 1).
+ *   st_in : H2D of a batch into slot i % B2D_NSLOT (waits until the kernels of the slot's previous batch released it)
+ *   lanes : kernels + CRC of the batch on lane i % B2D_NLANE (waits for its H2D and for the D2H of the slot's previous batch);
  *           consecutive batches overlap, which fills the tail waves of each other's kernels
- *   st_out: D2H of batch j-1 (issued once the host knows its size)
- * The host only blocks on "kernels of batch j-2 done", by which time batches j-1 and j are already queued.
+ *   st_out: D2H of an earlier batch (issued once the host knows its size and where it goes)
+ * The host only blocks on "kernels of the batch two back are done", by which time the next two are already queued.
  * Pageable input / output goes through pinned staging slots (copied by a few host threads), so those callers
  * get the same overlap. */
 static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, const uint8_t *data, uint64_t n, const uint8_t *dict,
-                                  uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t reserve, uint64_t *produced_out,
-                                  uint32_t *crc_acc, uint32_t *adler_acc, bool in_pinned, bool out_pinned) {
+                                  uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t reserve, bool want_crc, bool want_adler,
+                                  bool in_pinned, bool out_pinned, uint64_t batch, uint64_t first, uint64_t stride, b2d_ledger *G) {
     int rc = ensure_second_slot(c);
     if (rc) return rc;
     if ((rc = ensure_second_lane(c))) return rc;
     if ((rc = ensure_staging(c, !in_pinned, !out_pinned))) return rc;
-    cudaStream_t *cs = c->stl;                  /* batch j computes on lane j % B2D_NLANE */
+    cudaStream_t *cs = c->stl;                  /* local batch i computes on lane i % B2D_NLANE */
     uint8_t *d_in[B2D_NSLOT] = {c->d_in}, *d_out[B2D_NSLOT] = {c->d_out};
     uint64_t *d_total[B2D_NSLOT] = {c->d_total};
     b2d_cksum_ws *ck[B2D_NSLOT] = {c->ck};
     for (int i = 1; i < B2D_NSLOT; ++i) { d_in[i] = c->d_inx[i - 1]; d_out[i] = c->d_outx[i - 1]; d_total[i] = c->d_totalx[i - 1]; ck[i] = c->ckx[i - 1]; }
-    const uint64_t nb = (n + c->max_batch - 1) / c->max_batch;
-    if ((rc = ensure_index(c, n))) return rc;
-    c->index_base.assign(nb, 0);
-    uint64_t produced = 0;
-    uint64_t drained = 0;                 /* bytes of `out` final (staged output only) */
+    const uint64_t nb = (n + batch - 1) / batch;                                  /* batches of the whole call */
+    const uint64_t nloc = first < nb ? (nb - first + stride - 1) / stride : 0;    /* ... of this context */
+    const uint64_t bpb = batch / B2D_BLOCK;
+    if ((rc = ensure_index(c, nloc * batch))) return rc;
+    c->index_base.assign(nloc, 0);
+    c->index_bpb = bpb;
     uint64_t pend_off = 0, pend_n = 0; int pend_s = -1;
+    auto batch_len = [&](uint64_t j) { return (j + 1 == nb) ? n - j * batch : batch; };
     auto drain = [&]() -> int {          /* staged output: copy the batch whose D2H was issued last */
         if (pend_s < 0) return B2D_OK;
         CU(cudaEventSynchronize(c->ev_out[pend_s]));
         par_memcpy(out + pend_off, c->h_out_s[pend_s], pend_n);
-        drained = pend_off + pend_n;
         pend_s = -1;
         return B2D_OK;
     };
-    auto finish = [&](uint64_t j) -> int {          /* batch j: wait for its kernels, fold its checksums, start its D2H */
-        const int s = (int)(j % B2D_NSLOT);
-        const uint64_t m = (j + 1 == nb) ? n - j * c->max_batch : c->max_batch;
+    auto finish = [&](uint64_t i) -> int {          /* local batch i: wait for its kernels, note its checksums, start its D2H */
+        const int s = (int)(i % B2D_NSLOT);
+        const uint64_t j = first + i * stride, m = batch_len(j);
         CU(cudaEventSynchronize(c->ev_comp[s]));
-        if (crc_acc) *crc_acc = b2d_crc32_dev_finish(ck[s], m, *crc_acc);
-        if (adler_acc) *adler_acc = b2d_adler32_dev_finish(ck[s], m, *adler_acc);
+        if (want_crc) G->crc[j] = b2d_crc32_dev_finish(ck[s], m, 0);
+        if (want_adler) G->adler[j] = b2d_adler32_dev_finish(ck[s], m, 1);
         const uint64_t got = c->h_total[s];
-        if (produced + got + reserve > out_cap) return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
-        c->index_base[j] = produced;
+        uint64_t at;
+        {
+            std::unique_lock<std::mutex> lk(G->mu);
+            G->cv.wait(lk, [&] { return G->known >= j || G->rc != B2D_OK; });
+            if (G->rc != B2D_OK) return G->rc;            /* another context failed: its message is in the ledger */
+            at = G->off[j];
+            if (at + got + reserve > out_cap) {
+                lk.unlock();
+                G->fail_with(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+                return fail(B2D_BUF_ERROR, "Compressed output exceeds buffer size");
+            }
+            G->off[j + 1] = at + got;
+            G->known = j + 1;
+        }
+        G->cv.notify_all();
+        c->index_base[i] = at;
         if (out_pinned) {
-            CU(cudaMemcpyAsync(out + produced, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
+            CU(cudaMemcpyAsync(out + at, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
             CU(cudaEventRecord(c->ev_out[s], c->st_out));
         } else {
             int rc2 = drain(); if (rc2) return rc2;     /* the previous batch's bytes, while this one's kernels ran */
             CU(cudaMemcpyAsync(c->h_out_s[s], d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
             CU(cudaEventRecord(c->ev_out[s], c->st_out));
-            pend_s = s; pend_off = produced; pend_n = got;
+            pend_s = s; pend_off = at; pend_n = got;
         }
-        produced += got;
         return B2D_OK;
     };
-    for (uint64_t j = 0; j < nb; ++j) {
-        const int s = (int)(j % B2D_NSLOT);
-        const int ln = (int)(j % B2D_NLANE);  /* compute lane */
-        const uint64_t off = j * c->max_batch;
-        const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
+    for (uint64_t i = 0; i < nloc; ++i) {
+        const int s = (int)(i % B2D_NSLOT);
+        const int ln = (int)(i % B2D_NLANE);  /* compute lane */
+        const uint64_t j = first + i * stride;
+        const uint64_t off = j * batch;
+        const uint64_t m = batch_len(j);
         uint64_t D;
-        if (j >= B2D_NSLOT) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));      /* slot's input no longer read */
+        if (i >= B2D_NSLOT) CU(cudaStreamWaitEvent(c->st_in, c->ev_comp[s], 0));      /* slot's input no longer read */
         if (j == 0) {
             D = dict_n;
             if (D) { CU(cudaMemcpyAsync(d_in[s], dict, D, cudaMemcpyHostToDevice, c->st_in)); }
@@ -557,14 +609,14 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
             D = B2D_WINDOW;
             if (in_pinned) { CU(cudaMemcpyAsync(d_in[s], data + off - B2D_WINDOW, B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in)); }
             else {
-                /* the slot's previous H2D (batch j-3) finished before that batch's kernels, which finish(j-3) waited for */
+                /* the slot's previous H2D (three batches back) finished before that batch's kernels, which finish() waited for */
                 par_memcpy(c->h_in_s[s], data + off - B2D_WINDOW, B2D_WINDOW + m);
                 CU(cudaMemcpyAsync(d_in[s], c->h_in_s[s], B2D_WINDOW + m, cudaMemcpyHostToDevice, c->st_in));
             }
         }
         CU(cudaEventRecord(c->ev_in[s], c->st_in));
         CU(cudaStreamWaitEvent(cs[ln], c->ev_in[s], 0));
-        if (j >= B2D_NSLOT) CU(cudaStreamWaitEvent(cs[ln], c->ev_out[s], 0));         /* slot's output already copied out */
+        if (i >= B2D_NSLOT) CU(cudaStreamWaitEvent(cs[ln], c->ev_out[s], 0));         /* slot's output already copied out */
         CU(cudaMemsetAsync(d_out[s], 0, align_up(b2d_deflate_bound(m), 4), cs[ln]));
         CU(cudaMemsetAsync(d_total[s], 0, sizeof(uint64_t), cs[ln]));
         b2d_job J; fill_job(c, &J, d_in[s], D, m, c->d_in_cap, level, d_out[s], max_dist, ln);
@@ -572,22 +624,32 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         CU(b2d_launch_pipeline(&J, cs[ln], nullptr));
         c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
-        CU(cudaMemcpyAsync(c->d_index + off / B2D_BLOCK, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK) * sizeof(uint64_t),
+        CU(cudaMemcpyAsync(c->d_index + i * bpb, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK) * sizeof(uint64_t),
                            cudaMemcpyDeviceToDevice, cs[ln]));
-        if (crc_acc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
-        if (adler_acc) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
+        if (want_crc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
+        if (want_adler) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
         /* the host trails by one batch per lane: the lanes stay busy while it waits for the oldest batch */
-        if (j >= B2D_NLANE && (rc = finish(j - B2D_NLANE))) { cudaDeviceSynchronize(); return rc; }
+        if (i >= B2D_NLANE && (rc = finish(i - B2D_NLANE))) { cudaDeviceSynchronize(); return rc; }
     }
-    for (uint64_t k = nb > B2D_NLANE ? nb - B2D_NLANE : 0; k < nb; ++k)
+    for (uint64_t k = nloc > B2D_NLANE ? nloc - B2D_NLANE : 0; k < nloc; ++k)
         if ((rc = finish(k))) { cudaDeviceSynchronize(); return rc; }
     if ((rc = drain())) { cudaDeviceSynchronize(); return rc; }
     CU(cudaStreamSynchronize(c->st_out));
-    *produced_out = produced;
-    c->index_total = produced;
-    c->index_n = (n + B2D_BLOCK - 1) / B2D_BLOCK + 1;
+    /* the index of this context's blocks (b2d_block_index, collect_index): relative offsets stay on the device */
+    c->index_n = 0;
+    c->index_local = nloc ? (nloc - 1) * bpb + (batch_len(first + (nloc - 1) * stride) + B2D_BLOCK - 1) / B2D_BLOCK : 0;
     return B2D_OK;
+}
+
+/* fold the per-batch checksums of a finished call in stream order */
+static void ledger_fold(const b2d_ledger &G, uint64_t n, uint64_t batch, uint32_t *crc_acc, uint32_t *adler_acc) {
+    const uint64_t nb = (n + batch - 1) / batch;
+    for (uint64_t j = 0; j < nb; ++j) {
+        const uint64_t m = (j + 1 == nb) ? n - j * batch : batch;
+        if (crc_acc) *crc_acc = b2d_host_crc32_combine(*crc_acc, G.crc[j], m);
+        if (adler_acc) *adler_acc = b2d_host_adler32_combine(*adler_acc, G.adler[j], m);
+    }
 }
 
 /* crc32 / adler32 of a host buffer larger than one batch: copy-in (through pinned staging when the caller's
@@ -654,9 +716,14 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         const bool opinned = out && cudaPointerGetAttributes(&ot, out) == cudaSuccess && ot.type == cudaMemoryTypeHost;
         cudaGetLastError();
         if (n > c->max_batch) {
-            int rc = deflate_host_pipelined(c, level, max_dist, data, n, dict, dict_n, out, out_cap, final ? 2 : 0, &produced,
-                                            crc ? &crc_acc : nullptr, adler ? &adler_acc : nullptr, pinned, opinned);
+            b2d_ledger G((n + c->max_batch - 1) / c->max_batch);
+            int rc = deflate_host_pipelined(c, level, max_dist, data, n, dict, dict_n, out, out_cap, final ? 2 : 0, crc != nullptr,
+                                            adler != nullptr, pinned, opinned, c->max_batch, 0, 1, &G);
             if (rc) return rc;
+            ledger_fold(G, n, c->max_batch, crc ? &crc_acc : nullptr, adler ? &adler_acc : nullptr);
+            produced = G.off[G.off.size() - 1];
+            c->index_total = produced;
+            c->index_n = (n + B2D_BLOCK - 1) / B2D_BLOCK + 1;
             if (final) { out[produced++] = 0x03; out[produced++] = 0x00; }
             *out_n = produced;
             if (crc) *crc = crc_acc;
@@ -747,6 +814,161 @@ extern "C" int b2d_compress_and_crc_indexed(b2d_ctx *c, int level, const uint8_t
 }
 
 /* ------------------------------------------------------------------------- */
+/* one stream over several devices: what the reference does with N worker threads on one stream —
+ * round-robin dispatch (gzip_ng_threaded.py:316-321), in-order output and the crc32_combine fold of its writer
+ * thread (:382-398) — with one GPU context per worker.  No device talks to another: batch j goes to device j % k
+ * primed with the 32 KiB of host input before it, its output lands behind batch j - 1's in the caller's buffer, the
+ * host folds the checksums. */
+/* ------------------------------------------------------------------------- */
+#define B2D_MAX_DEVICES 16
+struct b2d_mctx {
+    int n;
+    b2d_ctx *ctx[B2D_MAX_DEVICES];
+    uint64_t max_batch;
+    std::mutex mu;                 /* one call at a time */
+    std::vector<uint64_t> sizes;   /* compressed size of every device block of the last call */
+};
+
+extern "C" int b2d_mctx_create(const int *devices, int n_devices, uint64_t max_batch, b2d_mctx **out) {
+    if (!out || !devices) return fail(B2D_STREAM_ERROR, "null argument");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > B2D_MAX_DEVICES) return fail(B2D_STREAM_ERROR, "between 1 and 16 devices");
+    b2d_mctx *m = new b2d_mctx();
+    m->n = n_devices;
+    for (int i = 0; i < B2D_MAX_DEVICES; ++i) m->ctx[i] = nullptr;
+    /* contexts come up side by side: the first CUDA call on a device pays for its primary context */
+    int rcs[B2D_MAX_DEVICES];
+    char errs[B2D_MAX_DEVICES][512];
+    std::thread th[B2D_MAX_DEVICES];
+    for (int i = 0; i < n_devices; ++i)
+        th[i] = std::thread([&, i] {
+            rcs[i] = b2d_ctx_create(devices[i], max_batch, &m->ctx[i]);
+            snprintf(errs[i], sizeof errs[i], "%s", rcs[i] ? g_err : "");
+        });
+    for (int i = 0; i < n_devices; ++i) th[i].join();
+    for (int i = 0; i < n_devices; ++i)
+        if (rcs[i]) {
+            const int rc = rcs[i];
+            snprintf(g_err, sizeof g_err, "device %d: %s", devices[i], errs[i]);
+            for (int k = 0; k < n_devices; ++k) ctx_free(m->ctx[k]);
+            delete m;
+            return rc;
+        }
+    m->max_batch = m->ctx[0]->max_batch;
+    *out = m;
+    return B2D_OK;
+}
+extern "C" void b2d_mctx_destroy(b2d_mctx *m) {
+    if (!m) return;
+    for (int i = 0; i < m->n; ++i) ctx_free(m->ctx[i]);
+    delete m;
+}
+extern "C" int b2d_mctx_devices(b2d_mctx *m) { return m ? m->n : 0; }
+extern "C" uint64_t b2d_mctx_launch_count(b2d_mctx *m) {
+    uint64_t t = 0;
+    if (m) for (int i = 0; i < m->n; ++i) t += m->ctx[i]->launches;
+    return t;
+}
+
+/* batch size of a multi-device call over n bytes: small enough that every device gets two batches (its two lanes
+ * overlap), at least 8 MiB (below that a batch does not fill a device), at most the contexts' max_batch */
+static uint64_t multi_batch(const b2d_mctx *m, uint64_t n) {
+    uint64_t b = align_up((n + 2ull * m->n - 1) / (2ull * m->n), B2D_BLOCK);
+    const uint64_t lo = 8ull << 20;
+    if (b < lo) b = lo;
+    if (b > m->max_batch) b = m->max_batch;
+    return b;
+}
+
+extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                      uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                      uint32_t *adler, uint64_t *block_sizes, uint64_t cap, uint64_t *count) {
+    if (!m || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (!b2d_level_valid(level)) return fail(B2D_STREAM_ERROR, "Bad compression level");
+    if (window_bits < 9 || window_bits > 15) return fail(B2D_STREAM_ERROR, "window_bits outside 9..15");
+    std::lock_guard<std::mutex> whole(m->mu);
+    const uint64_t nblocks = (n + B2D_BLOCK - 1) / B2D_BLOCK;
+    if (count) *count = nblocks;
+    if (block_sizes && cap < nblocks) return fail(B2D_BUF_ERROR, "b2d_deflate_host_multi: capacity below the number of blocks");
+    const uint64_t batch = multi_batch(m, n);
+    const uint64_t nb = (n + batch - 1) / batch;
+    if (nb < 2) {
+        /* one batch: one device, the single-context path (same bytes: the output does not depend on how batches are cut) */
+        b2d_ctx *c = m->ctx[0];
+        std::lock_guard<std::recursive_mutex> g(c->mu);
+        int rc = b2d_deflate_host(c, level, window_bits, data, n, dict, dict_n, final, out, out_cap, out_n, crc, adler);
+        if (rc || !block_sizes || !nblocks) return rc;
+        std::vector<uint64_t> offs(nblocks + 1);
+        uint64_t cnt = 0;
+        if ((rc = b2d_block_index(c, offs.data(), nblocks + 1, &cnt))) return rc;
+        if (cnt != nblocks + 1) return fail(B2D_STREAM_ERROR, "block index does not match the input size");
+        for (uint64_t i = 0; i < nblocks; ++i) block_sizes[i] = offs[i + 1] - offs[i];
+        return B2D_OK;
+    }
+    const uint32_t max_dist = 1u << window_bits;
+    if (dict_n > max_dist) { dict += dict_n - max_dist; dict_n = max_dist; }
+    if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
+    const int k = (uint64_t)m->n < nb ? m->n : (int)nb;      /* contexts that get work */
+    b2d_ledger G(nb);
+    std::thread th[B2D_MAX_DEVICES];
+    std::vector<uint64_t> rel[B2D_MAX_DEVICES];               /* per context: its blocks' offsets relative to their batch */
+    for (int d = 0; d < k; ++d)
+        th[d] = std::thread([&, d] {
+            b2d_ctx *c = m->ctx[d];
+            std::lock_guard<std::recursive_mutex> g(c->mu);
+            int rc = B2D_OK;
+            cudaError_t e = cudaSetDevice(c->device);
+            if (e != cudaSuccess) rc = fail_cuda(e, "cudaSetDevice");
+            if (!rc) {
+                cudaPointerAttributes at;
+                const bool ip = cudaPointerGetAttributes(&at, data) == cudaSuccess && at.type == cudaMemoryTypeHost;
+                cudaGetLastError();
+                const bool op = cudaPointerGetAttributes(&at, out) == cudaSuccess && at.type == cudaMemoryTypeHost;
+                cudaGetLastError();
+                rc = deflate_host_pipelined(c, level, max_dist, data, n, dict, dict_n, out, out_cap, final ? 2 : 0, crc != nullptr,
+                                            adler != nullptr, ip, op, batch, (uint64_t)d, (uint64_t)k, &G);
+            }
+            if (!rc && block_sizes && c->index_local) {
+                rel[d].resize(c->index_local);
+                e = cudaMemcpyAsync(rel[d].data(), c->d_index, c->index_local * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+                if (e != cudaSuccess) rc = fail_cuda(e, "block index copy");
+            }
+            if (rc) G.fail_with(rc, g_err);       /* wakes the contexts that wait for this one's offsets */
+        });
+    for (int d = 0; d < k; ++d) th[d].join();
+    if (G.rc != B2D_OK) { snprintf(g_err, sizeof g_err, "%s", G.err); return G.rc; }
+    uint64_t produced = G.off[nb];
+    if (block_sizes) {
+        /* absolute start of every block = its batch's place in the output + its offset inside the batch's output */
+        const uint64_t bpb = batch / B2D_BLOCK;
+        uint64_t prev = 0;
+        for (uint64_t b = 0; b < nblocks; ++b) {
+            const uint64_t j = b / bpb, d = j % (uint64_t)k, i = j / (uint64_t)k;
+            const uint64_t start = G.off[j] + rel[d][i * bpb + b % bpb];
+            if (b) block_sizes[b - 1] = start - prev;
+            prev = start;
+        }
+        block_sizes[nblocks - 1] = produced - prev;
+    }
+    uint32_t crc_acc = crc ? *crc : 0, adler_acc = adler ? *adler : 1;
+    ledger_fold(G, n, batch, crc ? &crc_acc : nullptr, adler ? &adler_acc : nullptr);
+    if (final) { out[produced++] = 0x03; out[produced++] = 0x00; }
+    *out_n = produced;
+    if (crc) *crc = crc_acc;
+    if (adler) *adler = adler_acc;
+    return B2D_OK;
+}
+
+extern "C" int b2d_compress_and_crc_multi(b2d_mctx *m, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                          uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                          uint64_t *block_sizes, uint64_t cap, uint64_t *count) {
+    if (!crc) return fail(B2D_STREAM_ERROR, "null argument");
+    *crc = 0;
+    return b2d_deflate_host_multi(m, level, 15, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr, block_sizes, cap, count);
+}
+
+/* ------------------------------------------------------------------------- */
 /* inflate side (first version): streams of this library + their block index */
 /* ------------------------------------------------------------------------- */
 extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint64_t *count) {
@@ -759,11 +981,22 @@ extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint
     CU(cudaMemcpyAsync(offsets, c->d_index, c->index_n * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
     if (!c->index_base.empty()) {       /* multi-batch host call: offsets were relative to each batch's output */
-        const uint64_t bpb = c->max_batch / B2D_BLOCK;
+        const uint64_t bpb = c->index_bpb;
         for (uint64_t i = 0; i + 1 < c->index_n; ++i) offsets[i] += c->index_base[i / bpb];
         offsets[c->index_n - 1] = c->index_total;
     }
     return B2D_OK;
+}
+
+/* how the three inflate kernels are issued: side by side where the device can do that, on one stream where it
+ * cannot (or where a tool serialises launches anyway) */
+static int inflate_mode(b2d_ctx *c) {
+    static const bool forced = (getenv("B2D_INF_SERIAL") && getenv("B2D_INF_SERIAL")[0] == '1') ||
+                               (getenv("CUDA_LAUNCH_BLOCKING") && getenv("CUDA_LAUNCH_BLOCKING")[0] == '1');
+    if (forced) return B2D_INF_SERIAL;
+    int conc = 1;
+    if (cudaDeviceGetAttribute(&conc, cudaDevAttrConcurrentKernels, c->device) != cudaSuccess) { cudaGetLastError(); conc = 1; }
+    return conc ? B2D_INF_CONCURRENT : B2D_INF_SERIAL;
 }
 
 extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
@@ -793,32 +1026,46 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         CU(cudaMalloc(&c->d_inf_index, nblocks * sizeof(uint64_t)));
         c->inf_index_cap = nblocks;
     }
-    if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, sizeof(uint32_t)));
+    if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, 2 * sizeof(uint32_t)));
     if (nblocks > c->inf_flags_cap) {
         cudaFree(c->d_inf_flags); c->d_inf_flags = nullptr; c->inf_flags_cap = 0;
         CU(cudaMalloc(&c->d_inf_flags, nblocks * sizeof(uint32_t)));
         c->inf_flags_cap = nblocks;
     }
     if (!c->st_inf) {
-        CU(cudaStreamCreateWithFlags(&c->st_inf, cudaStreamNonBlocking));
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&c->st_inf, cudaStreamNonBlocking, hi));     /* the serial pass is the critical path */
         CU(cudaEventCreateWithFlags(&c->ev_inf_fork, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&c->ev_inf_join, cudaEventDisableTiming));
     }
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
-    CU(cudaMemsetAsync(c->d_inf_err, 0, sizeof(uint32_t), c->st));
+    CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
-                          c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join));
+                          c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join, inflate_mode(c)));
     c->launches += B2D_INF_LAUNCHES;
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
-    uint32_t err = 0;
-    CU(cudaMemcpyAsync(&err, c->d_inf_err, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    uint32_t err[2] = {0, 0};
+    CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
+    if (err[1] && !err[0]) {
+        /* the pass over the tails gave up waiting for the decode (it could not run beside it and the wait ran out).
+         * That says nothing about the data: every block is decoded by now, so resolve again on one stream. */
+        CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
+        CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+                              c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join, B2D_INF_RESOLVE_ONLY));
+        c->launches += 2;
+        if (ms) CU(cudaEventRecord(c->ev1, c->st));
+        CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        if (err[1] && !err[0]) return fail(B2D_CUDA_ERROR, "inflate: the resolving pass did not complete");
+    }
     if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
-    if (err) {
+    if (err[0]) {
         static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code",
-                                    "decode did not arrive", "", "", ""};
-        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err >> 28) & 7], err & 0x0fffffffu);
+                                    "", "", "", ""};
+        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err[0] >> 28) & 7], err[0] & 0x0fffffffu);
         return -3;   /* Z_DATA_ERROR */
     }
     return B2D_OK;

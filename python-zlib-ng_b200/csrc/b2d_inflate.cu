@@ -15,7 +15,8 @@
  *                  markers around like bytes, so a block never waits for its predecessor.
  *   k_inf_tails    one cluster of 8 CTAs walks the blocks in order and resolves the last 32 KiB of each (one
  *                  gather per marker from the predecessor's resolved tail): the only serial part.  It is launched
- *                  first, on its own stream, and follows the decode through one ready flag per block.
+ *                  right behind the decode, on its own stream, and follows it through one ready flag per block;
+ *                  the decode never waits for it, so nothing depends on the two kernels running at the same time.
  *   k_inf_finish   one CTA per block resolves the rest of the block against the now final tails.
  *
  * Reference code this stands in for: zng_inflate (zlib-ng/inflate.c:474-1150), inflate_table
@@ -270,7 +271,12 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
         }
     }
     if (!fail && produced != expect) fail = 2;
-    if (fail && lane == 0) atomicCAS(err, 0u, (fail << 28) | (b & 0x0fffffffu));
+    if (fail) {
+        /* the scratch is reused across calls: what this block did not decode would otherwise reach the resolving
+         * passes as stale symbols (markers included) of an earlier call */
+        for (uint32_t i = produced + lane; i < expect; i += 32) o16[i] = 0;
+        if (lane == 0) atomicCAS(err, 0u, (fail << 28) | (b & 0x0fffffffu));
+    }
     /* the block's symbols are in memory: k_inf_tails (running beside this kernel) may pick its tail up */
     __syncwarp();
     if (lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = 1u; }
@@ -278,7 +284,10 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
 
 /* the byte a marker stands for: `k` indexes the 32 KiB that precede the block starting at output byte bs */
 __device__ __forceinline__ uint32_t inf_behind(const uint8_t *out8, const uint8_t *dict, uint32_t dict_n, uint64_t bs, uint32_t k) {
-    if (bs == 0) return dict[dict_n - B2D_WINDOW + k];      /* k >= 32768 - dict_n was checked by the decoder */
+    /* the decoder only emits markers with 32768 - reach <= k < 32768; the tests below keep a marker that did not come
+     * from it (a failed block, see k_inf_decode) inside the buffers */
+    if (k >= B2D_WINDOW) return 0u;
+    if (bs == 0) return k + dict_n >= B2D_WINDOW ? dict[dict_n - B2D_WINDOW + k] : 0u;
     return __ldcg(out8 + (bs - B2D_WINDOW + k));
 }
 
@@ -309,20 +318,23 @@ k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ di
     const uint32_t t = blockIdx.x * INF_TAIL_THREADS + threadIdx.x;          /* 0 .. 4095: one group of 8 symbols */
     const uint32_t nfull = (uint32_t)(raw_n / B2D_BLOCK);          /* blocks of 128 KiB: their tails are aligned */
     const uint64_t toff = (B2D_BLOCK - B2D_WINDOW) + 8u * t;
-    /* This kernel starts before k_inf_decode and follows it block by block: blocks [first, last) must have been
-     * decoded before their symbols are read.  One thread per flag polls (bounded: a decode that never arrives
-     * is reported, not waited for). */
+    /* This kernel is launched AFTER k_inf_decode, on a second stream, and follows it block by block: blocks
+     * [first, last) must have been decoded before their symbols are read.  The decode never waits for this kernel,
+     * so the flags always arrive — at once when the two kernels cannot run side by side (profilers,
+     * CUDA_LAUNCH_BLOCKING: the decode has finished by the time this one starts).  The bound below is a hang guard
+     * for a decode that died; it sets err[1], which the host answers by running this pass again after the decode
+     * (never by reporting bad data). */
     auto wait_ready = [&](uint32_t first, uint32_t last) {
         bool ok = true;
-        if (threadIdx.x < last - first && *reinterpret_cast<volatile uint32_t *>(err) == 0u) {
+        if (threadIdx.x < last - first && *reinterpret_cast<volatile uint32_t *>(err + 1) == 0u) {
             const volatile uint32_t *f = flags + first + threadIdx.x;
             uint32_t spins = 0;
             while (*f == 0u) {
                 __nanosleep(1000);
-                if (++spins > 20000000u) { ok = false; break; }   /* ~20 s: a hang guard, not a deadline */
+                if (++spins > 4000000u) { ok = false; break; }
             }
         }
-        if (!__syncthreads_and(ok) && threadIdx.x == 0) atomicCAS(err, 0u, (4u << 28) | (first & 0x0fffffffu));
+        if (!__syncthreads_and(ok) && threadIdx.x == 0) atomicCAS(err + 1, 0u, 1u + first);
         __threadfence();
     };
     auto load = [&](uint32_t b) { return __ldcg(reinterpret_cast<const uint4 *>(out16 + (uint64_t)b * B2D_BLOCK + toff)); };
@@ -365,46 +377,50 @@ k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *_
     }
 }
 
+static cudaError_t launch_tails(const uint16_t *d_out16, uint8_t *d_out, const uint8_t *d_dict, uint32_t dict_n, uint32_t nblocks,
+                                uint64_t raw_n, const uint32_t *d_flags, uint32_t *d_err, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = INF_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, k_inf_tails, d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err);
+}
+
+/* Dynamic shared memory that k_inf_decode asks for without using it: with it 12 of its CTAs (48 warps) fit an SM
+ * instead of 13, which leaves the 16 warps one CTA of the tails cluster needs free on every SM — the serial pass
+ * finds room beside the decode whenever the device can run two kernels at once. */
+#define INF_DECODE_PAD 1024
+
 cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
                                const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
                                uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st, cudaStream_t st_tails,
-                               cudaEvent_t ev_fork, cudaEvent_t ev_join) {
+                               cudaEvent_t ev_fork, cudaEvent_t ev_join, int mode) {
     if (nblocks == 0) return cudaSuccess;
     cudaError_t e;
-    {   /* With lazy module loading the first launch of a kernel loads it, which can wait for running kernels to end:
-         * k_inf_decode must be resident in the driver before k_inf_tails starts waiting for it. */
-        cudaFuncAttributes fa;
-        if ((e = cudaFuncGetAttributes(&fa, k_inf_decode)) != cudaSuccess) return e;
-        if ((e = cudaFuncGetAttributes(&fa, k_inf_tails)) != cudaSuccess) return e;
-        if ((e = cudaFuncGetAttributes(&fa, k_inf_finish)) != cudaSuccess) return e;
+    if (mode == B2D_INF_RESOLVE_ONLY) {
+        /* the decode of an earlier launch is complete (the caller synchronised): resolve on one stream */
+        if ((e = launch_tails(d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err, st)) != cudaSuccess) return e;
+        k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
+        return cudaGetLastError();
     }
     if ((e = cudaMemsetAsync(d_flags, 0, nblocks * sizeof(uint32_t), st)) != cudaSuccess) return e;
-    /* B2D_INF_SERIAL=1: one stream, decode before the tails (profilers serialise kernels: the concurrent form
-     * would have the tails pass wait for a decode that cannot start) */
-    static const bool serial = getenv("B2D_INF_SERIAL") && getenv("B2D_INF_SERIAL")[0] == '1';
-    if (serial) st_tails = st;
-    if (serial)
-        k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
-                                                                                    d_out16, d_flags, d_err);
-    /* otherwise the serial pass over the tails goes first, on its own stream, and follows the decode through d_flags */
-    if ((e = cudaEventRecord(ev_fork, st)) != cudaSuccess) return e;
-    if ((e = cudaStreamWaitEvent(st_tails, ev_fork, 0)) != cudaSuccess) return e;
-    {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st_tails;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = INF_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
-        e = cudaLaunchKernelEx(&cfg, k_inf_tails, (const uint16_t *)d_out16, d_out, d_dict, dict_n, nblocks, raw_n,
-                               (const uint32_t *)d_flags, d_err);
-        if (e != cudaSuccess) return e;
+    /* The decode goes first and waits for nobody.  B2D_INF_SERIAL: everything on one stream (chosen by the caller
+     * where kernels cannot overlap anyway); otherwise the serial pass over the tails starts right behind it on its
+     * own (high-priority) stream and follows the decode through d_flags. */
+    if (mode != B2D_INF_SERIAL) {
+        if ((e = cudaEventRecord(ev_fork, st)) != cudaSuccess) return e;          /* flags are cleared */
+        if ((e = cudaStreamWaitEvent(st_tails, ev_fork, 0)) != cudaSuccess) return e;
+    } else st_tails = st;
+    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st>>>(d_in, in_n, d_index, nblocks, raw_n,
+                                                                                              dict_n, d_out16, d_flags, d_err);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if ((e = launch_tails(d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err, st_tails)) != cudaSuccess) return e;
+    if (mode != B2D_INF_SERIAL) {
+        if ((e = cudaEventRecord(ev_join, st_tails)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(st, ev_join, 0)) != cudaSuccess) return e;
     }
-    if (!serial)
-        k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, nblocks, raw_n, dict_n,
-                                                                                    d_out16, d_flags, d_err);
-    if ((e = cudaEventRecord(ev_join, st_tails)) != cudaSuccess) return e;
-    if ((e = cudaStreamWaitEvent(st, ev_join, 0)) != cudaSuccess) return e;
     k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
     return cudaGetLastError();
 }

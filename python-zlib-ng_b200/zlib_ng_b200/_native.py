@@ -52,6 +52,9 @@ SIGNATURES = {
     "b2d_copy_h2d": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _u64]),
     "b2d_copy_d2h": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _u64]),
     "b2d_device_sync": (ctypes.c_int, [ctypes.c_void_p]),
+    "b2d_pinned_alloc": (ctypes.c_int, [_u64, _P(ctypes.c_void_p)]),
+    "b2d_pinned_free": (ctypes.c_int, [ctypes.c_void_p]),
+    "b2d_host_is_pinned": (ctypes.c_int, [ctypes.c_void_p]),
     "b2d_host_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, _u64, ctypes.c_int]),
     "b2d_launch_count": (_u64, [ctypes.c_void_p]),
     "b2d_block_index": (ctypes.c_int, [ctypes.c_void_p, _P(_u64), _u64, _P(_u64)]),
@@ -60,6 +63,14 @@ SIGNATURES = {
     "b2d_inflate_device": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64,
                                           _P(ctypes.c_float)]),
     "b2d_inflate_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _u64, _u8p, _u64, _u8p, _u64, _P(_u32)]),
+    "b2d_mctx_create": (ctypes.c_int, [_P(ctypes.c_int), ctypes.c_int, _u64, _P(ctypes.c_void_p)]),
+    "b2d_mctx_destroy": (None, [ctypes.c_void_p]),
+    "b2d_mctx_devices": (ctypes.c_int, [ctypes.c_void_p]),
+    "b2d_mctx_launch_count": (_u64, [ctypes.c_void_p]),
+    "b2d_deflate_host_multi": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _u8p, _u64, _u8p, _u64, ctypes.c_int,
+                                              _u8p, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u64), _u64, _P(_u64)]),
+    "b2d_compress_and_crc_multi": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
+                                                  _P(_u64), _P(_u32), _P(_u64), _u64, _P(_u64)]),
     "b2d_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "b2d_profile_read": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_double), _P(_u64), ctypes.c_int]),
 }
@@ -158,6 +169,57 @@ class Context:
         return int(lib().b2d_launch_count(self.handle))
 
 
+def pinned_alloc(n: int) -> int:
+    p = ctypes.c_void_p()
+    check(lib().b2d_pinned_alloc(n, ctypes.byref(p)))
+    return p.value
+
+
+def pinned_free(p: int) -> None:
+    check(lib().b2d_pinned_free(ctypes.c_void_p(p)))
+
+
+class MultiContext:
+    """Several GPU contexts working on one stream (b2d_mctx): batch j of a call runs on devices[j % len(devices)]."""
+
+    def __init__(self, devices, max_batch: int = 0):
+        self.devices = list(devices)
+        arr = (ctypes.c_int * len(self.devices))(*self.devices)
+        self._h = ctypes.c_void_p()
+        check(lib().b2d_mctx_create(arr, len(self.devices), max_batch, ctypes.byref(self._h)))
+        self.device = self.devices[0]         # where page-locked buffers of this context's users are allocated from
+
+    @property
+    def handle(self):
+        if not self._h:
+            raise ValueError("context is closed")
+        return self._h
+
+    def close(self):
+        if self._h:
+            lib().b2d_mctx_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def launch_count(self) -> int:
+        return int(lib().b2d_mctx_launch_count(self.handle))
+
+    def compress_and_crc(self, level, daddr, n, zaddr, zn, out_addr, out_cap, want_sizes=False):
+        """-> (out_n, crc, [compressed size of every 128 KiB block] or None); raises NativeError"""
+        out_n, crc, cnt = _u64(0), _u32(0), _u64(0)
+        nb = (n + 131071) // 131072
+        sizes = (_u64 * max(nb, 1))() if want_sizes else None
+        check(lib().b2d_compress_and_crc_multi(self.handle, level, daddr, n, zaddr if zn else None, zn, out_addr, out_cap,
+                                               ctypes.byref(out_n), ctypes.byref(crc), sizes, nb if want_sizes else 0,
+                                               ctypes.byref(cnt)))
+        return out_n.value, crc.value, (list(sizes[:nb]) if want_sizes else None)
+
+
 _default = {}
 _default_lock = threading.Lock()
 
@@ -188,8 +250,35 @@ def _addr(buf):
     if n == 0:
         return 0, 0, mv
     if mv.readonly:
-        import numpy as np
-        a = np.frombuffer(mv, dtype=np.uint8)
-        return a.ctypes.data, n, (a, mv)
+        # ctypes' from_buffer wants a writable export: ask the buffer protocol directly (PyObject_GetBuffer, what the
+        # reference does with "y*", zlib_ngmodule.c:1819) and release the view when the caller drops `keep`
+        view = _PyBuffer()
+        if ctypes.pythonapi.PyObject_GetBuffer(ctypes.py_object(mv), ctypes.byref(view), 0) != 0:   # PyBUF_SIMPLE
+            raise BufferError("object does not export a simple buffer")
+        return view.buf or 0, n, (_BufferHold(view), mv)
     c = (ctypes.c_char * n).from_buffer(mv)
     return ctypes.addressof(c), n, (c, mv)
+
+
+class _PyBuffer(ctypes.Structure):
+    """Py_buffer (cpython/object.h)"""
+    _fields_ = [("buf", ctypes.c_void_p), ("obj", ctypes.c_void_p), ("len", ctypes.c_ssize_t), ("itemsize", ctypes.c_ssize_t),
+                ("readonly", ctypes.c_int), ("ndim", ctypes.c_int), ("format", ctypes.c_char_p),
+                ("shape", ctypes.POINTER(ctypes.c_ssize_t)), ("strides", ctypes.POINTER(ctypes.c_ssize_t)),
+                ("suboffsets", ctypes.POINTER(ctypes.c_ssize_t)), ("internal", ctypes.c_void_p)]
+
+
+ctypes.pythonapi.PyObject_GetBuffer.argtypes = [ctypes.py_object, ctypes.POINTER(_PyBuffer), ctypes.c_int]
+ctypes.pythonapi.PyObject_GetBuffer.restype = ctypes.c_int
+ctypes.pythonapi.PyBuffer_Release.argtypes = [ctypes.POINTER(_PyBuffer)]
+ctypes.pythonapi.PyBuffer_Release.restype = None
+
+
+class _BufferHold:
+    def __init__(self, view):
+        self._view = view
+
+    def __del__(self):
+        if self._view is not None:
+            ctypes.pythonapi.PyBuffer_Release(ctypes.byref(self._view))
+            self._view = None

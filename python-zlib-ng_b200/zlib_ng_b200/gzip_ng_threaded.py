@@ -5,15 +5,22 @@
 reference's signature (gzip_ng_threaded.py:22-24).  What changes is what sits
 behind it.  The reference hands ``block_size`` pieces to N CPU threads, each
 calling ``compress_and_crc`` (gzip_ng_threaded.py:299-322, 361-380).  Here
-the writer gathers ``threads * block_size`` bytes straight into *pinned* host
-memory (the only host copy), and one submitter per GPU sends that batch through
-the kernels primed with the 32 KiB before it; the member's CRC is folded with
-crc32_combine exactly as the reference's writer thread does (:382-398).
-Header, terminator ``03 00`` and trailer are the reference's (:269-284,
-:324-338), including its header quirk of packing the OS byte before XFL.
+the writer gathers a batch of the caller's bytes straight into *pinned* host
+memory (the only host copy; none at all for buffers from ``pinned_buffer()``),
+and hands it to a multi-device context (``b2d_compress_and_crc_multi``): the
+batch is dealt over ``min(threads, GPUs)`` devices primed with the 32 KiB before
+each piece, the pieces come back in order in one buffer, and the member's CRC is
+folded with crc32_combine exactly as the reference's writer thread does
+(:382-398).  Header, terminator ``03 00`` and trailer are the reference's
+(:269-284, :324-338), including its header quirk of packing the OS byte before
+XFL.
 
-Reading is not on the accelerated path: "rb" goes to CPython's
-gzip module.
+What ``close()`` leaves on disk differs from the reference in one way: after the
+reference's two members come a few *empty* gzip members whose FEXTRA
+fields hold a block index (``B2D_WRITE_INDEX=0`` switches them off).  Every gzip
+reader skips them; this module's reader uses them to inflate the file on the
+GPU ("rb" mode).  BGZF files (``BC`` extra subfields) are read on the GPU as
+well; any other gzip stream goes to CPython's gzip module.
 """
 from __future__ import annotations
 
@@ -32,13 +39,13 @@ from . import _native, zlib_ng
 DEFLATE_WINDOW_SIZE = 2 ** 15
 _COMPRESS_LEVEL_TRADEOFF = 6
 _MIN_BATCH = 128 * 1024
-# What one GPU call covers.  The reference keeps threads * block_size bytes in flight; a GPU wants more
-# per launch, so batches grow to this size unless the caller asked for less than one 128 KiB device block in total
-# (then the reference's sizes, and its OverflowError on oversized blocks, are kept as they are).
+# What one native call covers, per GPU.  The reference keeps threads * block_size bytes in flight; a GPU wants more
+# per launch, so batches grow to this size (times the number of GPUs) unless the caller asked for less than one
+# 128 KiB device block in total (then the reference's sizes, and its OverflowError on oversized blocks, are kept).
 _STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
-# workers (each with its own GPU context and stream) per device: batch j+1's H2D and batch j-1's D2H
-# overlap batch j's kernels.  threads=N asks for min(N, this) of them.
-_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "4")), 1)
+# native calls in flight (each on its own multi-device context): call j+1's first H2D and call j-1's last D2H
+# overlap call j's kernels.  Inside a call the library already pipelines 3 slots x 2 lanes per device.
+_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "2")), 1)
 _COPY_CHUNK = 4 << 20
 # Block index (for the GPU reader): one data member, then the empty member the reference's close() leaves
 # (gzip_ng_threaded.py:340-355), then empty members whose FEXTRA field ("B2" subfields, RFC 1952 2.3.1.1) lists
@@ -89,29 +96,81 @@ def _parallel_copy(dst_addr: int, src, nbytes: int) -> None:
 
 
 class _PinnedPool:
-    """Page-locked host buffers are expensive to create (the driver pins every page), so writers hand
-    them back here instead of freeing them; they live until the process exits."""
+    """Page-locked host buffers are expensive to create (the driver pins every page), so writers and readers hand
+    them back here instead of freeing them.  At most _POOL_KEEP bytes stay pooled; what comes back beyond that is
+    freed (one writer on one GPU uses about 0.5 GiB: 3 input batches and 3 output buffers of 64 MiB and up)."""
 
     def __init__(self):
         self._lock = threading.Lock()
         self._free = {}
+        self._kept = 0
 
-    def get(self, ctx, size):
-        key = (ctx.device, size)
+    def get(self, size):
         with self._lock:
-            lst = self._free.get(key)
+            lst = self._free.get(size)
             if lst:
+                self._kept -= size
                 return lst.pop()
-        ptr = ctx.host_alloc(size)
+        ptr = _native.pinned_alloc(size)
         view = memoryview((ctypes.c_char * size).from_address(ptr)).cast("B")
         return ptr, view
 
-    def put(self, ctx, size, ptr, view):
+    def put(self, size, ptr, view):
         with self._lock:
-            self._free.setdefault((ctx.device, size), []).append((ptr, view))
+            if self._kept + size <= _POOL_KEEP:
+                self._kept += size
+                self._free.setdefault(size, []).append((ptr, view))
+                return
+        view.release()
+        _native.pinned_free(ptr)
 
 
+_POOL_KEEP = int(os.environ.get("B2D_PINNED_POOL_MIB", "4096")) << 20
 _pinned_pool = _PinnedPool()
+
+
+class PinnedBuffer:
+    """Page-locked host memory a caller can produce its data into: ``write()`` of (a slice of) such a buffer goes to
+    the GPUs by DMA straight from it, without the writer's copy into its own pinned batch.  Supports the buffer
+    protocol through ``.view`` (a writable memoryview of bytes) and ``numpy.frombuffer(buf.view, ...)``.
+    The reference has no counterpart: its write() always copies (``data = bytes(b)``, gzip_ng_threaded.py:315)."""
+
+    def __init__(self, nbytes: int):
+        self.nbytes = int(nbytes)
+        self._ptr = _native.pinned_alloc(max(self.nbytes, 1))
+        self.view = memoryview((ctypes.c_char * max(self.nbytes, 1)).from_address(self._ptr)).cast("B")[:self.nbytes]
+
+    @property
+    def address(self) -> int:
+        return self._ptr
+
+    def close(self):
+        if self._ptr:
+            try:
+                self.view.release()
+            except BufferError:
+                raise BufferError("PinnedBuffer.close(): views of the buffer are still exported") from None
+            _native.pinned_free(self._ptr)
+            self._ptr = 0
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            if self._ptr:
+                _native.pinned_free(self._ptr)
+                self._ptr = 0
+        except Exception:
+            pass
+
+
+def pinned_buffer(nbytes: int) -> PinnedBuffer:
+    """A page-locked buffer of nbytes (see PinnedBuffer): data written from it is not copied on the host."""
+    return PinnedBuffer(nbytes)
 
 
 def open(filename, mode="rb", compresslevel=_COMPRESS_LEVEL_TRADEOFF, encoding=None, errors=None, newline=None,
@@ -309,12 +368,12 @@ class _ThreadedGzipReader(io.RawIOBase):
         g["pinned"] = []
         g["free"], g["ready"], g["comp_free"], g["comp_ready"], g["stop"] = queue.Queue(), queue.Queue(), queue.Queue(), queue.Queue(), False
         for _ in range(2 if several else 1):
-            ent = (ctx, win_comp + 16) + _pinned_pool.get(ctx, win_comp + 16)
+            ent = (win_comp + 16,) + _pinned_pool.get(win_comp + 16)
             g["pinned"].append(ent)
-            g["comp_free"].put(ent[2:])
-            ent = (ctx, win_raw + 16) + _pinned_pool.get(ctx, win_raw + 16)
+            g["comp_free"].put(ent[1:])
+            ent = (win_raw + 16,) + _pinned_pool.get(win_raw + 16)
             g["pinned"].append(ent)
-            g["free"].put(ent[2:])
+            g["free"].put(ent[1:])
         g["cur"], g["cur_n"], g["off"], g["eof"] = None, 0, 0, False
         g["threads"] = [threading.Thread(target=self._gpu_file_reader, daemon=True),
                         threading.Thread(target=self._gpu_worker, daemon=True)]
@@ -328,8 +387,8 @@ class _ThreadedGzipReader(io.RawIOBase):
         g["stop"] = True
         for t in g["threads"]:
             t.join()
-        for ctx, size, ptr, view in g["pinned"]:
-            _pinned_pool.put(ctx, size, ptr, view)
+        for size, ptr, view in g["pinned"]:
+            _pinned_pool.put(size, ptr, view)
         g["pinned"] = []
 
     def readinto(self, b):
@@ -422,16 +481,15 @@ class FlushableBufferedWriter(io.BufferedWriter):
 class _PinnedBuffer:
     """[32 KiB dictionary area | batch bytes] in page-locked host memory."""
 
-    def __init__(self, ctx, batch):
-        self.ctx = ctx
+    def __init__(self, batch):
         self.size = DEFLATE_WINDOW_SIZE + batch
-        self.ptr, self.view = _pinned_pool.get(ctx, self.size)
+        self.ptr, self.view = _pinned_pool.get(self.size)
         self.fill = 0          # data bytes
         self.dict_n = 0        # dictionary bytes stored right before the data
 
     def free(self):
         if self.ptr:
-            _pinned_pool.put(self.ctx, self.size, self.ptr, self.view)
+            _pinned_pool.put(self.size, self.ptr, self.view)
             self.ptr, self.view = 0, None
 
 
@@ -454,15 +512,16 @@ class _ThreadedGzipWriter(io.RawIOBase):
         self._zlevel = zlib_ng._level(level)          # raises zlib_ng.error("Bad compression level")
         self.block_size = block_size
         self.threads = threads
-        devices = _devices()
-        # workers = (device, slot) pairs, each with its own GPU context: the counterpart of the
-        # reference's N compression threads (gzip_ng_threaded.py:233-246), round-robin like them
-        depth = min(threads, _STREAM_DEPTH)
-        self._contexts = [_context_for(d, slot) for slot in range(depth) for d in devices]
+        # The reference's N compression threads (gzip_ng_threaded.py:233-246) become min(N, GPUs) devices behind
+        # one multi-device context; `depth` such contexts take batches round-robin so that consecutive native
+        # calls overlap (what is left of N after one worker per GPU, at most _STREAM_DEPTH).
+        devices = _devices(threads)
+        depth = max(1, min(threads // len(devices), _STREAM_DEPTH))
+        self._contexts = [_multi_context_for(devices, slot) for slot in range(depth)]
         nw = len(self._contexts)
-        # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece
+        # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece per device
         nominal = max(block_size * threads // nw, 1)
-        self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, _STREAM_BATCH)
+        self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, _STREAM_BATCH * len(devices))
         self._out_cap = self.batch + max(self.batch // 10, 500)
         self.input_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)]
         self.output_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)] if nw > 1 else []
@@ -561,7 +620,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
                 break
             except queue.Empty:
                 if len(self._buffers) < self._max_buffers:       # pinned input buffers are created on demand
-                    buf = _PinnedBuffer(self._contexts[len(self._buffers) % len(self._contexts)], self.batch)
+                    buf = _PinnedBuffer(self.batch)
                     self._buffers.append(buf)
                     break
                 with self.lock:
@@ -592,7 +651,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
         self._last_tail = bytes(both[-DEFLATE_WINDOW_SIZE:])
         worker = self.index % len(self.input_queues)
         self.index += 1
-        self.input_queues[worker].put((data, zdict, buf))
+        self._put_job(worker, (data, zdict, buf))
 
     def write(self, b) -> int:
         self._check_closed()
@@ -603,6 +662,8 @@ class _ThreadedGzipWriter(io.RawIOBase):
         if mv.ndim != 1 or mv.format != "B":
             mv = mv.cast("B")
         length = mv.nbytes
+        if length >= self.batch and self.batch >= _MIN_BATCH and self._write_pinned(mv):
+            return length
         pos = 0
         while pos < length:
             if self._cur is None:
@@ -619,6 +680,54 @@ class _ThreadedGzipWriter(io.RawIOBase):
             if buf.fill == self.batch:
                 self._submit_current()
         return length
+
+    def _write_pinned(self, mv) -> bool:
+        """A large write from page-locked memory (pinned_buffer(), or any cudaHostAlloc'ed / registered memory) is
+        not gathered into the writer's own pinned batches: its pieces go to the workers as they lie, and the call
+        returns once they are compressed (the caller may reuse the buffer as soon as write() returns, as with any
+        file object)."""
+        addr, n, keep = _native._addr(mv)
+        try:
+            if not _native.lib().b2d_host_is_pinned(addr) or not _native.lib().b2d_host_is_pinned(addr + n - 1):
+                return False
+            if self._cur is not None and self._cur.fill % _DEVICE_BLOCK:
+                return False          # the stream would no longer consist of whole device blocks: gather as usual
+            self._submit_current()
+            pos = 0
+            while pos < n:
+                # whole device blocks, except at the very end of the write
+                k = min(self.batch, n - pos)
+                data = mv[pos:pos + k]
+                if pos >= DEFLATE_WINDOW_SIZE:
+                    zdict = mv[pos - DEFLATE_WINDOW_SIZE:pos]
+                else:
+                    zdict = (self._last_tail + bytes(mv[:pos]))[-DEFLATE_WINDOW_SIZE:]
+                worker = self.index % len(self.input_queues)
+                self.index += 1
+                self._put_job(worker, (data, zdict, None))
+                pos += k
+            self._last_tail = (self._last_tail + bytes(mv[-DEFLATE_WINDOW_SIZE:]))[-DEFLATE_WINDOW_SIZE:]
+            for q in list(self.input_queues) + list(self.output_queues):
+                self._join(q)
+            with self.lock:
+                if self.exception:
+                    raise self.exception
+            return True
+        finally:
+            del keep
+
+    def _put_job(self, worker, job):
+        q = self.input_queues[worker]
+        while True:
+            try:
+                q.put(job, timeout=0.05)
+                return
+            except queue.Full:
+                with self.lock:
+                    if self.exception:
+                        raise self.exception
+                if not self.running:
+                    raise ValueError("writer is not running")
 
     def _end_gzip_stream(self):
         self._check_closed()
@@ -687,29 +796,22 @@ class _ThreadedGzipWriter(io.RawIOBase):
         data, zdict = job[0], job[1]
         daddr, n, k1 = _native._addr(data)
         zaddr, zn, k2 = _native._addr(zdict)
-        out_n = ctypes.c_uint64(0)
-        crc = ctypes.c_uint32(0)
-        ctx = self._contexts[index]
-        nb = (n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK
-        offs, cnt = None, ctypes.c_uint64(0)
-        if self._indexing:
-            # compress and fetch the block offsets in one call: contexts are shared by every writer of the process
-            offs = (ctypes.c_uint64 * (nb + 1))()
-            rc = _native.lib().b2d_compress_and_crc_indexed(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
-                                                            out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc),
-                                                            offs, nb + 1, ctypes.byref(cnt))
-        else:
-            rc = _native.lib().b2d_compress_and_crc(ctx.handle, self._zlevel, daddr, n, zaddr if zn else None, zn,
-                                                    out_buf.ptr, self._out_cap, ctypes.byref(out_n), ctypes.byref(crc))
-        del k1, k2
-        if rc == _native.B2D_BUF_ERROR:
-            raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}")
-        if rc:
-            zlib_ng._raise(rc, "while compressing data")
-        sizes = None
-        if offs is not None and cnt.value == nb + 1 and offs[nb] == out_n.value:
-            sizes = [offs[i + 1] - offs[i] for i in range(nb)]
-        return out_buf.view[:out_n.value], crc.value, n, sizes
+        try:
+            # one stream over the context's devices; the block sizes come back with the call (contexts are shared
+            # by every writer of the process, so they cannot be asked for afterwards)
+            out_n, crc, sizes = self._contexts[index].compress_and_crc(self._zlevel, daddr, n, zaddr, zn, out_buf.ptr,
+                                                                       self._out_cap, want_sizes=self._indexing)
+        except _native.NativeError as e:
+            if e.code == _native.B2D_BUF_ERROR:
+                raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}") from None
+            if e.code == _native.B2D_MEM_ERROR:
+                raise MemoryError(e.msg) from None
+            raise zlib_ng.error(f"Error {e.code} while compressing data: {e.msg[:200]}") from None
+        finally:
+            del k1, k2
+        if sizes is not None and sum(sizes) != out_n:
+            sizes = None
+        return out_buf.view[:out_n], crc, n, sizes
 
     def _release(self, job):
         if len(job) > 2 and job[2] is not None:
@@ -717,7 +819,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
 
     def _compress_and_write(self):
         in_queue = self.input_queues[0]
-        out_buf = _OutBuffer(self._contexts[0], self._out_cap)
+        out_buf = _OutBuffer(self._out_cap)
         try:
             while True:
                 try:
@@ -750,7 +852,7 @@ class _ThreadedGzipWriter(io.RawIOBase):
         out_queue = self.output_queues[index]
         # two pinned output buffers per worker: the writer thread owns one while the next batch fills the other
         spare = queue.Queue()
-        bufs = [_OutBuffer(self._contexts[index], self._out_cap) for _ in range(2)]
+        bufs = [_OutBuffer(self._out_cap) for _ in range(2)]
         for b in bufs:
             spare.put(b)
         try:
@@ -836,32 +938,43 @@ class _ThreadedGzipWriter(io.RawIOBase):
 
 
 class _OutBuffer:
-    def __init__(self, ctx, cap):
-        self.ctx = ctx
+    def __init__(self, cap):
         self.cap = max(cap, 16)
-        self.ptr, self.view = _pinned_pool.get(ctx, self.cap)
+        self.ptr, self.view = _pinned_pool.get(self.cap)
 
     def free(self):
         if self.ptr:
-            _pinned_pool.put(self.ctx, self.cap, self.ptr, self.view)
+            _pinned_pool.put(self.cap, self.ptr, self.view)
             self.ptr, self.view = 0, None
 
 
-_ctx_lock = threading.Lock()
-_ctx_by_device = {}
+_mctx_lock = threading.Lock()
+_mctx = {}
 
 
-def _devices():
-    """GPUs the writer spreads batches over: B2D_DEVICES="0,1,…" or "all"; default device 0."""
-    spec = os.environ.get("B2D_DEVICES", "0").strip()
+def _devices(threads: int):
+    """GPUs one writer spreads its batches over.  The reference's ``threads`` asks for that many compression
+    workers; a worker here is a GPU, so min(threads, GPUs present) of them are used.  B2D_DEVICES="0,1,..." names the
+    candidates (default: all devices the process can see)."""
+    spec = os.environ.get("B2D_DEVICES", "all").strip()
     if spec == "all":
-        n = _native.lib().b2d_device_count()
-        return list(range(max(n, 1)))
-    return [int(x) for x in spec.split(",") if x.strip() != ""] or [0]
+        cand = list(range(max(_native.lib().b2d_device_count(), 1)))
+    else:
+        cand = [int(x) for x in spec.split(",") if x.strip() != ""] or [0]
+    return cand[:max(threads, 1)]
 
 
-def _context_for(device: int, slot: int = 0):
-    try:
-        return _native.default_context(device, slot)
-    except _native.NativeError as e:
-        raise zlib_ng.error(f"Error {e.code} while opening the B200 device: {e.msg}") from None
+def _multi_context_for(devices, slot: int = 0):
+    """Process-wide multi-device contexts, created on first use and shared by every writer of the process."""
+    key = (tuple(devices), slot)
+    m = _mctx.get(key)
+    if m is None:
+        with _mctx_lock:
+            m = _mctx.get(key)
+            if m is None:
+                try:
+                    m = _native.MultiContext(devices, _STREAM_BATCH)
+                except _native.NativeError as e:
+                    raise zlib_ng.error(f"Error {e.code} while opening the B200 device: {e.msg}") from None
+                _mctx[key] = m
+    return m

@@ -96,6 +96,14 @@ def reference():
         return None
 
 
+def reference_pkg():
+    """(zlib_ng, gzip_ng, gzip_ng_threaded) of the real reference (oracle/_ref), or None if absent."""
+    if reference() is None:
+        return None
+    from zlib_ng import gzip_ng, gzip_ng_threaded, zlib_ng  # type: ignore
+    return zlib_ng, gzip_ng, gzip_ng_threaded
+
+
 def golden(name):
     with open(os.path.join(GOLDEN, name)) as f:
         return json.load(f)

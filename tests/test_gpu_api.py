@@ -422,16 +422,118 @@ def test_program_can_exit_on_error(tmp_path):
     assert r.returncode == 1 and b"Exception: Error" in r.stderr
 
 
-def test_two_devices_round_robin_if_present(gzt, tmp_path, monkeypatch):
+@pytest.mark.parametrize("devices", ["0,0", "0,0,0", "0,1"])
+def test_one_file_over_several_gpu_contexts(gzt, tmp_path, monkeypatch, devices):
+    """The writer's multi-device path.  "0,0" puts two contexts on device 0, so a one-GPU box runs the same
+    shard / concatenate / crc32_combine code as a box with several GPUs ("0,1" when there are two)."""
     from zlib_ng_b200 import _native
-    if _native.lib().b2d_device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    monkeypatch.setenv("B2D_DEVICES", "0,1")
-    data = synthdata.make("mixed", 6_000_000, 9).tobytes()
+    if devices == "0,1" and _native.lib().b2d_device_count() < 2:
+        pytest.skip("one GPU on this box")
+    monkeypatch.setenv("B2D_DEVICES", devices)
+    monkeypatch.setattr(gzt, "_STREAM_BATCH", 8 << 20)
+    data = synthdata.make("mixed", 70_000_000, 9).tobytes()
     p = tmp_path / "m.gz"
-    with gzt.open(p, "wb", threads=4, block_size=256 * 1024) as f:
+    with gzt.open(p, "wb", threads=8, block_size=1 << 20) as f:
+        assert len(f.raw._contexts[0].devices) == len(devices.split(","))
+        for off in range(0, len(data), 9_000_001):
+            f.write(data[off:off + 9_000_001])
+    blob = p.read_bytes()
+    assert gzip.decompress(blob) == data
+    # the same bytes as one context on one device writes: sharding does not change the stream
+    monkeypatch.setenv("B2D_DEVICES", "0")
+    q = tmp_path / "one.gz"
+    with gzt.open(q, "wb", threads=8, block_size=1 << 20) as f:
         f.write(data)
-    assert gzip.decompress(p.read_bytes()) == data
+    assert q.read_bytes() == blob
+    with gzt.open(p, "rb") as f:
+        assert f.raw._gpu is not None and f.read() == data
+
+
+@pytest.mark.parametrize("index", ["1", "0"])
+def test_written_files_read_back_through_the_reference(gzt, fastq, tmp_path, monkeypatch, index):
+    """north_star: "zlib_ng.decompress (the reference) must round-trip every output bit-exactly".  The reference's own
+    reader (_GzipReader behind gzip_ng_threaded.open(..., "rb"), zlib_ngmodule.c:2426-2637, CRC / ISIZE check
+    :2581-2599) and gzip_ng.decompress read what this writer wrote, with the block index and without
+    (the reference's writer test decodes the same way: tests/test_gzip_ng_threaded.py:32-50)."""
+    from helpers import reference_pkg
+    ref = reference_pkg()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    ref_zlib, ref_gzip, ref_gzt = ref
+    monkeypatch.setattr(gzt, "_WRITE_INDEX", index == "1")
+    data = fastq * 3
+    p = tmp_path / "r.gz"
+    for level in (1, 6, 9):
+        with gzt.open(p, "wb", compresslevel=level, threads=3, block_size=512 * 1024) as f:
+            f.write(data)
+        with ref_gzt.open(p, "rb") as f:
+            assert f.read() == data
+        assert ref_gzip.decompress(p.read_bytes()) == data
+    with gzt.open(p, "wb", threads=2) as f:
+        f.write(data[:1000])
+        f.flush()
+        f.write(data[1000:])
+    with ref_gzt.open(p, "rb") as f:
+        assert f.read() == data
+
+
+def test_reference_decoder_on_every_api(zng, fastq):
+    """The reference's zlib_ng.decompress / decompressobj as the decoder of compress(), compressobj() and
+    compress_and_crc() output (all 21 wbits forms, zdict, flush modes)."""
+    from helpers import reference
+    ref = reference()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    for wbits in WBITS:
+        for level in (1, 6):
+            assert ref.decompress(zng.compress(fastq, level, wbits), wbits=wbits) == fastq
+    zdict = fastq[:20_000]
+    co = zng.compressobj(6, zng.DEFLATED, -15, zdict=zdict)
+    blob = co.compress(fastq) + co.flush()
+    assert ref.decompressobj(-15, zdict=zdict).decompress(blob) == fastq
+    for mode in (zng.Z_SYNC_FLUSH, zng.Z_FULL_FLUSH, zng.Z_PARTIAL_FLUSH, zng.Z_BLOCK):
+        co = zng.compressobj(6)
+        blob = co.compress(fastq[:100_000]) + co.flush(mode) + co.compress(fastq[100_000:]) + co.flush()
+        assert ref.decompress(blob) == fastq
+    pc = zng._ParallelCompress(len(fastq) + len(fastq) // 10 + 500, 6)
+    out, crc = pc.compress_and_crc(fastq, zdict)
+    d = ref.decompressobj(-15, zdict=zdict)
+    assert d.decompress(out + b"\x03\x00") == fastq and crc == ref.crc32(fastq)
+
+
+def test_pinned_buffer_writes_are_not_copied_and_give_the_same_file(gzt, tmp_path, monkeypatch):
+    monkeypatch.setattr(gzt, "_STREAM_BATCH", 8 << 20)
+    data = synthdata.make("mixed", 40_000_000, 19).tobytes()
+    a, b = tmp_path / "a.gz", tmp_path / "b.gz"
+    with gzt.open(a, "wb", threads=4) as f:
+        f.write(data)
+    with gzt.pinned_buffer(len(data)) as pb:
+        pb.view[:] = data
+        with gzt.open(b, "wb", threads=4) as f:
+            copies = []
+            monkeypatch.setattr(gzt, "_parallel_copy", lambda *args: copies.append(args) or gzt._native.check(-2))
+            assert f.write(pb.view) == len(data)
+        assert not copies                                   # nothing went through the gather copy
+    assert b.read_bytes() == a.read_bytes()
+    assert gzip.decompress(b.read_bytes()) == data
+    # a pinned write after an unaligned pageable one falls back to the gather path, and the other way round
+    monkeypatch.undo()
+    monkeypatch.setattr(gzt, "_STREAM_BATCH", 8 << 20)
+    c = tmp_path / "c.gz"
+    with gzt.pinned_buffer(20_000_000) as pb:
+        pb.view[:] = data[5:20_000_005]
+        with gzt.open(c, "wb", threads=4) as f:
+            f.write(data[:5])
+            f.write(pb.view)
+            f.write(data[20_000_005:])
+    assert gzip.decompress(c.read_bytes()) == data
+    d = tmp_path / "d.gz"
+    with gzt.pinned_buffer(16 << 20) as pb:
+        pb.view[:] = data[:16 << 20]
+        with gzt.open(d, "wb", threads=4) as f:
+            f.write(pb.view)
+            f.write(data[16 << 20:])
+    assert d.read_bytes() == a.read_bytes()
 
 
 # ---------------------------------------------------------------- gzip_ng

@@ -295,3 +295,81 @@ def test_gzip_ng_decompress_of_indexed_data(gzt):
     r.close()
     assert gzip_ng.decompress(blob) == data
     assert gzip_ng.decompress(gzip.compress(data[:1000])) == data[:1000]        # no index: CPython
+
+
+def test_failed_block_never_leaves_stale_symbols_behind(nat):
+    """the 16-bit symbol scratch is reused across calls.  A dictionary-primed inflate leaves markers
+    below 32768 in it; a later call WITHOUT a dictionary whose block 0 fails part-way must not resolve those stale
+    markers (it used to read dict[-32768 + k] from a null pointer: a sticky illegal address).  The context must
+    report bad data and go on working."""
+    L = nat.lib()
+    c = nat.Context(0, 8 << 20)
+    try:
+        rng = np.random.default_rng(9)
+        period = rng.integers(32, 127, 30_000, dtype=np.uint8).tobytes()
+        zdict = period[-20_000:]
+        data = period * 12                       # nearly every symbol of block 0 refers into the dictionary
+        stream, offs, d_buf, d_out, _ = deflate_indexed(nat, c, data, 6, zdict)
+        try:
+            back = inflate_device(nat, c, d_out, len(stream), offs, d_buf, len(zdict), len(data))
+            assert back == data
+        finally:
+            c.device_free(d_buf)
+            c.device_free(d_out)
+        # same size, no dictionary, block 0 damaged right after its first header
+        plain = synthdata.make("mixed", len(data), 61).tobytes()
+        stream2, offs2, d_buf2, d_out2, _ = deflate_indexed(nat, c, plain, 6)
+        c.device_free(d_buf2)
+        c.device_free(d_out2)
+        nb = len(offs2) - 1
+        arr = (ctypes.c_uint64 * nb)(*offs2[:nb])
+        out = ctypes.create_string_buffer(len(plain))
+        for cut in (40, 200, 5000):
+            bad = bytearray(stream2)
+            bad[cut:cut + 64] = b"\xff" * 64
+            rc = L.b2d_inflate_host(c.handle, bytes(bad), len(bad), arr, nb, None, 0, out, len(plain), None)
+            assert rc == -3 or out.raw != plain              # detected (or, at worst, different bytes: the CRC catches it)
+        # the context still works: nothing sticky happened on the device
+        nat.check(L.b2d_inflate_host(c.handle, stream2, len(stream2), arr, nb, None, 0, out, len(plain), None))
+        assert out.raw == plain
+    finally:
+        c.close()
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("env", [{"CUDA_LAUNCH_BLOCKING": "1"}, {"B2D_INF_SERIAL": "1"}, {}])
+def test_inflate_does_not_depend_on_two_kernels_running_at_once(tmp_path, env):
+    """the pass over the tails used to be launched first and to wait for a decode kernel that, when
+    launches are serialised (CUDA_LAUNCH_BLOCKING=1, profilers), could not start: 20 s of spinning, then a false
+    Z_DATA_ERROR.  Now the decode goes first and waits for nobody; a valid file reads correctly, and fast, however
+    kernels are scheduled."""
+    import os
+    import subprocess
+    import sys
+    import time
+    code = r'''
+import sys, time
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import synthdata
+from zlib_ng_b200 import gzip_ng_threaded as gzt
+data = synthdata.make("mixed", 6_000_000, 71).tobytes()
+with gzt.open(sys.argv[3], "wb", threads=2) as f:
+    f.write(data)
+t0 = time.perf_counter()
+with gzt.open(sys.argv[3], "rb") as f:
+    assert f.raw._gpu is not None
+    back = f.read()
+dt = time.perf_counter() - t0
+assert back == data
+print("READ_SECONDS", dt)
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ)
+    e.update(env)
+    t0 = time.perf_counter()
+    p = subprocess.run([sys.executable, "-c", code, root, os.path.join(root, "python-zlib-ng_b200"), str(tmp_path / "f.gz")],
+                       env=e, capture_output=True, text=True, timeout=100)
+    assert p.returncode == 0, p.stderr[-2000:]
+    secs = float(p.stdout.split("READ_SECONDS")[1].split()[0])
+    assert secs < 2.0, f"reading took {secs:.2f} s"
+    del t0
