@@ -8,10 +8,13 @@
  * independent given the raw input).
  */
 #include <cuda_runtime.h>
+#include <sys/mman.h>
 #include <condition_variable>
+#include <map>
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <chrono>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -41,9 +44,70 @@ extern "C" uint64_t b2d_deflate_bound(uint64_t n) {
     return n + 5 * nsub + 5 * (nblk ? nblk : 1) + 2 + 8;
 }
 
+/* ---- page-locked host memory ------------------------------------------------------------------------------
+ * cudaHostAlloc pins fresh pages at ~2.7 GB/s on the test box (it faults and pins them 4 KiB at a time on one thread):
+ * 1.6 GiB of staging per GPU would cost the first call of a process 0.6 s.  Memory that is mapped with transparent huge
+ * pages, touched by several threads and then registered is ready 5-6 times faster (tools/pin_probe.cu: 15 GB/s), and
+ * DMA treats it like any other page-locked memory.  Falls back to cudaHostAlloc where registering is refused. */
+static std::mutex g_pin_mu;
+static std::map<void *, size_t> g_pin_mapped;          /* blocks that came from mmap + cudaHostRegister */
+
+static cudaError_t pinned_alloc(void **p, size_t bytes) {
+    if (bytes == 0) bytes = 1;
+    const size_t huge = 2ull << 20;
+    const size_t len = (bytes + huge - 1) / huge * huge;
+    if (len >= (8ull << 20)) {
+        void *m = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (m != MAP_FAILED) {
+            madvise(m, len, MADV_HUGEPAGE);
+            {   /* first touch on several threads */
+                unsigned nt = (unsigned)(len / (32ull << 20));
+                if (nt < 1) nt = 1;
+                if (nt > 8) nt = 8;
+                std::thread th[8];
+                const size_t per = (len / nt + huge - 1) / huge * huge;
+                for (unsigned i = 0; i < nt; ++i)
+                    th[i] = std::thread([=] {
+                        const size_t o = (size_t)i * per;
+                        const size_t k = o >= len ? 0 : (len - o < per ? len - o : per);
+                        for (size_t q = 0; q < k; q += 4096) ((volatile char *)m)[o + q] = 0;
+                    });
+                for (unsigned i = 0; i < nt; ++i) th[i].join();
+            }
+            if (cudaHostRegister(m, len, cudaHostRegisterPortable) == cudaSuccess) {
+                std::lock_guard<std::mutex> g(g_pin_mu);
+                g_pin_mapped[m] = len;
+                *p = m;
+                return cudaSuccess;
+            }
+            cudaGetLastError();
+            munmap(m, len);
+        }
+    }
+    return cudaHostAlloc(p, bytes, cudaHostAllocPortable);
+}
+static cudaError_t pinned_free(void *p) {
+    if (!p) return cudaSuccess;
+    size_t len = 0;
+    {
+        std::lock_guard<std::mutex> g(g_pin_mu);
+        auto it = g_pin_mapped.find(p);
+        if (it != g_pin_mapped.end()) { len = it->second; g_pin_mapped.erase(it); }
+    }
+    if (len) {
+        cudaError_t e = cudaHostUnregister(p);
+        munmap(p, len);
+        return e;
+    }
+    return cudaFreeHost(p);
+}
+
 #define PROF_BATCHES 64
 #ifndef B2D_NLANE
-#define B2D_NLANE 2     /* batches of one call in flight on the device, each on its own stream with its own intermediates */
+#define B2D_NLANE 4     /* batches of one call in flight on the device, each on its own stream with its own intermediates.  The
+                         * chain stage runs one warp per 128 KiB block, so a batch of 64 MiB fills a quarter of the device's warp
+                         * slots: four lanes of 64 MiB do what two of 256 MiB do (profiles/ab_lanes_r2.log) with a quarter of the
+                         * memory and of the pipeline's fill and drain time */
 #endif
 #define B2D_NSLOT (B2D_NLANE + 1)   /* input/output slots of the host pipeline: one more than compute lanes */
 /* per-batch intermediates of the kernel pipeline.  Two of them ("lanes") let consecutive batches of one
@@ -84,7 +148,7 @@ struct b2d_ctx {
     cudaEvent_t ev_scan[B2D_NLANE], ev_fork, ev_join[B2D_NLANE];
     uint64_t *d_total;                      /* running output byte offset of a call           */
     uint64_t *h_total;                      /* pinned                                         */
-    uint8_t *h_stage; uint64_t h_stage_cap; /* pinned staging for pageable host buffers       */
+    uint8_t *h_stage; uint64_t h_stage_cap, h_stage_max; /* pinned staging for pageable host buffers (one-batch calls) */
     b2d_cksum_ws *ck;
     /* second slot + copy streams: lets b2d_deflate_host overlap H2D(j+1), kernels(j) and D2H(j-1) */
     uint8_t *d_inx[B2D_NSLOT - 1], *d_outx[B2D_NSLOT - 1];      /* slots 1.. (slot 0 = d_in / d_out / d_total / ck) */
@@ -131,11 +195,11 @@ static void ctx_free(b2d_ctx *c) {
         if (c->ev_comp[i]) cudaEventDestroy(c->ev_comp[i]);
         if (c->ev_out[i]) cudaEventDestroy(c->ev_out[i]);
     }
-    for (int i = 0; i < B2D_NSLOT; ++i) { if (c->h_in_s[i]) cudaFreeHost(c->h_in_s[i]); if (c->h_out_s[i]) cudaFreeHost(c->h_out_s[i]); }
+    for (int i = 0; i < B2D_NSLOT; ++i) { pinned_free(c->h_in_s[i]); pinned_free(c->h_out_s[i]); }
     if (c->st_in) cudaStreamDestroy(c->st_in);
     if (c->st_out) cudaStreamDestroy(c->st_out);
     if (c->h_total) cudaFreeHost(c->h_total);
-    if (c->h_stage) cudaFreeHost(c->h_stage);
+    pinned_free(c->h_stage);
     b2d_cksum_ws_destroy(c->ck);
     for (int i = 0; i < PROF_BATCHES; ++i) for (int j = 0; j <= B2D_NSTAGE; ++j) if (c->pev[i][j]) cudaEventDestroy(c->pev[i][j]);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -144,9 +208,22 @@ static void ctx_free(b2d_ctx *c) {
     delete c;
 }
 
+/* B2D_TRACE=1: where the time of creating a context goes, on stderr (cold-start work) */
+struct init_trace {
+    bool on; std::chrono::steady_clock::time_point t;
+    init_trace() : on(getenv("B2D_TRACE") && getenv("B2D_TRACE")[0] == '1'), t(std::chrono::steady_clock::now()) {}
+    void mark(const char *what, int device) {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[b2d] device %d: %-28s %7.1f ms\n", device, what, std::chrono::duration<double, std::milli>(now - t).count());
+        t = now;
+    }
+};
+
 extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     if (!out) return fail(B2D_STREAM_ERROR, "null out pointer");
     *out = nullptr;
+    init_trace tr;
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
@@ -155,7 +232,10 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     if (max_batch == 0) max_batch = 256ull << 20;
     max_batch = align_up(max_batch, B2D_BLOCK);
     if (max_batch > (2048ull << 20)) return fail(B2D_STREAM_ERROR, "max_batch above 2 GiB");
+    tr.mark("cudaGetDeviceCount (cuInit)", device);
     if ((e = cudaSetDevice(device)) != cudaSuccess) return fail_cuda(e, "cudaSetDevice");
+    if ((e = cudaFree(nullptr)) != cudaSuccess) return fail_cuda(e, "primary context");
+    tr.mark("primary context", device);
     b2d_ctx *c = new b2d_ctx();
     c->device = device; c->max_batch = max_batch; c->st = nullptr; c->ev0 = c->ev1 = nullptr;
 #define CC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { int rc_ = fail_cuda(e_, #x); ctx_free(c); return rc_; } } while (0)
@@ -163,17 +243,22 @@ extern "C" int b2d_ctx_create(int device, uint64_t max_batch, b2d_ctx **out) {
     CC(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
     CC(cudaEventCreate(&c->ev0)); CC(cudaEventCreate(&c->ev1));
     CC(b2d_kernels_init());
+    tr.mark("stream, events, kernel attrs", device);
     c->d_in_cap = B2D_WINDOW + max_batch + 1024;
     c->d_out_cap = align_up(b2d_deflate_bound(max_batch), 256);
     CC(cudaMalloc(&c->d_in, c->d_in_cap));
     CC(cudaMalloc(&c->d_out, c->d_out_cap));
     CC(work_alloc(&c->wk[0], max_batch));
     CC(cudaMalloc(&c->d_total, sizeof(uint64_t)));
-    CC(cudaMallocHost(&c->h_total, (B2D_NSLOT + 1) * sizeof(uint64_t)));
-    c->h_stage_cap = (B2D_WINDOW + max_batch) > c->d_out_cap ? (B2D_WINDOW + max_batch) : c->d_out_cap;
-    if (c->h_stage_cap > (64ull << 20)) c->h_stage_cap = 64ull << 20;   /* staged in pieces */
-    CC(cudaMallocHost(&c->h_stage, c->h_stage_cap));
+    CC(cudaMallocHost(&c->h_total, (B2D_NSLOT + 1) * sizeof(uint64_t)));   /* a few words: not worth a mapping */
+    c->h_stage_max = (B2D_WINDOW + max_batch) > c->d_out_cap ? (B2D_WINDOW + max_batch) : c->d_out_cap;
+    if (c->h_stage_max > (64ull << 20)) c->h_stage_max = 64ull << 20;   /* staged in pieces */
+    /* h_stage (pageable callers of the one-batch path) starts small and grows with the calls: ensure_stage */
+    c->h_stage_cap = c->h_stage_max < (1ull << 20) ? c->h_stage_max : (1ull << 20);
+    CC(pinned_alloc((void **)&c->h_stage, c->h_stage_cap));
+    tr.mark("device + stage buffers", device);
     CC(b2d_cksum_ws_create(&c->ck));
+    tr.mark("checksum workspace", device);
     /* the second slot is allocated on first use (ensure_second_slot) */
 #undef CC
     *out = c;
@@ -186,8 +271,8 @@ extern "C" uint64_t b2d_launch_count(b2d_ctx *c) { return c ? c->launches : 0; }
 /* ---- memory helpers -------------------------------------------------------- */
 extern "C" int b2d_device_alloc(b2d_ctx *c, uint64_t bytes, void **p) { CU(cudaSetDevice(c->device)); CU(cudaMalloc(p, bytes)); return B2D_OK; }
 extern "C" int b2d_device_free(b2d_ctx *c, void *p) { CU(cudaSetDevice(c->device)); CU(cudaFree(p)); return B2D_OK; }
-extern "C" int b2d_host_alloc(b2d_ctx *c, uint64_t bytes, void **p) { CU(cudaSetDevice(c->device)); CU(cudaMallocHost(p, bytes)); return B2D_OK; }
-extern "C" int b2d_host_free(b2d_ctx *c, void *p) { CU(cudaSetDevice(c->device)); CU(cudaFreeHost(p)); return B2D_OK; }
+extern "C" int b2d_host_alloc(b2d_ctx *c, uint64_t bytes, void **p) { CU(cudaSetDevice(c->device)); CU(pinned_alloc(p, bytes)); return B2D_OK; }
+extern "C" int b2d_host_free(b2d_ctx *c, void *p) { CU(cudaSetDevice(c->device)); CU(pinned_free(p)); return B2D_OK; }
 extern "C" int b2d_copy_h2d(b2d_ctx *c, void *d, const void *h, uint64_t n) {
     CU(cudaSetDevice(c->device)); CU(cudaMemcpyAsync(d, h, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return B2D_OK;
 }
@@ -198,10 +283,10 @@ extern "C" int b2d_copy_d2h(b2d_ctx *c, void *h, const void *d, uint64_t n) {
  * use to hand such memory to the GPU without staging it */
 extern "C" int b2d_pinned_alloc(uint64_t bytes, void **p) {
     if (!p) return fail(B2D_STREAM_ERROR, "null argument");
-    CU(cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocPortable));
+    CU(pinned_alloc(p, bytes));
     return B2D_OK;
 }
-extern "C" int b2d_pinned_free(void *p) { if (p) CU(cudaFreeHost(p)); return B2D_OK; }
+extern "C" int b2d_pinned_free(void *p) { CU(pinned_free(p)); return B2D_OK; }
 extern "C" int b2d_host_is_pinned(const void *p) {
     cudaPointerAttributes at;
     const bool pinned = p && cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeHost;
@@ -247,6 +332,21 @@ extern "C" int b2d_adler32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, 
 
 static int checksum_host_pipelined(b2d_ctx *c, const uint8_t *data, uint64_t n, uint32_t start, bool adler, uint32_t *out);
 
+/* the one-batch paths stage pageable memory through h_stage: 1 MiB to begin with (small calls are latency-bound and
+ * must not pay for pinning 64 MiB), grown to what a call moves, at most h_stage_max */
+static int ensure_stage(b2d_ctx *c, uint64_t want) {
+    if (want > c->h_stage_max) want = c->h_stage_max;
+    if (want <= c->h_stage_cap) return B2D_OK;
+    uint64_t cap = c->h_stage_cap;
+    while (cap < want) cap *= 2;
+    if (cap > c->h_stage_max) cap = c->h_stage_max;
+    CU(cudaStreamSynchronize(c->st));
+    pinned_free(c->h_stage); c->h_stage = nullptr; c->h_stage_cap = 0;
+    CU(pinned_alloc((void **)&c->h_stage, cap));
+    c->h_stage_cap = cap;
+    return B2D_OK;
+}
+
 /* host bytes -> device in pieces through the pinned stage (or directly when the
  * caller's buffer is itself pinned), calling `fn` on each resident piece */
 template <typename F>
@@ -259,6 +359,7 @@ static int for_each_staged(b2d_ctx *c, const uint8_t *data, uint64_t n, F fn) {
         const uint64_t m = n - off < piece_cap ? n - off : piece_cap;
         if (pinned) { CU(cudaMemcpyAsync(c->d_in, data + off, m, cudaMemcpyHostToDevice, c->st)); }
         else {
+            { int rc = ensure_stage(c, m); if (rc) return rc; }
             for (uint64_t o = 0; o < m; o += c->h_stage_cap) {
                 const uint64_t k = m - o < c->h_stage_cap ? m - o : c->h_stage_cap;
                 memcpy(c->h_stage, data + off + o, k);
@@ -493,8 +594,8 @@ extern "C" int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int thr
 
 static int ensure_staging(b2d_ctx *c, bool in, bool out) {
     for (int i = 0; i < B2D_NSLOT; ++i) {
-        if (in && !c->h_in_s[i]) CU(cudaMallocHost(&c->h_in_s[i], c->d_in_cap));
-        if (out && !c->h_out_s[i]) CU(cudaMallocHost(&c->h_out_s[i], c->d_out_cap));
+        if (in && !c->h_in_s[i]) CU(pinned_alloc((void **)&c->h_in_s[i], c->d_in_cap));
+        if (out && !c->h_out_s[i]) CU(pinned_alloc((void **)&c->h_out_s[i], c->d_out_cap));
     }
     return B2D_OK;
 }
@@ -733,6 +834,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
     }
     auto h2d = [&](uint8_t *dst, const uint8_t *src, uint64_t bytes, bool src_pinned) -> int {
         if (src_pinned) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st)); return B2D_OK; }
+        { int rc = ensure_stage(c, bytes); if (rc) return rc; }
         for (uint64_t o = 0; o < bytes; o += c->h_stage_cap) {
             const uint64_t k = bytes - o < c->h_stage_cap ? bytes - o : c->h_stage_cap;
             CU(cudaStreamSynchronize(c->st));            /* the stage may still be in flight */
@@ -775,6 +877,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         const bool opinned = cudaPointerGetAttributes(&ot, out) == cudaSuccess && ot.type == cudaMemoryTypeHost;
         cudaGetLastError();
         if (opinned) { CU(cudaMemcpyAsync(out + produced, c->d_out, got, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); }
+        else if ((rc = ensure_stage(c, got))) return rc;
         else for (uint64_t o = 0; o < got; o += c->h_stage_cap) {
             const uint64_t k = got - o < c->h_stage_cap ? got - o : c->h_stage_cap;
             CU(cudaMemcpyAsync(c->h_stage, c->d_out + o, k, cudaMemcpyDeviceToHost, c->st));

@@ -42,7 +42,10 @@ _MIN_BATCH = 128 * 1024
 # What one native call covers, per GPU.  The reference keeps threads * block_size bytes in flight; a GPU wants more
 # per launch, so batches grow to this size (times the number of GPUs) unless the caller asked for less than one
 # 128 KiB device block in total (then the reference's sizes, and its OverflowError on oversized blocks, are kept).
-_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "64")) << 20
+_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "256")) << 20
+# what one GPU context works on at a time (its batch): a call's bytes are dealt to the devices in pieces of this size,
+# four of which are in flight per device
+_CTX_BATCH = int(os.environ.get("B2D_MAX_BATCH_MIB", "64")) << 20
 # native calls in flight (each on its own multi-device context): call j+1's first H2D and call j-1's last D2H
 # overlap call j's kernels.  Inside a call the library already pipelines 3 slots x 2 lanes per device.
 _STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "2")), 1)
@@ -260,10 +263,19 @@ class _ThreadedGzipReader(io.RawIOBase):
             if len(sizes) != nblocks or off != len(buf):
                 return None
             raw.seek(here)
-            if raw.read(4) != b"\x1f\x8b\x08\x00":
+            head = raw.read(10)
+            # the data member's header is the fixed one this writer emits (no flags, mtime 0, OS byte 0xff first)
+            if len(head) != 10 or head[:8] != b"\x1f\x8b\x08\x00\x00\x00\x00\x00" or head[8] != 0xFF or head[9] not in (0, 2, 4):
                 return None
-            # data member: 10-byte header, the blocks, 03 00, CRC32, ISIZE; then the empty member of close()
-            if here + 10 + sum(sizes) + 2 + 8 > index_off:
+            # data member: 10-byte header, the blocks, 03 00, CRC32, ISIZE; then exactly the empty member close() leaves
+            # (gzip_ng_threaded.py:340-355 in the reference), then the index.  Anything else between the data and the
+            # index (further members, say) would be skipped by this path and read by every other gzip reader: refuse.
+            data_end = here + 10 + sum(sizes) + 2 + 8
+            if index_off != data_end + 20:
+                return None
+            raw.seek(data_end)
+            empty = raw.read(20)
+            if (len(empty) != 20 or empty[:8] != head[:8] or empty[8] != 0xFF or empty[10:] != b"\x03\x00" + b"\x00" * 8):
                 return None
             _native.default_context()      # no usable GPU: the CPU reader takes over (raises here)
             return {"sizes": sizes, "raw_n": raw_n, "cpos": here + 10}
@@ -318,9 +330,11 @@ class _ThreadedGzipReader(io.RawIOBase):
                 if isinstance(item, BaseException):
                     raise item
                 if isinstance(item, bytes):                       # the member's end
-                    want_crc, isize = struct.unpack("<II", item[2:10]) if len(item) == 10 else (None, None)
+                    if len(item) != 10:
+                        raise EOFError("Compressed file ended before the end-of-stream marker was reached")
                     if item[:2] != b"\x03\x00":
                         raise _stdgzip.BadGzipFile("Bad stream end")
+                    want_crc, isize = struct.unpack("<II", item[2:10])
                     if want_crc != crc.value:
                         raise _stdgzip.BadGzipFile(f"CRC check failed {hex(want_crc)} != {hex(crc.value)}")
                     if isize != (g["raw_n"] & 0xFFFFFFFF):
@@ -405,6 +419,8 @@ class _ThreadedGzipReader(io.RawIOBase):
             if g["cur"] is not None:
                 g["free"].put(g["cur"])
                 g["cur"] = None
+            if g.get("error") is not None:
+                raise g["error"]                 # a damaged file stays damaged: later reads raise again
             if g["eof"]:
                 return 0
             item = g["ready"].get()
@@ -412,13 +428,20 @@ class _ThreadedGzipReader(io.RawIOBase):
                 g["eof"] = True
                 return 0
             if isinstance(item, BaseException):
-                g["eof"] = True
+                g["error"] = item
                 raise item
             g["cur"], g["cur_n"] = item
             g["off"] = 0
         mv = memoryview(b).cast("B")
         n = min(len(mv), g["cur_n"] - g["off"])
-        mv[:n] = g["cur"][1][g["off"]:g["off"] + n]
+        if n >= 2 * _COPY_CHUNK:
+            # big reads (BufferedReader hands read(n) its own fresh bytes object): copy on native threads, which also
+            # spreads the page faults of a destination nobody has touched yet
+            daddr, _, keep = _native._addr(mv)
+            _native.check(_native.lib().b2d_host_copy(daddr, g["cur"][0] + g["off"], n, _COPY_THREADS))
+            del keep
+        else:
+            mv[:n] = g["cur"][1][g["off"]:g["off"] + n]
         g["off"] += n
         self.pos += n
         return n
@@ -523,6 +546,11 @@ class _ThreadedGzipWriter(io.RawIOBase):
         nominal = max(block_size * threads // nw, 1)
         self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, _STREAM_BATCH * len(devices))
         self._out_cap = self.batch + max(self.batch // 10, 500)
+        # the first batches of a file go out early (a quarter, then half of the full size), so that the GPUs start
+        # while the caller is still writing and short files do not wait for a batch that never fills
+        self._target = self.batch
+        if self.batch >= 4 * _CTX_BATCH * len(devices):
+            self._target = self.batch // 4 // _DEVICE_BLOCK * _DEVICE_BLOCK
         self.input_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)]
         self.output_queues = [queue.Queue(max(queue_size, 1)) for _ in range(nw)] if nw > 1 else []
         self._free = queue.Queue()
@@ -662,14 +690,14 @@ class _ThreadedGzipWriter(io.RawIOBase):
         if mv.ndim != 1 or mv.format != "B":
             mv = mv.cast("B")
         length = mv.nbytes
-        if length >= self.batch and self.batch >= _MIN_BATCH and self._write_pinned(mv):
+        if length >= self.batch and self.batch >= _MIN_BATCH and self._write_direct(mv):
             return length
         pos = 0
         while pos < length:
             if self._cur is None:
                 self._cur = self._take_buffer()
             buf = self._cur
-            k = min(length - pos, self.batch - buf.fill)
+            k = min(length - pos, self._target - buf.fill)
             o = DEFLATE_WINDOW_SIZE + buf.fill
             if k >= 2 * _COPY_CHUNK:
                 _parallel_copy(buf.ptr + o, mv[pos:pos + k], k)
@@ -677,44 +705,41 @@ class _ThreadedGzipWriter(io.RawIOBase):
                 buf.view[o:o + k] = mv[pos:pos + k]
             buf.fill += k
             pos += k
-            if buf.fill == self.batch:
+            if buf.fill >= self._target:
                 self._submit_current()
+                self._target = min(self.batch, self._target * 2)
         return length
 
-    def _write_pinned(self, mv) -> bool:
-        """A large write from page-locked memory (pinned_buffer(), or any cudaHostAlloc'ed / registered memory) is
-        not gathered into the writer's own pinned batches: its pieces go to the workers as they lie, and the call
-        returns once they are compressed (the caller may reuse the buffer as soon as write() returns, as with any
-        file object)."""
-        addr, n, keep = _native._addr(mv)
-        try:
-            if not _native.lib().b2d_host_is_pinned(addr) or not _native.lib().b2d_host_is_pinned(addr + n - 1):
-                return False
-            if self._cur is not None and self._cur.fill % _DEVICE_BLOCK:
-                return False          # the stream would no longer consist of whole device blocks: gather as usual
-            self._submit_current()
-            pos = 0
-            while pos < n:
-                # whole device blocks, except at the very end of the write
-                k = min(self.batch, n - pos)
-                data = mv[pos:pos + k]
-                if pos >= DEFLATE_WINDOW_SIZE:
-                    zdict = mv[pos - DEFLATE_WINDOW_SIZE:pos]
-                else:
-                    zdict = (self._last_tail + bytes(mv[:pos]))[-DEFLATE_WINDOW_SIZE:]
-                worker = self.index % len(self.input_queues)
-                self.index += 1
-                self._put_job(worker, (data, zdict, None))
-                pos += k
-            self._last_tail = (self._last_tail + bytes(mv[-DEFLATE_WINDOW_SIZE:]))[-DEFLATE_WINDOW_SIZE:]
-            for q in list(self.input_queues) + list(self.output_queues):
-                self._join(q)
-            with self.lock:
-                if self.exception:
-                    raise self.exception
-            return True
-        finally:
-            del keep
+    def _write_direct(self, mv) -> bool:
+        """A write of a whole batch or more is not gathered into the writer's own pinned batches: its pieces go to
+        the workers as they lie and the call returns once they are compressed (so the caller may reuse the buffer as
+        soon as write() returns, as with any file object).  Page-locked memory (pinned_buffer(), or anything
+        cudaHostAlloc'ed / registered) then moves by DMA without any host copy; pageable memory is staged by the
+        library's per-device threads, overlapped with the kernels."""
+        n = mv.nbytes
+        if self._cur is not None and self._cur.fill % _DEVICE_BLOCK:
+            return False          # the stream would no longer consist of whole device blocks: gather as usual
+        self._submit_current()
+        pos = 0
+        while pos < n:
+            # whole device blocks, except at the very end of the write
+            k = min(self.batch, n - pos)
+            data = mv[pos:pos + k]
+            if pos >= DEFLATE_WINDOW_SIZE:
+                zdict = mv[pos - DEFLATE_WINDOW_SIZE:pos]
+            else:
+                zdict = (self._last_tail + bytes(mv[:pos]))[-DEFLATE_WINDOW_SIZE:]
+            worker = self.index % len(self.input_queues)
+            self.index += 1
+            self._put_job(worker, (data, zdict, None))
+            pos += k
+        self._last_tail = (self._last_tail + bytes(mv[-DEFLATE_WINDOW_SIZE:]))[-DEFLATE_WINDOW_SIZE:]
+        for q in list(self.input_queues) + list(self.output_queues):
+            self._join(q)
+        with self.lock:
+            if self.exception:
+                raise self.exception
+        return True
 
     def _put_job(self, worker, job):
         q = self.input_queues[worker]
@@ -973,7 +998,7 @@ def _multi_context_for(devices, slot: int = 0):
             m = _mctx.get(key)
             if m is None:
                 try:
-                    m = _native.MultiContext(devices, _STREAM_BATCH)
+                    m = _native.MultiContext(devices, _CTX_BATCH)
                 except _native.NativeError as e:
                     raise zlib_ng.error(f"Error {e.code} while opening the B200 device: {e.msg}") from None
                 _mctx[key] = m
