@@ -84,6 +84,18 @@ int b2d_deflate_device(b2d_ctx *ctx, int level, const uint8_t *d_buf, uint64_t d
 int b2d_crc32_device(b2d_ctx *ctx, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out, float *kernel_ms);
 int b2d_adler32_device(b2d_ctx *ctx, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out, float *kernel_ms);
 
+/* Adler-32 of device-resident bytes for callers that may not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Needs no context and calls no cudaMalloc / cudaFree / allocating routine: the partial sums of the bulk
+ * kernel live in a file-scope device array of 24 KiB that every GPU loading the library holds until exit.  At most
+ * B2D_NOALLOC_MAX_BYTES (1 GiB) per call: larger sizes are refused with B2D_STREAM_ERROR and a message (b2d_last_error).
+ * Synchronous (the calling thread's per-thread stream).  Every call shares the array, which keeps the last call's
+ * contents (the entries a call reads are cleared first); calls are serialised inside one process, calls that overlap
+ * on the GPU otherwise race.  Same result as b2d_adler32_device, bit for bit. */
+#define B2D_NOALLOC_MAX_BYTES (1ull << 30)
+uint64_t b2d_noalloc_max_bytes(void);
+int b2d_adler32_device_noalloc(int device, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out);
+
 /* ---- memory helpers for callers without their own CUDA binding --------------- */
 int b2d_device_alloc(b2d_ctx *ctx, uint64_t bytes, void **ptr);
 int b2d_device_free(b2d_ctx *ctx, void *ptr);

@@ -330,6 +330,20 @@ extern "C" int b2d_adler32_device(b2d_ctx *c, uint32_t start, const uint8_t *d, 
     return B2D_OK;
 }
 
+extern "C" uint64_t b2d_noalloc_max_bytes(void) { return B2D_NOALLOC_MAX_BYTES; }
+extern "C" int b2d_adler32_device_noalloc(int device, uint32_t start, const uint8_t *d_data, uint64_t n, uint32_t *out) {
+    if (!out || (!d_data && n)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (n > B2D_NOALLOC_MAX_BYTES) {
+        snprintf(g_err, sizeof g_err, "b2d_adler32_device_noalloc: %llu bytes exceed the maximum of %llu (use b2d_adler32_device)",
+                 (unsigned long long)n, (unsigned long long)B2D_NOALLOC_MAX_BYTES);
+        return B2D_STREAM_ERROR;
+    }
+    const char *why = "";
+    cudaError_t e = b2d_adler32_noalloc(device, d_data, n, start, out, &why);
+    if (e != cudaSuccess) return fail_cuda(e, why);
+    return B2D_OK;
+}
+
 static int checksum_host_pipelined(b2d_ctx *c, const uint8_t *data, uint64_t n, uint32_t start, bool adler, uint32_t *out);
 
 /* the one-batch paths stage pageable memory through h_stage: 1 MiB to begin with (small calls are latency-bound and

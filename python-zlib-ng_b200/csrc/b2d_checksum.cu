@@ -364,3 +364,75 @@ cudaError_t b2d_adler32_dev(b2d_cksum_ws *w, const uint8_t *d, uint64_t n, uint3
     *out = b2d_adler32_dev_finish(w, n, start);
     return cudaSuccess;
 }
+
+/* ---- Adler-32 without any allocation (b2d_adler32_device_noalloc, include/b2d.h) -----------------------------
+ * For callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  No counterpart in the reference.  The per-CTA partial
+ * sums that k_adler_bulk / k_adler_edges write — the scratch the other entry points keep in a cudaMalloc'ed
+ * workspace — live in a file-scope device array instead: B2D_NOALLOC_PARTS partial sums, 24 KiB, held by every GPU
+ * that loads the library until the process exits.  Every call shares the array and it keeps the last call's
+ * contents; calls are serialised inside the library, but calls that overlap on the GPU from several processes'
+ * worth of streams would race (there is one array per device, not per caller). */
+#define B2D_NOALLOC_PARTS (CK_MAX_SEG + 2u)
+static __device__ __align__(256) adler_part g_noalloc_parts[B2D_NOALLOC_PARTS];
+
+#include <mutex>
+#define B2D_NOALLOC_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static adler_part *g_noalloc_ptr[B2D_NOALLOC_MAX_DEVICES];      /* device address of the array, per device */
+static int g_noalloc_sms[B2D_NOALLOC_MAX_DEVICES];
+
+/* 0 = ok; on failure *why names the step.  `max_bytes` is enforced by the caller (b2d_api.cu). */
+cudaError_t b2d_adler32_noalloc(int device, const uint8_t *d, uint64_t n, uint32_t start, uint32_t *out, const char **why) {
+    *why = "";
+    if (device < 0 || device >= B2D_NOALLOC_MAX_DEVICES) { *why = "device index"; return cudaErrorInvalidDevice; }
+    if (n == 0) { *out = start; return cudaSuccess; }
+    std::lock_guard<std::mutex> g(g_noalloc_mu);                /* one call at a time: the scratch is shared */
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { *why = "cudaSetDevice"; return e; }
+    if (!g_noalloc_ptr[device]) {
+        /* once per device, with that device current: in host code the array's name is only a stand-in for the
+         * symbol, not a device address */
+        adler_part *p = nullptr;
+        if ((e = cudaGetSymbolAddress((void **)&p, g_noalloc_parts)) != cudaSuccess) { *why = "cudaGetSymbolAddress"; return e; }
+        int sms = 0;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) { *why = "cudaDeviceGetAttribute"; return e; }
+        g_noalloc_sms[device] = sms > 0 ? sms : 148;
+        g_noalloc_ptr[device] = p;
+    }
+    adler_part *parts = g_noalloc_ptr[device];
+    cudaStream_t st = cudaStreamPerThread;
+    uint64_t head = (16 - ((uintptr_t)d & 15)) & 15;
+    if (head > n) head = n;
+    const uint64_t npieces = (n - head) / 16;
+    const uint64_t tail = n - head - npieces * 16;
+    uint32_t G = 0;
+    uint64_t per = 0;
+    if (npieces) {
+        uint64_t want = (uint64_t)g_noalloc_sms[device] * 2;
+        if (want > CK_MAX_SEG) want = CK_MAX_SEG;
+        per = (npieces + want - 1) / want;
+        per = (per + 1023) / 1024 * 1024;
+        G = (uint32_t)((npieces + per - 1) / per);
+    }
+    /* the array keeps the last call's sums: clear the entries this call reads back */
+    if ((e = cudaMemsetAsync(parts, 0, (2 + G) * sizeof(adler_part), st)) != cudaSuccess) { *why = "cudaMemsetAsync"; return e; }
+    if (G) k_adler_bulk<<<G, 1024, 0, st>>>(reinterpret_cast<const uint4 *>(d + head), npieces, per, n - head, parts + 2);
+    ck_range r0 = { d, head }, r1 = { d + head + npieces * 16, tail };
+    k_adler_edges<<<1, 2, 0, st>>>(r0, 0, r1, head + npieces * 16, n, parts);
+    if ((e = cudaGetLastError()) != cudaSuccess) { *why = "kernel launch"; return e; }
+    adler_part h[B2D_NOALLOC_PARTS];                            /* on the stack: nothing is allocated */
+    if ((e = cudaMemcpyAsync(h, parts, (2 + G) * sizeof(adler_part), cudaMemcpyDeviceToHost, st)) != cudaSuccess) { *why = "cudaMemcpyAsync"; return e; }
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) { *why = "cudaStreamSynchronize"; return e; }
+    uint64_t S1 = 0, P = 0, Q = 0;
+    for (uint32_t i = 0; i < 2 + G; ++i) {
+        S1 = (S1 + h[i].s1 % ADLER_BASE) % ADLER_BASE;
+        P = (P + h[i].p) % ADLER_BASE;
+        Q = (Q + h[i].q % ADLER_BASE) % ADLER_BASE;
+    }
+    const uint64_t a = start & 0xffffu, b = (start >> 16) & 0xffffu;
+    const uint64_t s1 = (a + S1) % ADLER_BASE;
+    const uint64_t s2 = (b + (n % ADLER_BASE) * a % ADLER_BASE + P + ADLER_BASE - Q) % ADLER_BASE;
+    *out = (uint32_t)(s1 | (s2 << 16));
+    return cudaSuccess;
+}

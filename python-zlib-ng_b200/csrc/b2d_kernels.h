@@ -44,6 +44,10 @@ uint32_t b2d_crc32_dev_finish(b2d_cksum_ws *ws, uint64_t n, uint32_t start);
 cudaError_t b2d_adler32_dev_launch(b2d_cksum_ws *ws, const uint8_t *d, uint64_t n, cudaStream_t st);
 uint32_t b2d_adler32_dev_finish(b2d_cksum_ws *ws, uint64_t n, uint32_t start);
 
+/* adler32 of n device bytes without allocating anything: the partial sums live in a file-scope device array
+ * (b2d_checksum.cu); synchronous, on the calling thread's per-thread stream */
+cudaError_t b2d_adler32_noalloc(int device, const uint8_t *d, uint64_t n, uint32_t start, uint32_t *out, const char **why);
+
 /* host GF(2) helpers (b2d_checksum.cu) */
 uint32_t b2d_host_crc32_combine(uint32_t crc1, uint32_t crc2, uint64_t len2);
 uint32_t b2d_host_adler32_combine(uint32_t a1, uint32_t a2, uint64_t len2);

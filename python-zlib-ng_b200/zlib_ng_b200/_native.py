@@ -45,6 +45,8 @@ SIGNATURES = {
                                           _P(_u32), _P(ctypes.c_float)]),
     "b2d_crc32_device": (ctypes.c_int, [ctypes.c_void_p, _u32, _u8p, _u64, _P(_u32), _P(ctypes.c_float)]),
     "b2d_adler32_device": (ctypes.c_int, [ctypes.c_void_p, _u32, _u8p, _u64, _P(_u32), _P(ctypes.c_float)]),
+    "b2d_noalloc_max_bytes": (_u64, []),
+    "b2d_adler32_device_noalloc": (ctypes.c_int, [ctypes.c_int, _u32, _u8p, _u64, _P(_u32)]),
     "b2d_device_alloc": (ctypes.c_int, [ctypes.c_void_p, _u64, _P(ctypes.c_void_p)]),
     "b2d_device_free": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "b2d_host_alloc": (ctypes.c_int, [ctypes.c_void_p, _u64, _P(ctypes.c_void_p)]),
