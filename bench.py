@@ -144,7 +144,20 @@ def dist_setup():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
+        global _CPU_GROUP
+        _CPU_GROUP = dist_mod.new_group(backend="gloo")
     return rank, world, local, dist
+
+
+_CPU_GROUP = None
+
+
+def cpu_barrier(dist):
+    """A barrier that leaves the GPUs alone.  While rank 0 drives all N GPUs from one process (the end-to-end leg, the
+    streaming legs) the other ranks must not sit in an NCCL barrier: its kernel spins on their GPU, and kernels of two
+    processes on one GPU are time-sliced, which halves what rank 0 gets there (measured: 36.7 instead of 77 GB/s at N=2)."""
+    if dist is not None:
+        dist.barrier(group=_CPU_GROUP)
 
 
 def barrier(dist, local):
@@ -397,6 +410,7 @@ def main():
     ctx.device_free(d_out)
     d_in = d_out = None
     barrier(dist, local)
+    ctx.sync()
     if rank == 0:
         try:
             total = world * n
@@ -405,7 +419,9 @@ def main():
             hv = np.frombuffer((ctypes.c_uint8 * total).from_address(h_in), dtype=np.uint8)
             for r in range(world):
                 hv[r * n:(r + 1) * n] = shard if r == rank else shard_bytes(base, r, n)
-            m = nat.MultiContext(list(range(world)), a.batch_mib * MIB)
+            # 64 MiB batches for the host path: four lanes of them fill a device like two of 256 MiB do, with a quarter of
+            # the pipeline's fill and drain time (profiles/r2_i_multi_e2e.log: 100.7 against 95.9 GB/s on 8 GPUs)
+            m = nat.MultiContext(list(range(world)), min(a.batch_mib, 64) * MIB)
 
             def host_pass():
                 return m.compress_and_crc(a.level, h_in, total, None, 0, h_out, cap_all, want_sizes=True)
@@ -454,7 +470,7 @@ def main():
             nat.pinned_free(h_out)
         except Exception as e:  # report, never fake
             e2e = {"value": None, "unit": "GB/s", "error": f"{type(e).__name__}: {e}"}
-    barrier(dist, local)
+    cpu_barrier(dist)             # ranks > 0 sleep here (no GPU work) while rank 0 drives every GPU
     verify["shard_crcs_fold_to_reference_crc32"] = bool(shards_ok)
     verify_ok = bool(e2e and e2e.get("value")) and all(v for k, v in verify.items() if isinstance(v, bool))
 
@@ -608,7 +624,7 @@ def main():
         if extra:
             line["extra"] = extra
         emit_line(line)
-    barrier(dist, local)          # the other ranks leave together with rank 0 (its extras run last)
+    cpu_barrier(dist)             # the other ranks leave together with rank 0 (its extras run last)
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -157,14 +157,31 @@ int b2d_compress_and_crc_indexed(b2d_ctx *ctx, int level, const uint8_t *data, u
  * array; nblocks = ceil(raw_n / 128 KiB)) and the dictionary the stream was primed with (device pointer, at
  * most 32 KiB, may be NULL/0).  Every block is decoded by its own warp; references into the preceding 32 KiB
  * are carried as markers and resolved afterwards (b2d_inflate.cu).  Needs 2 * raw_n bytes of device scratch
- * (owned by the context).  Returns -3 (Z_DATA_ERROR) if a block does not decode to its expected length. */
+ * (owned by the context).  Returns -3 (Z_DATA_ERROR) if a block does not decode to its expected length — and only then:
+ * the decode kernel is issued first and waits for nobody, so the result does not depend on kernels running side by side
+ * (profilers, CUDA_LAUNCH_BLOCKING). */
 int b2d_inflate_device(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
                        uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
                        float *ms);
-/* the same with host buffers (H2D, kernels, D2H; callers overlap consecutive calls on two contexts).  `crc`
+/* the same with host buffers: chunks of 512 blocks flow through H2D / decode / resolve / D2H side by side.  `crc`
  * (optional) is continued over the output: *crc = crc32(out[0, raw_n), *crc), computed on the device. */
 int b2d_inflate_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
                      const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc);
+
+/* ---- BGZF (blocked gzip: htslib / bgzip; the reference reads such files with its one zng_inflate thread, fixture
+ * tests/data/test.fastq.bgzip.gz, tests/test_gzip_ng.py:466-473) ----------------------------------------------------
+ * b2d_bgzf_scan walks the members at buf[0, n): gzip members whose "BC" extra subfield holds their total size.  For each
+ * of the first *count (<= max_members) complete members it reports where the DEFLATE data lies, the ISIZE and the CRC-32
+ * of its trailer; *consumed = offset behind the last complete member (the rest of the buffer is a partial member, or not
+ * BGZF).  Pure host code; the arrays may be NULL to count only. */
+int b2d_bgzf_scan(const uint8_t *buf, uint64_t n, uint64_t max_members, uint64_t *payload_off, uint32_t *payload_len,
+                  uint32_t *raw_len, uint32_t *crc, uint64_t *count, uint64_t *consumed);
+/* Inflate independent DEFLATE streams (no dictionary, each at most 64 KiB of output: BGZF members) from a host buffer into
+ * `out`, back to back, one warp per member.  crcs (optional): the members' CRC-32s, verified against the output (-3 on
+ * mismatch, like a damaged gzip member: zlib_ngmodule.c:2581-2599). */
+int b2d_inflate_members_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *payload_off,
+                             const uint32_t *payload_len, const uint32_t *raw_len, const uint32_t *crcs, uint64_t nmembers,
+                             uint8_t *out, uint64_t out_cap, uint64_t *out_n);
 
 /* Per-kernel timing of b2d_deflate_device calls (CUDA events on the launching
  * stream, accumulated): stages 0..5 = chains, match, parse, plan, scan, emit.

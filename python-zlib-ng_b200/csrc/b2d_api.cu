@@ -23,6 +23,7 @@
 #include "../../include/b2d.h"
 #include "b2d_kernels.h"
 #include "b2d_inflate.h"
+#include "b2d_hostcopy.h"
 
 static thread_local char g_err[512];
 static int fail_cuda(cudaError_t e, const char *where) {
@@ -170,6 +171,9 @@ struct b2d_ctx {
     uint8_t *d_inf_in, *d_inf_out; uint64_t inf_in_cap, inf_out_cap;     /* device copies for b2d_inflate_host */
     uint32_t *d_inf_flags; uint64_t inf_flags_cap;                       /* one ready flag per block */
     cudaStream_t st_inf; cudaEvent_t ev_inf_fork, ev_inf_join;           /* the serial pass runs beside the decode */
+    cudaStream_t st_inf_in, st_inf_out;                                  /* host calls: copies of chunk c+1 / c-1 beside chunk c's kernels */
+    cudaStream_t st_inf_dec[4];                                          /* ... and the decodes of neighbouring chunks beside each other */
+    std::vector<cudaEvent_t> ev_inf_h2d, ev_inf_done;                    /* per chunk */
     /* optional per-stage timing of device-resident calls */
     int profiling;
     cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
@@ -187,6 +191,11 @@ static void ctx_free(b2d_ctx *c) {
     cudaFree(c->d_total);
     cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out); cudaFree(c->d_inf_flags);
     if (c->st_inf) cudaStreamDestroy(c->st_inf);
+    if (c->st_inf_in) cudaStreamDestroy(c->st_inf_in);
+    if (c->st_inf_out) cudaStreamDestroy(c->st_inf_out);
+    for (int i = 0; i < 4; ++i) if (c->st_inf_dec[i]) cudaStreamDestroy(c->st_inf_dec[i]);
+    for (cudaEvent_t e : c->ev_inf_h2d) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_inf_done) cudaEventDestroy(e);
     if (c->ev_inf_fork) cudaEventDestroy(c->ev_inf_fork);
     if (c->ev_inf_join) cudaEventDestroy(c->ev_inf_join);
     for (int i = 0; i < B2D_NSLOT - 1; ++i) { cudaFree(c->d_inx[i]); cudaFree(c->d_outx[i]); cudaFree(c->d_totalx[i]); b2d_cksum_ws_destroy(c->ckx[i]); }
@@ -582,22 +591,8 @@ static int ensure_second_slot(b2d_ctx *c) {
     return B2D_OK;
 }
 
-/* host copy in a few threads: one thread moves ~10 GB/s, the pipeline wants more */
-static void par_memcpy_n(void *dst, const void *src, uint64_t n, unsigned nt) {
-    const uint64_t piece = 4ull << 20;
-    if (nt > 32) nt = 32;
-    if (nt < 2 || n < 2 * piece) { memcpy(dst, src, n); return; }
-    if ((uint64_t)nt * piece > n) nt = (unsigned)(n / piece);
-    std::thread th[32];
-    const uint64_t per = (n / nt + 4095) & ~4095ull;
-    for (unsigned i = 1; i < nt; ++i) {
-        const uint64_t o = (uint64_t)i * per;
-        const uint64_t k = o >= n ? 0 : (n - o < per ? n - o : per);
-        th[i] = std::thread([=] { if (k) memcpy((uint8_t *)dst + o, (const uint8_t *)src + o, k); });
-    }
-    memcpy(dst, src, per < n ? per : n);          /* the calling thread takes the first piece */
-    for (unsigned i = 1; i < nt; ++i) th[i].join();
-}
+/* host copies run on a persistent pool with non-temporal stores (b2d_hostcopy.cpp): one thread moves ~14 GB/s */
+static void par_memcpy_n(void *dst, const void *src, uint64_t n, unsigned nt) { b2d_par_memcpy(dst, src, n, nt); }
 static void par_memcpy(void *dst, const void *src, uint64_t n) { par_memcpy_n(dst, src, n, 4); }
 
 extern "C" int b2d_host_copy(void *dst, const void *src, uint64_t bytes, int threads) {
@@ -662,6 +657,10 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     c->index_base.assign(nloc, 0);
     c->index_bpb = bpb;
     uint64_t pend_off = 0, pend_n = 0; int pend_s = -1;
+    static const bool trace = getenv("B2D_TRACE") && getenv("B2D_TRACE")[0] == '1';
+    double t_comp = 0, t_ledger = 0, t_issue = 0;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = now();
     auto batch_len = [&](uint64_t j) { return (j + 1 == nb) ? n - j * batch : batch; };
     auto drain = [&]() -> int {          /* staged output: copy the batch whose D2H was issued last */
         if (pend_s < 0) return B2D_OK;
@@ -673,7 +672,10 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
     auto finish = [&](uint64_t i) -> int {          /* local batch i: wait for its kernels, note its checksums, start its D2H */
         const int s = (int)(i % B2D_NSLOT);
         const uint64_t j = first + i * stride, m = batch_len(j);
+        const double t0 = now();
         CU(cudaEventSynchronize(c->ev_comp[s]));
+        const double t1 = now();
+        t_comp += t1 - t0;
         if (want_crc) G->crc[j] = b2d_crc32_dev_finish(ck[s], m, 0);
         if (want_adler) G->adler[j] = b2d_adler32_dev_finish(ck[s], m, 1);
         const uint64_t got = c->h_total[s];
@@ -692,6 +694,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
             G->known = j + 1;
         }
         G->cv.notify_all();
+        t_ledger += now() - t1;
         c->index_base[i] = at;
         if (out_pinned) {
             CU(cudaMemcpyAsync(out + at, d_out[s], got, cudaMemcpyDeviceToHost, c->st_out));
@@ -705,6 +708,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         return B2D_OK;
     };
     for (uint64_t i = 0; i < nloc; ++i) {
+        const double ti = now();
         const int s = (int)(i % B2D_NSLOT);
         const int ln = (int)(i % B2D_NLANE);  /* compute lane */
         const uint64_t j = first + i * stride;
@@ -744,13 +748,18 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         if (want_crc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
         if (want_adler) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
+        t_issue += now() - ti;
         /* the host trails by one batch per lane: the lanes stay busy while it waits for the oldest batch */
         if (i >= B2D_NLANE && (rc = finish(i - B2D_NLANE))) { cudaDeviceSynchronize(); return rc; }
     }
     for (uint64_t k = nloc > B2D_NLANE ? nloc - B2D_NLANE : 0; k < nloc; ++k)
         if ((rc = finish(k))) { cudaDeviceSynchronize(); return rc; }
     if ((rc = drain())) { cudaDeviceSynchronize(); return rc; }
+    const double t_tail0 = now();
     CU(cudaStreamSynchronize(c->st_out));
+    if (trace)
+        fprintf(stderr, "[b2d] device %d: %llu batches of %llu MiB: total %.1f ms = issue %.1f + wait kernels %.1f + ledger/D2H issue %.1f + last D2H %.1f\n",
+                c->device, (unsigned long long)nloc, (unsigned long long)(batch >> 20), now() - t_begin, t_issue, t_comp, t_ledger, now() - t_tail0);
     /* the index of this context's blocks (b2d_block_index, collect_index): relative offsets stay on the device */
     c->index_n = 0;
     c->index_local = nloc ? (nloc - 1) * bpb + (batch_len(first + (nloc - 1) * stride) + B2D_BLOCK - 1) / B2D_BLOCK : 0;
@@ -1105,6 +1114,45 @@ extern "C" int b2d_block_index(b2d_ctx *c, uint64_t *offsets, uint64_t cap, uint
     return B2D_OK;
 }
 
+/* scratch of the inflate side, grown on demand: 16-bit symbols (streams of this library only), block index, ready
+ * flags, error words, the second stream */
+static int inflate_prepare(b2d_ctx *c, uint64_t nblocks, uint64_t raw_n, bool need16) {
+    if (!need16) raw_n = 0;
+    if (raw_n > c->inf16_cap) {
+        cudaFree(c->d_inf16); c->d_inf16 = nullptr; c->inf16_cap = 0;
+        cudaError_t e = cudaMalloc(&c->d_inf16, raw_n * sizeof(uint16_t));
+        if (e != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate scratch (2 bytes per output byte) does not fit"); }
+        c->inf16_cap = raw_n;
+    }
+    if (nblocks > c->inf_index_cap) {
+        cudaFree(c->d_inf_index); c->d_inf_index = nullptr; c->inf_index_cap = 0;
+        CU(cudaMalloc(&c->d_inf_index, nblocks * sizeof(uint64_t)));
+        c->inf_index_cap = nblocks;
+    }
+    if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, 2 * sizeof(uint32_t)));
+    if (nblocks > c->inf_flags_cap) {
+        cudaFree(c->d_inf_flags); c->d_inf_flags = nullptr; c->inf_flags_cap = 0;
+        CU(cudaMalloc(&c->d_inf_flags, nblocks * sizeof(uint32_t)));
+        c->inf_flags_cap = nblocks;
+    }
+    if (!c->st_inf) {
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&c->st_inf, cudaStreamNonBlocking, hi));     /* the serial pass is the critical path */
+        CU(cudaEventCreateWithFlags(&c->ev_inf_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_inf_join, cudaEventDisableTiming));
+    }
+    return B2D_OK;
+}
+
+/* report what the decode left in the error words (streams synchronised by the caller) */
+static int inflate_verdict(const uint32_t err[2]) {
+    if (!err[0]) return B2D_OK;
+    static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code", "", "", "", ""};
+    snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err[0] >> 28) & 7], err[0] & 0x0fffffffu);
+    return -3;   /* Z_DATA_ERROR */
+}
+
 /* how the three inflate kernels are issued: side by side where the device can do that, on one stream where it
  * cannot (or where a tool serialises launches anyway) */
 static int inflate_mode(b2d_ctx *c) {
@@ -1132,35 +1180,22 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
     if (raw_n == 0) return B2D_OK;
     std::lock_guard<std::recursive_mutex> g(c->mu);
     CU(cudaSetDevice(c->device));
-    if (raw_n > c->inf16_cap) {
-        cudaFree(c->d_inf16); c->d_inf16 = nullptr; c->inf16_cap = 0;
-        cudaError_t e = cudaMalloc(&c->d_inf16, raw_n * sizeof(uint16_t));
-        if (e != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate scratch (2 bytes per output byte) does not fit"); }
-        c->inf16_cap = raw_n;
-    }
-    if (nblocks > c->inf_index_cap) {
-        cudaFree(c->d_inf_index); c->d_inf_index = nullptr; c->inf_index_cap = 0;
-        CU(cudaMalloc(&c->d_inf_index, nblocks * sizeof(uint64_t)));
-        c->inf_index_cap = nblocks;
-    }
-    if (!c->d_inf_err) CU(cudaMalloc(&c->d_inf_err, 2 * sizeof(uint32_t)));
-    if (nblocks > c->inf_flags_cap) {
-        cudaFree(c->d_inf_flags); c->d_inf_flags = nullptr; c->inf_flags_cap = 0;
-        CU(cudaMalloc(&c->d_inf_flags, nblocks * sizeof(uint32_t)));
-        c->inf_flags_cap = nblocks;
-    }
-    if (!c->st_inf) {
-        int lo = 0, hi = 0;
-        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        CU(cudaStreamCreateWithPriority(&c->st_inf, cudaStreamNonBlocking, hi));     /* the serial pass is the critical path */
-        CU(cudaEventCreateWithFlags(&c->ev_inf_fork, cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&c->ev_inf_join, cudaEventDisableTiming));
-    }
+    { int rc = inflate_prepare(c, nblocks, raw_n, true); if (rc) return rc; }
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
     CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
-    CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
-                          c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join, inflate_mode(c)));
+    CU(cudaMemsetAsync(c->d_inf_flags, 0, nblocks * sizeof(uint32_t), c->st));
+    const int mode = inflate_mode(c);
+    if (mode == B2D_INF_CONCURRENT) {
+        CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* flags and error words are cleared */
+        CU(cudaStreamWaitEvent(c->st_inf, c->ev_inf_fork, 0));
+    }
+    CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+                          c->d_inf_flags, c->d_inf_err, c->st, mode == B2D_INF_CONCURRENT ? c->st_inf : c->st, mode));
+    if (mode == B2D_INF_CONCURRENT) {
+        CU(cudaEventRecord(c->ev_inf_join, c->st_inf));
+        CU(cudaStreamWaitEvent(c->st, c->ev_inf_join, 0));
+    }
     c->launches += B2D_INF_LAUNCHES;
     if (ms) CU(cudaEventRecord(c->ev1, c->st));
     uint32_t err[2] = {0, 0};
@@ -1170,8 +1205,8 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         /* the pass over the tails gave up waiting for the decode (it could not run beside it and the wait ran out).
          * That says nothing about the data: every block is decoded by now, so resolve again on one stream. */
         CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
-        CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
-                              c->d_inf_flags, c->d_inf_err, c->st, c->st_inf, c->ev_inf_fork, c->ev_inf_join, B2D_INF_RESOLVE_ONLY));
+        CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+                              c->d_inf_flags, c->d_inf_err, c->st, c->st, B2D_INF_RESOLVE_ONLY));
         c->launches += 2;
         if (ms) CU(cudaEventRecord(c->ev1, c->st));
         CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
@@ -1179,44 +1214,202 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         if (err[1] && !err[0]) return fail(B2D_CUDA_ERROR, "inflate: the resolving pass did not complete");
     }
     if (ms) CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
-    if (err[0]) {
-        static const char *why[] = {"", "invalid block header", "output does not match the block layout", "invalid code",
-                                    "", "", "", ""};
-        snprintf(g_err, sizeof g_err, "inflate: %s in device block %u", why[(err[0] >> 28) & 7], err[0] & 0x0fffffffu);
-        return -3;   /* Z_DATA_ERROR */
+    return inflate_verdict(err);
+}
+
+#ifndef B2D_INF_CHUNK_BLOCKS
+#define B2D_INF_CHUNK_BLOCKS 512u    /* 64 MiB of output per chunk of a host call */
+#endif
+
+/* device copies of a host call's input (32 KiB of room for the dictionary in front of it) and output: kept by the
+ * context, grown on demand */
+static int inflate_host_buffers(b2d_ctx *c, uint64_t in_n, uint64_t out_n) {
+    const uint64_t need_in = B2D_WINDOW + in_n + 64, need_out = out_n + 64;
+    if (need_in > c->inf_in_cap) {
+        cudaFree(c->d_inf_in); c->d_inf_in = nullptr; c->inf_in_cap = 0;
+        if (cudaMalloc(&c->d_inf_in, need_in) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate input buffer does not fit"); }
+        c->inf_in_cap = need_in;
+    }
+    if (need_out > c->inf_out_cap) {
+        cudaFree(c->d_inf_out); c->d_inf_out = nullptr; c->inf_out_cap = 0;
+        if (cudaMalloc(&c->d_inf_out, need_out) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate output buffer does not fit"); }
+        c->inf_out_cap = need_out;
     }
     return B2D_OK;
 }
 
 extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
                                 const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
-    if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n) || (!block_offsets && nblocks)) return fail(B2D_STREAM_ERROR, "null argument");
     if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
+    if (nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
+    if (nblocks > 0x0fffffffull) return fail(B2D_STREAM_ERROR, "too many blocks");
+    for (uint64_t b = 0; b < nblocks; ++b)
+        if (block_offsets[b] >= in_n || (b && block_offsets[b] <= block_offsets[b - 1])) return fail(B2D_STREAM_ERROR, "bad block index");
     if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
     std::lock_guard<std::recursive_mutex> whole(c->mu);      /* the device copies below belong to this call until it returns */
-    {
-        /* device copies of the stream (+ dictionary in front of it) and of the output: kept by the context, grown on demand */
-        CU(cudaSetDevice(c->device));
-        const uint64_t need_in = B2D_WINDOW + in_n + 64, need_out = raw_n + 64;
-        if (need_in > c->inf_in_cap) {
-            cudaFree(c->d_inf_in); c->d_inf_in = nullptr; c->inf_in_cap = 0;
-            if (cudaMalloc(&c->d_inf_in, need_in) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate input buffer does not fit"); }
-            c->inf_in_cap = need_in;
-        }
-        if (need_out > c->inf_out_cap) {
-            cudaFree(c->d_inf_out); c->d_inf_out = nullptr; c->inf_out_cap = 0;
-            if (cudaMalloc(&c->d_inf_out, need_out) != cudaSuccess) { cudaGetLastError(); return fail(B2D_MEM_ERROR, "inflate output buffer does not fit"); }
-            c->inf_out_cap = need_out;
-        }
-        if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, c->st));
-        CU(cudaMemcpyAsync(c->d_inf_in + B2D_WINDOW, in, in_n, cudaMemcpyHostToDevice, c->st));
+    CU(cudaSetDevice(c->device));
+    { int rc = inflate_host_buffers(c, in_n, raw_n); if (rc) return rc; }
+    { int rc = inflate_prepare(c, nblocks, raw_n, true); if (rc) return rc; }
+    if (!c->st_inf_in) {
+        CU(cudaStreamCreateWithFlags(&c->st_inf_in, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->st_inf_out, cudaStreamNonBlocking));
+        for (int i = 0; i < 4; ++i) CU(cudaStreamCreateWithFlags(&c->st_inf_dec[i], cudaStreamNonBlocking));
     }
-    int rc = b2d_inflate_device(c, c->d_inf_in + B2D_WINDOW, in_n, block_offsets, nblocks, dict_n ? c->d_inf_in : nullptr, dict_n,
-                                c->d_inf_out, raw_n, nullptr);
-    if (rc) return rc;
-    if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, c->st)); c->launches += crc_launches(c->d_inf_out, raw_n); }
-    CU(cudaMemcpyAsync(out, c->d_inf_out, raw_n, cudaMemcpyDeviceToHost, c->st));
+    const uint64_t nchunks = (nblocks + B2D_INF_CHUNK_BLOCKS - 1) / B2D_INF_CHUNK_BLOCKS;
+    while (c->ev_inf_h2d.size() < nchunks) {
+        cudaEvent_t e1, e2;
+        CU(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
+        c->ev_inf_h2d.push_back(e1);
+        CU(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+        c->ev_inf_done.push_back(e2);
+    }
+    const int mode = inflate_mode(c);
+    const bool conc = mode == B2D_INF_CONCURRENT;
+    uint8_t *d_stream = c->d_inf_in + B2D_WINDOW;
+    const uint8_t *d_dict = dict_n ? c->d_inf_in : nullptr;
+    /* Chunks of 512 blocks flow through three stages: the compressed bytes of chunk k + 1 go up (st_inf_in) while chunk
+     * k is decoded (one of four decode streams: a block takes a warp milliseconds, so neighbouring chunks must decode
+     * side by side to fill the device) and resolved (st_inf, which follows the decodes block by block) and the bytes of
+     * chunk k - 1 come back (st_inf_out).  The chain over the block tails runs through all chunks on st_inf. */
+    CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
+    CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
+    CU(cudaMemsetAsync(c->d_inf_flags, 0, nblocks * sizeof(uint32_t), c->st));
+    if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, c->st));
+    if (conc) {
+        CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* index, flags, error words, dictionary are in place */
+        CU(cudaStreamWaitEvent(c->st_inf, c->ev_inf_fork, 0));
+        for (int i = 0; i < 4; ++i) CU(cudaStreamWaitEvent(c->st_inf_dec[i], c->ev_inf_fork, 0));
+    }
+    cudaStream_t st_res = conc ? c->st_inf : c->st;                    /* where a chunk's bytes become final */
+    for (uint64_t k = 0; k < nchunks; ++k) {
+        const uint64_t b0 = k * B2D_INF_CHUNK_BLOCKS, b1 = b0 + B2D_INF_CHUNK_BLOCKS < nblocks ? b0 + B2D_INF_CHUNK_BLOCKS : nblocks;
+        const uint64_t lo = block_offsets[b0], hi = b1 < nblocks ? block_offsets[b1] : in_n;
+        cudaStream_t st_dec = conc ? c->st_inf_dec[k & 3] : c->st;
+        CU(cudaMemcpyAsync(d_stream + lo, in + lo, hi - lo, cudaMemcpyHostToDevice, c->st_inf_in));
+        CU(cudaEventRecord(c->ev_inf_h2d[k], c->st_inf_in));
+        CU(cudaStreamWaitEvent(st_dec, c->ev_inf_h2d[k], 0));
+        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, d_dict, (uint32_t)dict_n,
+                              c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_dec, st_res, mode));
+        c->launches += B2D_INF_LAUNCHES;
+        CU(cudaEventRecord(c->ev_inf_done[k], st_res));
+        CU(cudaStreamWaitEvent(c->st_inf_out, c->ev_inf_done[k], 0));
+        const uint64_t o0 = b0 * (uint64_t)B2D_BLOCK, o1 = b1 * (uint64_t)B2D_BLOCK < raw_n ? b1 * (uint64_t)B2D_BLOCK : raw_n;
+        CU(cudaMemcpyAsync(out + o0, c->d_inf_out + o0, o1 - o0, cudaMemcpyDeviceToHost, c->st_inf_out));
+        if (k + 1 == nchunks) {
+            if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, st_res)); c->launches += crc_launches(c->d_inf_out, raw_n); }
+            if (st_res != c->st) { CU(cudaEventRecord(c->ev_inf_join, st_res)); CU(cudaStreamWaitEvent(c->st, c->ev_inf_join, 0)); }
+        }
+    }
+    uint32_t err[2] = {0, 0};
+    CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
+    CU(cudaStreamSynchronize(c->st_inf_out));
+    if (err[1] && !err[0]) {
+        /* the pass over the tails gave up waiting for a decode (never a statement about the data): every block is decoded
+         * by now, so resolve everything again on one stream and fetch the bytes once more */
+        CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
+        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16,
+                              c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, c->st, c->st, B2D_INF_RESOLVE_ONLY));
+        c->launches += 2;
+        if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, c->st)); c->launches += crc_launches(c->d_inf_out, raw_n); }
+        CU(cudaMemcpyAsync(out, c->d_inf_out, raw_n, cudaMemcpyDeviceToHost, c->st));
+        CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        if (err[1] && !err[0]) return fail(B2D_CUDA_ERROR, "inflate: the resolving pass did not complete");
+    }
+    { int rc = inflate_verdict(err); if (rc) return rc; }
     if (crc) *crc = b2d_crc32_dev_finish(c->ck, raw_n, *crc);
+    return B2D_OK;
+}
+
+/* ------------------------------------------------------------------------- */
+/* BGZF (the blocked gzip of htslib / bgzip; the reference ships and reads one: tests/data/test.fastq.bgzip.gz,
+ * tests/test_gzip_ng.py:466-473): a series of gzip members of at most 64 KiB, each a complete DEFLATE stream without
+ * a dictionary, whose total size sits in a "BC" extra subfield — a block index for free. */
+/* ------------------------------------------------------------------------- */
+extern "C" int b2d_bgzf_scan(const uint8_t *buf, uint64_t n, uint64_t max_members, uint64_t *payload_off, uint32_t *payload_len,
+                             uint32_t *raw_len, uint32_t *crc, uint64_t *count, uint64_t *consumed) {
+    if (!count || !consumed || (!buf && n)) return fail(B2D_STREAM_ERROR, "null argument");
+    uint64_t pos = 0, k = 0;
+    while (k < max_members && pos + 18 <= n) {
+        const uint8_t *h = buf + pos;
+        if (h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || h[3] != 4) break;             /* a gzip member with FEXTRA and nothing else */
+        const uint32_t xlen = h[10] | (h[11] << 8);
+        if (pos + 12 + xlen > n) break;
+        uint32_t bsize = 0; bool found = false;
+        for (uint32_t o = 0; o + 4 <= xlen;) {                                         /* RFC 1952 2.3.1.1 subfields */
+            const uint8_t *f = h + 12 + o;
+            const uint32_t slen = f[2] | (f[3] << 8);
+            if (o + 4 + slen > xlen) break;
+            if (f[0] == 'B' && f[1] == 'C' && slen == 2) { bsize = (f[4] | (f[5] << 8)) + 1u; found = true; }
+            o += 4 + slen;
+        }
+        if (!found || bsize < 12u + xlen + 8u) break;
+        if (pos + bsize > n) break;                                                    /* member not complete in this buffer */
+        const uint8_t *t = h + bsize - 8;
+        const uint32_t isize = t[4] | (t[5] << 8) | (t[6] << 16) | ((uint32_t)t[7] << 24);
+        if (isize > 65536u) break;                                                     /* the format's limit */
+        if (payload_off) {
+            payload_off[k] = pos + 12 + xlen;
+            payload_len[k] = bsize - 12u - xlen - 8u;
+            crc[k] = t[0] | (t[1] << 8) | (t[2] << 16) | ((uint32_t)t[3] << 24);
+            raw_len[k] = isize;
+        }
+        pos += bsize;
+        ++k;
+    }
+    *count = k;
+    *consumed = pos;
+    return B2D_OK;
+}
+
+/* Inflate `nmembers` independent DEFLATE streams (host buffers): member i is in[payload_off[i], + payload_len[i]) and
+ * decodes to raw_len[i] bytes that land back to back in `out`.  One warp per member, bytes written directly.  `crcs`
+ * (optional): the CRC-32 every member must have — checked against one device CRC of the whole output, folded on the host
+ * with crc32_combine. */
+extern "C" int b2d_inflate_members_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *payload_off,
+                                        const uint32_t *payload_len, const uint32_t *raw_len, const uint32_t *crcs, uint64_t nmembers,
+                                        uint8_t *out, uint64_t out_cap, uint64_t *out_n) {
+    if (!c || !out_n || (!in && in_n) || (nmembers && (!payload_off || !payload_len || !raw_len))) return fail(B2D_STREAM_ERROR, "null argument");
+    if (nmembers > 0x0fffffffull) return fail(B2D_STREAM_ERROR, "too many members");
+    std::vector<uint64_t> idx(2 * nmembers + 2);
+    uint64_t *in_idx = idx.data(), *out_idx = idx.data() + nmembers;        /* out_idx has nmembers + 1 entries */
+    uint64_t total = 0;
+    uint32_t want = 0;
+    for (uint64_t i = 0; i < nmembers; ++i) {
+        if (payload_off[i] + payload_len[i] > in_n || raw_len[i] > 65536u) return fail(B2D_STREAM_ERROR, "bad member index");
+        in_idx[i] = payload_off[i];
+    }
+    for (uint64_t i = 0; i < nmembers; ++i) {
+        out_idx[i] = total;
+        if (crcs) want = b2d_host_crc32_combine(want, crcs[i], raw_len[i]);
+        total += raw_len[i];
+    }
+    out_idx[nmembers] = total;
+    *out_n = total;
+    if (total > out_cap) return fail(B2D_BUF_ERROR, "output buffer too small");
+    if (total == 0) return B2D_OK;
+    if (!out) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::recursive_mutex> whole(c->mu);
+    CU(cudaSetDevice(c->device));
+    { int rc = inflate_host_buffers(c, in_n, total); if (rc) return rc; }
+    { int rc = inflate_prepare(c, 2 * nmembers + 2, 0, false); if (rc) return rc; }
+    CU(cudaMemcpyAsync(c->d_inf_index, idx.data(), (2 * nmembers + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
+    CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
+    CU(cudaMemcpyAsync(c->d_inf_in, in, in_n, cudaMemcpyHostToDevice, c->st));
+    CU(b2d_launch_inflate_members(c->d_inf_in, in_n, c->d_inf_index, c->d_inf_index + nmembers, (uint32_t)nmembers, c->d_inf_out, total,
+                                  c->d_inf_err, c->st));
+    c->launches += 1;
+    if (crcs) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, total, c->st)); c->launches += crc_launches(c->d_inf_out, total); }
+    CU(cudaMemcpyAsync(out, c->d_inf_out, total, cudaMemcpyDeviceToHost, c->st));
+    uint32_t err[2] = {0, 0};
+    CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    { int rc = inflate_verdict(err); if (rc) return rc; }
+    if (crcs && b2d_crc32_dev_finish(c->ck, total, 0) != want) {
+        snprintf(g_err, sizeof g_err, "inflate: CRC check failed");
+        return -3;
+    }
     return B2D_OK;
 }

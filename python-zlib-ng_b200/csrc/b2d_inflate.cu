@@ -28,6 +28,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <type_traits>
 
 #include "b2d_common.h"
 #include "b2d_inflate.h"
@@ -123,30 +124,37 @@ __device__ __forceinline__ void inf_fill(uint16_t *tab, int tbits, const uint16_
     }
 }
 
+/* INDEP = false: the stream of this library — block b covers output bytes [b * 128 KiB, ...), may look 32 KiB behind
+ * its own start (markers), writes 16-bit symbols.  INDEP = true: independent members (BGZF: every member is its own
+ * DEFLATE stream without a dictionary) — block b covers [out_index[b], out_index[b + 1]), nothing may reach behind
+ * it, bytes are written as bytes and no resolving pass is needed.  A launch covers blocks [b0, b0 + nb). */
+template <bool INDEP>
 __global__ void __launch_bounds__(INF_WARPS * 32)
-k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__restrict__ index, uint32_t nblocks,
-             uint64_t raw_n, uint32_t dict_n, uint16_t *out16, uint32_t *flags, uint32_t *err) {
+k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__restrict__ index,
+             const uint64_t *__restrict__ out_index, uint32_t b0, uint32_t nb, uint64_t raw_n, uint32_t dict_n, void *outp,
+             uint32_t *flags, uint32_t *err) {
+    typedef typename std::conditional<INDEP, uint8_t, uint16_t>::type sym_t;
     __shared__ inf_warp s_w[INF_WARPS];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t b = blockIdx.x * INF_WARPS + warp;
-    if (b >= nblocks) return;
+    const uint32_t b = b0 + blockIdx.x * INF_WARPS + warp;
+    if (b >= b0 + nb) return;
     inf_warp *T = &s_w[warp];
-    const uint64_t bs = (uint64_t)b * B2D_BLOCK;
-    const uint32_t expect = (uint32_t)(raw_n - bs < B2D_BLOCK ? raw_n - bs : B2D_BLOCK);
+    const uint64_t bs = INDEP ? out_index[b] : (uint64_t)b * B2D_BLOCK;
+    const uint32_t expect = INDEP ? (uint32_t)(out_index[b + 1] - bs) : (uint32_t)(raw_n - bs < B2D_BLOCK ? raw_n - bs : B2D_BLOCK);
     /* how far behind its own start this block may reach: 32 KiB, or the caller's dictionary for block 0 */
-    const uint32_t reach = b == 0 ? dict_n : B2D_WINDOW;
-    uint16_t *o16 = out16 + bs;
+    const uint32_t reach = INDEP ? 0u : (b == 0 ? dict_n : B2D_WINDOW);
+    sym_t *o16 = reinterpret_cast<sym_t *>(outp) + bs;
     bitrd R;
     br_init(R, in, index[b], in_n);
     uint32_t produced = 0, fail = 0;
 
     while (produced < expect && !fail) {
         /* ---- block header (lane 0): type, and for dynamic blocks the code lengths into T->lens */
-        uint32_t type = 0, st_len = 0;
+        uint32_t type = 0, st_len = 0, bfinal = 0;
         uint64_t st_off = 0;
         if (lane == 0) {
             br_refill(R);
-            br_take(R, 1);                                  /* BFINAL: our writer never sets it on data blocks */
+            bfinal = br_take(R, 1);                         /* BFINAL: our writer never sets it on data blocks; members end with it */
             type = br_take(R, 2);
             if (type == 0) {
                 br_take(R, R.cnt & 7u);                     /* to the next byte boundary */
@@ -192,15 +200,17 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
             } else if (type == 3) type = 4;
         }
         type = __shfl_sync(FULL, type, 0);
+        bfinal = __shfl_sync(FULL, bfinal, 0);
         if (type == 4) { fail = 1; break; }
         if (type == 0) {
             st_len = __shfl_sync(FULL, st_len, 0);
             st_off = __shfl_sync(FULL, st_off, 0);
             if (produced + st_len > expect || st_off + st_len > in_n) { fail = 2; break; }
-            for (uint32_t i = lane; i < st_len; i += 32) o16[produced + i] = in[st_off + i];
+            for (uint32_t i = lane; i < st_len; i += 32) o16[produced + i] = (sym_t)in[st_off + i];
             produced += st_len;
             if (lane == 0) br_init(R, in, st_off + st_len, in_n);
             __syncwarp();
+            if (INDEP && bfinal) break;
             continue;
         }
         if (type == 1) {   /* fixed code: trees.c static_ltree / RFC 1951 3.2.6 */
@@ -222,7 +232,7 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
         for (;;) {
             uint32_t tok = 0, nlit = 0;
             if (lane == 0) {
-                uint16_t *lp = o16 + produced;
+                sym_t *lp = o16 + produced;
                 const uint32_t room = expect - produced;
                 for (;;) {
                     br_refill(R);
@@ -233,7 +243,7 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
                     br_take(R, len);
                     if (sym < 256) {
                         if (nlit >= room) { tok = INF_TOK_ERR; break; }
-                        lp[nlit++] = (uint16_t)sym;
+                        lp[nlit++] = (sym_t)sym;
                         continue;
                     }
                     if (sym == 256) { tok = INF_TOK_EOB; break; }
@@ -264,11 +274,12 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
                 const int rel = src0 + (int)(dist >= mlen ? i : i % dist);
                 /* before the block: a marker for byte (32768 + rel) of the 32 KiB that precede it */
                 const uint32_t v = rel < 0 ? 256u + (uint32_t)((int)B2D_WINDOW + rel) : (uint32_t)__ldcg(o16 + rel);
-                o16[produced + i] = (uint16_t)v;
+                o16[produced + i] = (sym_t)v;
             }
             produced += mlen;
             __syncwarp();
         }
+        if (INDEP && bfinal) break;                         /* a member is over after its final block, whatever its ISIZE says */
     }
     if (!fail && produced != expect) fail = 2;
     if (fail) {
@@ -279,7 +290,7 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
     }
     /* the block's symbols are in memory: k_inf_tails (running beside this kernel) may pick its tail up */
     __syncwarp();
-    if (lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = 1u; }
+    if (!INDEP && lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = 1u; }
 }
 
 /* the byte a marker stands for: `k` indexes the 32 KiB that precede the block starting at output byte bs */
@@ -312,8 +323,9 @@ __device__ __forceinline__ uint2 inf_resolve8(uint4 q, const uint8_t *out8, cons
 #define INF_TAIL_THREADS (B2D_WINDOW / 8 / INF_CLUSTER)      /* 512 */
 #define INF_READY_GROUP 32u                                  /* decode flags are polled for this many blocks at a time */
 __global__ void __launch_bounds__(INF_TAIL_THREADS)
-k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n, uint32_t nblocks,
-            uint64_t raw_n, const uint32_t *flags, uint32_t *err) {
+k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n, uint32_t b0, uint32_t b1,
+            uint32_t nblocks, uint64_t raw_n, const uint32_t *flags, uint32_t *err) {
+    /* blocks [b0, b1) of the stream's nblocks: the tail of block b0 - 1 was resolved by the launch before this one */
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t t = blockIdx.x * INF_TAIL_THREADS + threadIdx.x;          /* 0 .. 4095: one group of 8 symbols */
     const uint32_t nfull = (uint32_t)(raw_n / B2D_BLOCK);          /* blocks of 128 KiB: their tails are aligned */
@@ -339,21 +351,23 @@ k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ di
     };
     auto load = [&](uint32_t b) { return __ldcg(reinterpret_cast<const uint4 *>(out16 + (uint64_t)b * B2D_BLOCK + toff)); };
     uint4 cur = make_uint4(0, 0, 0, 0), nxt = cur;
-    if (nfull) {
-        wait_ready(0, nfull < INF_READY_GROUP ? nfull : INF_READY_GROUP);
-        cur = load(0);
+    const uint32_t e_full = b1 < nfull ? b1 : nfull;              /* end of the full blocks of this launch */
+    if (b0 < e_full) {
+        const uint32_t g = (b0 / INF_READY_GROUP + 1u) * INF_READY_GROUP;
+        wait_ready(b0, g < e_full ? g : e_full);
+        cur = load(b0);
     }
-    for (uint32_t b = 0; b < nfull; ++b) {
+    for (uint32_t b = b0; b < e_full; ++b) {
         const uint64_t bs = (uint64_t)b * B2D_BLOCK;
-        if (b + 1 < nfull) {
-            if ((b + 1) % INF_READY_GROUP == 0) wait_ready(b + 1, b + 1 + INF_READY_GROUP < nfull ? b + 1 + INF_READY_GROUP : nfull);
+        if (b + 1 < e_full) {
+            if ((b + 1) % INF_READY_GROUP == 0) wait_ready(b + 1, b + 1 + INF_READY_GROUP < e_full ? b + 1 + INF_READY_GROUP : e_full);
             nxt = load(b + 1);
         }
         *reinterpret_cast<uint2 *>(out8 + bs + toff) = inf_resolve8(cur, out8, dict, dict_n, bs);
         cluster.sync();
         cur = nxt;
     }
-    if (nfull < nblocks) {   /* the last, shorter block: nobody depends on it */
+    if (b1 == nblocks && nfull < nblocks) {   /* the last, shorter block: nobody depends on it */
         wait_ready(nfull, nblocks);
         const uint64_t bs = (uint64_t)nfull * B2D_BLOCK;
         const uint64_t ts = raw_n - bs > B2D_WINDOW ? raw_n - B2D_WINDOW : bs;
@@ -366,8 +380,8 @@ k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ di
 
 __global__ void __launch_bounds__(256)
 k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *__restrict__ dict, uint32_t dict_n,
-             uint64_t raw_n) {
-    const uint64_t bs = (uint64_t)blockIdx.x * B2D_BLOCK;
+             uint64_t raw_n, uint32_t b0) {
+    const uint64_t bs = (uint64_t)(b0 + blockIdx.x) * B2D_BLOCK;
     const uint64_t be = raw_n - bs < B2D_BLOCK ? raw_n : bs + B2D_BLOCK;
     const uint64_t ts = be - bs > B2D_WINDOW ? be - B2D_WINDOW : bs;      /* [ts, be) was written by k_inf_tails */
     for (uint64_t p = bs + 8ull * threadIdx.x; p < ts; p += 8ull * 256) {
@@ -377,15 +391,15 @@ k_inf_finish(const uint16_t *__restrict__ out16, uint8_t *out8, const uint8_t *_
     }
 }
 
-static cudaError_t launch_tails(const uint16_t *d_out16, uint8_t *d_out, const uint8_t *d_dict, uint32_t dict_n, uint32_t nblocks,
-                                uint64_t raw_n, const uint32_t *d_flags, uint32_t *d_err, cudaStream_t st) {
+static cudaError_t launch_tails(const uint16_t *d_out16, uint8_t *d_out, const uint8_t *d_dict, uint32_t dict_n, uint32_t b0, uint32_t b1,
+                                uint32_t nblocks, uint64_t raw_n, const uint32_t *d_flags, uint32_t *d_err, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(INF_CLUSTER); cfg.blockDim = dim3(INF_TAIL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = INF_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, k_inf_tails, d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err);
+    return cudaLaunchKernelEx(&cfg, k_inf_tails, d_out16, d_out, d_dict, dict_n, b0, b1, nblocks, raw_n, d_flags, d_err);
 }
 
 /* Dynamic shared memory that k_inf_decode asks for without using it: with it 12 of its CTAs (48 warps) fit an SM
@@ -393,34 +407,32 @@ static cudaError_t launch_tails(const uint16_t *d_out16, uint8_t *d_out, const u
  * finds room beside the decode whenever the device can run two kernels at once. */
 #define INF_DECODE_PAD 1024
 
-cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t nblocks,
+/* One chunk: blocks [b0, b0 + nb) of a stream of nblocks; chunks are issued in order (the tails of chunk c build on
+ * those of chunk c - 1).  The caller has cleared d_flags / d_err for the whole stream and made both streams wait for that. */
+cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t b0, uint32_t nb, uint32_t nblocks,
                                const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
-                               uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st, cudaStream_t st_tails,
-                               cudaEvent_t ev_fork, cudaEvent_t ev_join, int mode) {
-    if (nblocks == 0) return cudaSuccess;
+                               uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st_dec, cudaStream_t st_res, int mode) {
+    if (nb == 0) return cudaSuccess;
     cudaError_t e;
-    if (mode == B2D_INF_RESOLVE_ONLY) {
-        /* the decode of an earlier launch is complete (the caller synchronised): resolve on one stream */
-        if ((e = launch_tails(d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err, st)) != cudaSuccess) return e;
-        k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
-        return cudaGetLastError();
+    if (mode != B2D_INF_RESOLVE_ONLY) {
+        /* The decode goes first (in host order) and waits for nobody. */
+        k_inf_decode<false><<<(nb + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st_dec>>>(d_in, in_n, d_index, nullptr, b0, nb,
+                                                                                                         raw_n, dict_n, d_out16, d_flags, d_err);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
-    if ((e = cudaMemsetAsync(d_flags, 0, nblocks * sizeof(uint32_t), st)) != cudaSuccess) return e;
-    /* The decode goes first and waits for nobody.  B2D_INF_SERIAL: everything on one stream (chosen by the caller
-     * where kernels cannot overlap anyway); otherwise the serial pass over the tails starts right behind it on its
-     * own (high-priority) stream and follows the decode through d_flags. */
-    if (mode != B2D_INF_SERIAL) {
-        if ((e = cudaEventRecord(ev_fork, st)) != cudaSuccess) return e;          /* flags are cleared */
-        if ((e = cudaStreamWaitEvent(st_tails, ev_fork, 0)) != cudaSuccess) return e;
-    } else st_tails = st;
-    k_inf_decode<<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st>>>(d_in, in_n, d_index, nblocks, raw_n,
-                                                                                              dict_n, d_out16, d_flags, d_err);
-    if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    if ((e = launch_tails(d_out16, d_out, d_dict, dict_n, nblocks, raw_n, d_flags, d_err, st_tails)) != cudaSuccess) return e;
-    if (mode != B2D_INF_SERIAL) {
-        if ((e = cudaEventRecord(ev_join, st_tails)) != cudaSuccess) return e;
-        if ((e = cudaStreamWaitEvent(st, ev_join, 0)) != cudaSuccess) return e;
-    }
-    k_inf_finish<<<nblocks, 256, 0, st>>>(d_out16, d_out, d_dict, dict_n, raw_n);
+    /* The serial pass over the tails is launched right behind it — on its own (high-priority) stream when the device
+     * runs kernels side by side, where it follows the decode through d_flags — and the rest of each block is resolved
+     * on that stream too.  B2D_INF_SERIAL / B2D_INF_RESOLVE_ONLY: the caller passes st_res == st_dec. */
+    if ((e = launch_tails(d_out16, d_out, d_dict, dict_n, b0, b0 + nb, nblocks, raw_n, d_flags, d_err, st_res)) != cudaSuccess) return e;
+    k_inf_finish<<<nb, 256, 0, st_res>>>(d_out16, d_out, d_dict, dict_n, raw_n, b0);
+    return cudaGetLastError();
+}
+
+/* independent members (BGZF): every block decodes straight to bytes, nothing to resolve */
+cudaError_t b2d_launch_inflate_members(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, const uint64_t *d_out_index,
+                                       uint32_t nblocks, uint8_t *d_out, uint64_t raw_n, uint32_t *d_err, cudaStream_t st) {
+    if (nblocks == 0) return cudaSuccess;
+    k_inf_decode<true><<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, d_out_index, 0, nblocks, raw_n,
+                                                                                       0, d_out, nullptr, d_err);
     return cudaGetLastError();
 }

@@ -73,6 +73,9 @@ SIGNATURES = {
                                               _u8p, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u64), _u64, _P(_u64)]),
     "b2d_compress_and_crc_multi": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
                                                   _P(_u64), _P(_u32), _P(_u64), _u64, _P(_u64)]),
+    "b2d_bgzf_scan": (ctypes.c_int, [_u8p, _u64, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u32), _P(_u64), _P(_u64)]),
+    "b2d_inflate_members_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u32), _u64, _u8p, _u64,
+                                                _P(_u64)]),
     "b2d_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "b2d_profile_read": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_double), _P(_u64), ctypes.c_int]),
 }

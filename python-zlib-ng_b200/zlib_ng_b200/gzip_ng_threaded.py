@@ -62,6 +62,7 @@ _LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size
 _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
 _READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "512")), 1) * 8    # device blocks the reader decodes per GPU call
+_BGZF_WINDOW = max(int(os.environ.get("B2D_BGZF_WINDOW_MIB", "32")), 1) << 20       # compressed bytes of a BGZF file per GPU call
 
 
 def _extra_member(payload: bytes) -> bytes:
@@ -85,7 +86,7 @@ def _parse_extra_member(buf: bytes, off: int):
     return buf[off + 16:off + 16 + n], end + 10
 
 
-_COPY_THREADS = max(int(os.environ.get("B2D_COPY_THREADS", "8")), 1)
+_COPY_THREADS = max(int(os.environ.get("B2D_COPY_THREADS", "16")), 1)
 
 
 def _parallel_copy(dst_addr: int, src, nbytes: int) -> None:
@@ -119,6 +120,10 @@ class _PinnedPool:
         return ptr, view
 
     def put(self, size, ptr, view):
+        global _POOL_KEEP
+        if _POOL_KEEP is None:
+            env = os.environ.get("B2D_PINNED_POOL_MIB")
+            _POOL_KEEP = (int(env) << 20) if env else _pool_keep_default()
         with self._lock:
             if self._kept + size <= _POOL_KEEP:
                 self._kept += size
@@ -128,7 +133,21 @@ class _PinnedPool:
         _native.pinned_free(ptr)
 
 
-_POOL_KEEP = int(os.environ.get("B2D_PINNED_POOL_MIB", "4096")) << 20
+def _pool_keep_default():
+    """4 GiB per GPU the process can see (a writer over 8 GPUs cycles through ~14 GiB of batches), at most an eighth of
+    the machine's memory"""
+    try:
+        ndev = max(_native.lib().b2d_device_count(), 1)
+    except Exception:
+        ndev = 1
+    try:
+        phys = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES")
+    except (ValueError, OSError):
+        phys = 64 << 30
+    return min(ndev * (4 << 30), phys // 8)
+
+
+_POOL_KEEP = None          # bytes the pool may keep; set on first use (B2D_PINNED_POOL_MIB overrides)
 _pinned_pool = _PinnedPool()
 
 
@@ -225,7 +244,7 @@ class _ThreadedGzipReader(io.RawIOBase):
         self._gpu = None
         if _GPU_READ:
             try:
-                self._gpu = self._find_index()
+                self._gpu = self._find_index() or self._find_bgzf()
             except Exception:
                 self._gpu = None
         self.fileobj = None if self._gpu else _stdgzip.GzipFile(fileobj=self.raw, mode="rb")
@@ -367,9 +386,122 @@ class _ThreadedGzipReader(io.RawIOBase):
         except BaseException as e:       # surfaces in the reading thread
             g["ready"].put(e)
 
+    # ---- BGZF: blocked gzip as written by bgzip / htslib.  Every member carries its compressed size in a "BC" extra
+    # subfield and is an independent DEFLATE stream of at most 64 KiB, so the members of a window decode side by side
+    # (one warp each) without any index of ours.  The reference reads these files with its one inflate thread
+    # (tests/test_gzip_ng.py:466-473, fixture tests/data/test.fastq.bgzip.gz).
+    def _find_bgzf(self):
+        raw = self.raw
+        if not (hasattr(raw, "seekable") and raw.seekable()):
+            return None
+        here = raw.tell()
+        try:
+            head = raw.read(18)
+        finally:
+            raw.seek(here)
+        if len(head) < 18 or head[:4] != b"\x1f\x8b\x08\x04":
+            return None
+        xlen = struct.unpack_from("<H", head, 10)[0]
+        # the first header must hold a BC subfield (bgzip writes it first); whether the member is complete is found out
+        # while reading
+        o, ok = 12, False
+        while o + 4 <= 12 + xlen and o + 4 <= len(head):
+            si, slen = head[o:o + 2], struct.unpack_from("<H", head, o + 2)[0]
+            if si == b"BC" and slen == 2:
+                ok = True
+                break
+            o += 4 + slen
+        if not ok:
+            return None
+        _native.default_context()      # no usable GPU: the CPU reader takes over (raises here)
+        return {"kind": "bgzf", "raw_n": None}
+
+    def _bgzf_worker(self):
+        """Reads a window of compressed bytes, finds its complete members (b2d_bgzf_scan), inflates them in one call
+        (b2d_inflate_members_host: one warp per member, CRCs checked on the device) into a pinned buffer; whatever is
+        left over (a partial member) starts the next window."""
+        g = self._gpu
+        L, ctx = _native.lib(), _native.default_context()
+        win, cap = g["win"], g["out_cap"]
+        comp_ptr, comp_view = g["comp"]
+        try:
+            keep = 0                                  # bytes at the start of comp_view carried over from the last window
+            maxm = win // 28 + 16
+            po, pl = (ctypes.c_uint64 * maxm)(), (ctypes.c_uint32 * maxm)()
+            rl, cr = (ctypes.c_uint32 * maxm)(), (ctypes.c_uint32 * maxm)()
+            eof = False
+            while not g["stop"]:
+                while keep < win and not eof:
+                    k = self.raw.readinto(comp_view[keep:win])
+                    if not k:
+                        eof = True
+                        break
+                    keep += k
+                if keep == 0 and eof:
+                    g["ready"].put(None)
+                    return
+                cnt, used = ctypes.c_uint64(0), ctypes.c_uint64(0)
+                _native.check(L.b2d_bgzf_scan(comp_ptr, keep, maxm, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)))
+                n = cnt.value
+                if n == 0:
+                    # not (or no longer) BGZF: a partial member at the end of the file, trailing zero padding, or an
+                    # ordinary gzip member appended to the file — CPython's reader takes the rest, errors included
+                    rest = bytes(comp_view[:keep])
+                    g["ready"].put(("cpu", _stdgzip.GzipFile(fileobj=_Prefixed(rest, self.raw), mode="rb")))
+                    return
+                # as many members as fit the output buffer
+                total, take = 0, 0
+                while take < n and total + rl[take] <= cap:
+                    total += rl[take]
+                    take += 1
+                consumed = used.value if take == n else po[take - 1] + pl[take - 1] + 8
+                out = None
+                while out is None:
+                    try:
+                        out = g["free"].get(timeout=0.05)
+                    except queue.Empty:
+                        if g["stop"]:
+                            return
+                out_n = ctypes.c_uint64(0)
+                rc = L.b2d_inflate_members_host(ctx.handle, comp_ptr, keep, po, pl, rl, cr, take, out[0], cap, ctypes.byref(out_n))
+                if rc:
+                    g["free"].put(out)
+                    msg = _native.last_error()
+                    if "CRC" in msg:
+                        raise _stdgzip.BadGzipFile("CRC check failed")
+                    raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {msg}")
+                if out_n.value:
+                    g["ready"].put((out, out_n.value))
+                else:
+                    g["free"].put(out)
+                rest = keep - consumed
+                if rest:
+                    ctypes.memmove(comp_ptr, comp_ptr + consumed, rest)
+                keep = rest
+        except BaseException as e:       # surfaces in the reading thread
+            g["ready"].put(e)
+
+    def _bgzf_start(self):
+        g = self._gpu
+        g["win"] = _BGZF_WINDOW
+        g["out_cap"] = _BGZF_WINDOW * 4
+        g["pinned"] = []
+        g["free"], g["ready"], g["stop"] = queue.Queue(), queue.Queue(), False
+        ent = (g["win"] + 16,) + _pinned_pool.get(g["win"] + 16)
+        g["pinned"].append(ent)
+        g["comp"] = ent[1:]
+        for _ in range(2):
+            ent = (g["out_cap"] + 16,) + _pinned_pool.get(g["out_cap"] + 16)
+            g["pinned"].append(ent)
+            g["free"].put(ent[1:])
+        g["cur"], g["cur_n"], g["off"], g["eof"] = None, 0, 0, False
+        g["threads"] = [threading.Thread(target=self._bgzf_worker, daemon=True)]
+        g["threads"][0].start()
+
     def _gpu_start(self):
         g = self._gpu
-        ctx = _native.default_context()
+        if g.get("kind") == "bgzf":
+            return self._bgzf_start()
         sizes = g["sizes"]
 
         def bucket(n):       # few distinct sizes, so that the pinned pool can hand buffers to the next reader
@@ -415,6 +547,10 @@ class _ThreadedGzipReader(io.RawIOBase):
         g = self._gpu
         if "threads" not in g:
             self._gpu_start()
+        if g.get("cpu") is not None:             # the rest of a BGZF file that stopped being BGZF
+            n = g["cpu"].readinto(b)
+            self.pos += n
+            return n
         if g["cur"] is None or g["off"] >= g["cur_n"]:
             if g["cur"] is not None:
                 g["free"].put(g["cur"])
@@ -430,6 +566,9 @@ class _ThreadedGzipReader(io.RawIOBase):
             if isinstance(item, BaseException):
                 g["error"] = item
                 raise item
+            if item[0] == "cpu":
+                g["cpu"] = item[1]
+                return self.readinto(b)
             g["cur"], g["cur_n"] = item
             g["off"] = 0
         mv = memoryview(b).cast("B")
@@ -455,6 +594,13 @@ class _ThreadedGzipReader(io.RawIOBase):
             data = self.fileobj.read()
             self.pos += len(data)
             return data
+        if self._gpu["raw_n"] is None:           # BGZF: the size is not known in advance
+            parts, box = [], bytearray(16 << 20)
+            while True:
+                k = self.readinto(box)
+                if not k:
+                    return b"".join(parts)
+                parts.append(bytes(memoryview(box)[:k]))
         left = self._gpu["raw_n"] - self.pos
         if left <= 0:
             self.readinto(bytearray(1))      # runs the end-of-member checks
@@ -493,6 +639,25 @@ class _ThreadedGzipReader(io.RawIOBase):
     @property
     def closed(self) -> bool:
         return self._closed
+
+
+class _Prefixed(io.RawIOBase):
+    """bytes already taken from a stream, then the rest of the stream"""
+
+    def __init__(self, head: bytes, raw):
+        self._head, self._raw = head, raw
+
+    def readable(self):
+        return True
+
+    def readinto(self, b):
+        mv = memoryview(b).cast("B")
+        if self._head:
+            k = min(len(mv), len(self._head))
+            mv[:k] = self._head[:k]
+            self._head = self._head[k:]
+            return k
+        return self._raw.readinto(mv) or 0
 
 
 class FlushableBufferedWriter(io.BufferedWriter):
@@ -544,7 +709,10 @@ class _ThreadedGzipWriter(io.RawIOBase):
         nw = len(self._contexts)
         # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece per device
         nominal = max(block_size * threads // nw, 1)
-        self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, _STREAM_BATCH * len(devices))
+        # (several devices: half as much per device and call — two calls are in flight, and the pinned batches of a
+        # writer over 8 GPUs would otherwise add up to 16 GiB)
+        per_dev = _STREAM_BATCH if len(devices) == 1 else max(_STREAM_BATCH // 2, 2 * _CTX_BATCH)
+        self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, per_dev * len(devices))
         self._out_cap = self.batch + max(self.batch // 10, 500)
         # the first batches of a file go out early (a quarter, then half of the full size), so that the GPUs start
         # while the caller is still writing and short files do not wait for a batch that never fills

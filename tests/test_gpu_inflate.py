@@ -373,3 +373,109 @@ print("READ_SECONDS", dt)
     secs = float(p.stdout.split("READ_SECONDS")[1].split()[0])
     assert secs < 2.0, f"reading took {secs:.2f} s"
     del t0
+
+
+# ---- BGZF (blocked gzip, htslib / bgzip): members carry their size in a "BC" extra subfield; the reference reads its
+# fixture tests/data/test.fastq.bgzip.gz with one inflate thread (tests/test_gzip_ng.py:466-473)
+def make_bgzf(data: bytes, blk: int = 65280, level: int = 6, eof_marker: bool = True) -> bytes:
+    import struct
+    out = []
+    pieces = [data[o:o + blk] for o in range(0, len(data), blk)] + ([b""] if eof_marker else [])
+    for piece in pieces:
+        c = zlib.compressobj(level, zlib.DEFLATED, -15)
+        body = c.compress(piece) + c.flush()
+        out.append(b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff\x06\x00BC\x02\x00" + struct.pack("<H", len(body) + 25) + body
+                   + struct.pack("<II", zlib.crc32(piece), len(piece)))
+    return b"".join(out)
+
+
+def test_bgzf_files_are_inflated_on_the_gpu(gzt, tmp_path, monkeypatch):
+    import gzip
+    import io
+    data = synthdata.make("fastq", 9_000_000, 81).tobytes() + synthdata.make("mixed", 3_000_000, 82).tobytes()
+    blob = make_bgzf(data)
+    assert gzip.decompress(blob) == data                            # an ordinary multi-member gzip file to everyone else
+    path = tmp_path / "x.bgzip.gz"
+    path.write_bytes(blob)
+    for window in (1 << 20, 32 << 20):                              # a small window: members carried over between calls
+        monkeypatch.setattr(gzt, "_BGZF_WINDOW", window)
+        with gzt.open(path, "rb") as f:
+            assert f.raw._gpu is not None and f.raw._gpu["kind"] == "bgzf"
+            assert f.read() == data
+        with gzt.open(path, "rb") as f:
+            assert f.read(1000) == data[:1000] and f.tell() == 1000
+            assert f.read(5_000_000) == data[1000:5_001_000]
+    with gzt.open(path, "rt", encoding="latin-1") as f:
+        assert f.readline() == data[:data.index(b"\n") + 1].decode("latin-1")
+    # stored members (level 0) and members of a few bytes
+    small = make_bgzf(data[:200_000], blk=1000, level=0)
+    with gzt.open(io.BytesIO(small), "rb") as f:
+        assert f.raw._gpu["kind"] == "bgzf" and f.read() == data[:200_000]
+    # a flipped bit inside a member: decode error or CRC mismatch, reported like a damaged gzip file
+    bad = bytearray(blob)
+    bad[len(blob) // 2] ^= 0x04
+    with gzt.open(io.BytesIO(bytes(bad)), "rb") as f:
+        with pytest.raises((gzip.BadGzipFile, EOFError, OSError, zlib.error)):
+            f.read()
+    # an ordinary gzip member appended to a BGZF file: the rest is read the ordinary way
+    mixed = make_bgzf(data[:3_000_000], eof_marker=False) + gzip.compress(data[3_000_000:4_000_000])
+    with gzt.open(io.BytesIO(mixed), "rb") as f:
+        assert f.raw._gpu["kind"] == "bgzf" and f.read() == data[:4_000_000]
+    # a file cut off inside a member: EOFError, as gzip reports it
+    with gzt.open(io.BytesIO(blob[:len(blob) // 2]), "rb") as f:
+        with pytest.raises(EOFError):
+            f.read()
+
+
+def test_inflate_members_through_the_c_abi(nat, ctx):
+    L = nat.lib()
+    data = synthdata.make("mixed", 2_000_000, 83).tobytes()
+    blob = make_bgzf(data)
+    n = len(blob)
+    m = n // 28 + 16
+    po, pl = (ctypes.c_uint64 * m)(), (ctypes.c_uint32 * m)()
+    rl, cr = (ctypes.c_uint32 * m)(), (ctypes.c_uint32 * m)()
+    cnt, used = ctypes.c_uint64(0), ctypes.c_uint64(0)
+    nat.check(L.b2d_bgzf_scan(blob, n, m, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)))
+    assert used.value == n and sum(rl[:cnt.value]) == len(data)
+    out = ctypes.create_string_buffer(len(data))
+    out_n = ctypes.c_uint64(0)
+    nat.check(L.b2d_inflate_members_host(ctx.handle, blob, n, po, pl, rl, cr, cnt.value, out, len(data), ctypes.byref(out_n)))
+    assert out_n.value == len(data) and out.raw == data
+    # wrong CRC for one member: -3, like a damaged member
+    cr[3] ^= 1
+    assert L.b2d_inflate_members_host(ctx.handle, blob, n, po, pl, rl, cr, cnt.value, out, len(data), ctypes.byref(out_n)) == -3
+    assert "CRC" in nat.last_error()
+    cr[3] ^= 1
+    # output buffer too small, and a member that claims more than it holds
+    assert L.b2d_inflate_members_host(ctx.handle, blob, n, po, pl, rl, cr, cnt.value, out, 1000, ctypes.byref(out_n)) == nat.B2D_BUF_ERROR
+    rl[2] -= 1
+    assert L.b2d_inflate_members_host(ctx.handle, blob, n, po, pl, rl, None, cnt.value, out, len(data), ctypes.byref(out_n)) == -3
+    rl[2] += 1
+    nat.check(L.b2d_inflate_members_host(ctx.handle, blob, n, po, pl, rl, cr, cnt.value, out, len(data), ctypes.byref(out_n)))
+    assert out.raw == data
+
+
+def test_host_inflate_over_many_chunks(nat):
+    """b2d_inflate_host pipelines chunks of 512 blocks (H2D / decode / resolve / D2H side by side, the chain over the
+    block tails running through all of them): 1300 blocks = 3 chunks, with a dictionary, CRC continued on the device."""
+    L = nat.lib()
+    c = nat.Context(0, 64 << 20)
+    try:
+        n = 1300 * BLOCK - 4321
+        base = synthdata.make("mixed", 24_000_000, 84).tobytes()
+        data = (base * (n // len(base) + 1))[:n]
+        zdict = base[-30_000:]
+        stream, offs, d_buf, d_out, _ = deflate_indexed(nat, c, data, 6, zdict)
+        c.device_free(d_buf)
+        c.device_free(d_out)
+        nb = len(offs) - 1
+        arr = (ctypes.c_uint64 * nb)(*offs[:nb])
+        out = ctypes.create_string_buffer(n)
+        for rep in range(2):
+            crc = ctypes.c_uint32(zlib.crc32(b"before"))
+            nat.check(L.b2d_inflate_host(c.handle, stream, len(stream), arr, nb, zdict, len(zdict), out, n, ctypes.byref(crc)))
+            assert out.raw == data
+            assert crc.value == zlib.crc32(data, zlib.crc32(b"before"))
+    finally:
+        c.close()
