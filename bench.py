@@ -43,7 +43,7 @@ STAGES = ["k_chains", "k_match", "k_parse", "k_plan", "k_scan", "k_emit"]
 # capture of a 256 MiB level-6 batch of this workload (profiles/README.md names the capture the figures come from)
 NCU_DRAM_BYTES_PER_INPUT_BYTE = {"k_chains": 3.57, "k_match": 7.33, "k_parse": 9.32, "k_plan": 0.063,
                                  "k_scan": 0.004, "k_emit": 2.01}
-NCU_SOURCE = "profiles/ncu_r1_e_summary.txt"
+NCU_SOURCE = "profiles/ncu_r2_summary.txt"
 
 
 # ---------------------------------------------------------------------------------------------- workload
@@ -393,8 +393,12 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     alg_bytes_per_launch = (1.0 + out_n / n) * n * a.steps / max(int(stage_n[top]), 1)
     achieved = alg_bytes_per_launch / (stage_ms[top] / max(int(stage_n[top]), 1) * 1e-3) / 1e9
+    achieved_alone = alg_bytes_per_launch / (alone_ms[top] / max(int(stage_n[top]) // a.steps, 1) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak,
+                "frac": achieved / peak, "achieved_alone": achieved_alone, "frac_alone": achieved_alone / peak,
+                "durations": "achieved: CUDA events around the kernel inside the timed region, where two batches overlap on two "
+                             "streams (a stage's time includes what it shares the SMs with); achieved_alone: the same kernel "
+                             "with one batch in flight (b2d_profile mode 2, one pass after the timed region)",
                 "traffic": NCU_DRAM_BYTES_PER_INPUT_BYTE[STAGES[top]] * n * a.steps / max(int(stage_n[top]), 1),
                 "traffic_source": f"ncu --set full capture of one launch ({NCU_SOURCE}), DRAM bytes per "
                                   "input byte x input bytes per launch",

@@ -440,17 +440,23 @@ static void fill_job(b2d_ctx *c, b2d_job *J, const uint8_t *buf, uint64_t D, uin
 }
 
 /* second set of intermediates + its stream: only multi-batch calls pay for them */
-static int ensure_second_lane(b2d_ctx *c) {
-    if (c->ev_fork) return B2D_OK;
-    c->stl[0] = c->st;
-    for (int i = 1; i < B2D_NLANE; ++i) { CU(work_alloc(&c->wk[i], c->max_batch)); CU(cudaStreamCreateWithFlags(&c->stl[i], cudaStreamNonBlocking)); }
-    for (int i = 0; i < B2D_NLANE; ++i) {
-        CU(cudaEventCreateWithFlags(&c->ev_scan[i], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
+static int ensure_lanes(b2d_ctx *c, int want) {
+    if (!c->ev_fork) {
+        c->stl[0] = c->st;
+        for (int i = 0; i < B2D_NLANE; ++i) {
+            CU(cudaEventCreateWithFlags(&c->ev_scan[i], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
+        }
+        CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     }
-    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (int i = 1; i < want && i < B2D_NLANE; ++i)
+        if (!c->stl[i]) { CU(work_alloc(&c->wk[i], c->max_batch)); CU(cudaStreamCreateWithFlags(&c->stl[i], cudaStreamNonBlocking)); }
     return B2D_OK;
 }
+static int ensure_second_lane(b2d_ctx *c) { return ensure_lanes(c, B2D_NLANE); }
+/* lanes a device-resident call uses: two batches of 128 MiB or more fill the device (k_chains: one warp per 128 KiB
+ * block, 1776 warp slots), so more lanes would only hold memory (2.7 GiB each at 256 MiB); smaller batches use all four */
+static int device_lanes(const b2d_ctx *c) { return c->max_batch >= (128ull << 20) ? 2 : B2D_NLANE; }
 
 /* kernels one batch launches at this level / strategy */
 static uint32_t pipeline_launches(int level) {
@@ -525,20 +531,21 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
     /* several batches alternate between two lanes (streams + intermediates); b2d_profile(ctx, 2) keeps
      * one lane so that the stage times are those of kernels running alone */
     const bool two = n > c->max_batch && c->profiling != 2;
+    const int NL = device_lanes(c);
     if (two) {
-        int rc = ensure_second_lane(c); if (rc) return rc;
+        int rc = ensure_lanes(c, NL); if (rc) return rc;
         CU(cudaEventRecord(c->ev_fork, c->st));
-        for (int i = 1; i < B2D_NLANE; ++i) CU(cudaStreamWaitEvent(c->stl[i], c->ev_fork, 0));
+        for (int i = 1; i < NL; ++i) CU(cudaStreamWaitEvent(c->stl[i], c->ev_fork, 0));
     }
     uint64_t jb = 0;
     for (uint64_t off = 0; off < n; off += c->max_batch, ++jb) {
         const uint64_t m = n - off < c->max_batch ? n - off : c->max_batch;
-        const int lane = two ? (int)(jb % B2D_NLANE) : 0;
+        const int lane = two ? (int)(jb % NL) : 0;
         /* re-base so the work buffers are indexed from (at most) 32 KiB + 15 bytes before the batch */
         const uint64_t abs0 = dict_n + off;
         const uint64_t base = abs0 > B2D_WINDOW ? (abs0 - B2D_WINDOW) & ~(uint64_t)15 : 0;
         b2d_job J; fill_job(c, &J, d_buf + base, abs0 - base, m, readable - base, level, d_out, B2D_WINDOW, lane);
-        if (two) { J.scan_wait = jb ? c->ev_scan[(lane + B2D_NLANE - 1) % B2D_NLANE] : nullptr; J.scan_done = c->ev_scan[lane]; }
+        if (two) { J.scan_wait = jb ? c->ev_scan[(lane + NL - 1) % NL] : nullptr; J.scan_done = c->ev_scan[lane]; }
         cudaEvent_t *pe = nullptr;
         if (c->profiling) {
             if (nprof == PROF_BATCHES) { int rc = prof_drain(c, nprof, level); if (rc) return rc; nprof = 0; }
@@ -552,7 +559,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
         CU(cudaMemcpyAsync(c->d_index + off / B2D_BLOCK, J.block_off, (nb + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
                            lane ? c->stl[lane] : c->st));
     }
-    if (two) for (int i = 1; i < B2D_NLANE; ++i) { CU(cudaEventRecord(c->ev_join[i], c->stl[i])); CU(cudaStreamWaitEvent(c->st, c->ev_join[i], 0)); }
+    if (two) for (int i = 1; i < NL; ++i) { CU(cudaEventRecord(c->ev_join[i], c->stl[i])); CU(cudaStreamWaitEvent(c->st, c->ev_join[i], 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
     CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     if (ms) CU(cudaEventRecord(c->ev1, c->st));

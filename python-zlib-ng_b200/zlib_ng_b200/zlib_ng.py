@@ -15,11 +15,20 @@ compressobj/_Compress  zlib_compressobj_impl, Compress.compress/flush/copy
 _ParallelCompress      ParallelCompress_compress_and_crc (:1696-1782)
 =====================  =====================================================
 
-Inflate (decompress, decompressobj) is out of scope of the accelerated path
- and is served by CPython's own zlib, which is also the decoder
-the reference's tests use as the cross-check.  There is no CPU *compress*
-fallback: without libb2d.so or a CUDA device every compress/checksum call
-raises.
+Inflate of arbitrary streams (decompress, decompressobj) is out of scope of the
+accelerated path and is served by CPython's own zlib, which is
+also the decoder the reference's tests use as the cross-check; files written by
+gzip_ng_threaded (block index) and BGZF files are inflated on the GPU by
+gzip_ng_threaded's reader.  There is no CPU *compress* fallback: without
+libb2d.so or a CUDA device every compress/checksum call raises.
+
+Flush modes: every block this compressor emits ends byte-aligned with a sync
+marker, so Z_PARTIAL_FLUSH and Z_BLOCK produce what Z_SYNC_FLUSH produces (all
+pending input is emitted and the output ends on a byte boundary).  The
+reference distinguishes them (deflate.c:951-968: Z_PARTIAL_FLUSH sends an empty
+fixed block instead of the stored marker, Z_BLOCK stops at a block boundary
+without padding); both are valid DEFLATE continuations and decode identically,
+they differ by at most a few bytes per flush.
 """
 from __future__ import annotations
 
@@ -282,7 +291,7 @@ class _Compress:
     def _run(self, addr: int, n: int, final: bool) -> bytes:
         """n bytes at addr -> raw deflate bytes primed with the stream's last 32 KiB; updates checksums and tail"""
         body, crc, ad = _deflate(addr, n, self._tail, self._level | (self._strategy << 8), self._wb, final,
-                                 crc=self._crc if (self._kind == "gzip" or self._kind_crc) else None,
+                                 crc=self._crc if self._kind == "gzip" else None,
                                  adler=self._adler if self._kind == "zlib" else None)
         if crc is not None:
             self._crc = crc
@@ -310,7 +319,6 @@ class _Compress:
         return body
 
     _flush_empty = False
-    _kind_crc = False      # set by gzip_ng.GzipNGFile: keep a CRC-32 of the input although the stream is raw
 
     def compress(self, data, /):
         with self._lock:
@@ -394,6 +402,11 @@ def compressobj(level=Z_DEFAULT_COMPRESSION, method=DEFLATED, wbits=MAX_WBITS, m
     return _Compress(_level(level), wbits, zdict, strategy)
 
 
+_PC_CONTEXTS = 4
+_pc_counter = 0
+_pc_lock = threading.Lock()
+
+
 class _ParallelCompress:
     """_ParallelCompress(buffersize, level=-1).compress_and_crc(data, zdict) -> (bytes, crc32)
     (zlib_ngmodule.c:1598-1797).  One owner thread, no lock, like the reference."""
@@ -406,7 +419,17 @@ class _ParallelCompress:
         self._level = _level(level)
         self._cap = int(buffersize)
         self._buf = ctypes.create_string_buffer(max(self._cap, 1))
-        self._ctx = _ctx()
+        # The reference's pattern is N objects on N threads (gzip_ng_threaded.py:231-246), each with its own deflate
+        # state.  Calls on one GPU context are serialised, so the objects are dealt over a few contexts of device 0
+        # (their kernels then overlap on the device like the reference's threads do on the cores).
+        global _pc_counter
+        with _pc_lock:
+            slot = _pc_counter % _PC_CONTEXTS
+            _pc_counter += 1
+        try:
+            self._ctx = _native.default_context(0, slot)
+        except _native.NativeError as e:
+            raise error(f"Error {e.code} while opening the B200 device: {e.msg}") from None
 
     def compress_and_crc(self, data, zdict, /):
         daddr, n, k1 = _native._addr(data)
