@@ -3,9 +3,8 @@
 That module is serial glue around ``zlib_ng.compressobj`` and outside the accelerated path, so nearly
 all of it is left to the code it was derived from, CPython's ``gzip``:
 
-* ``open()`` hands binary / text opening to ``gzip_ng_threaded.open(..., threads=1)``: one GPU worker behind the
-  reference's file-object interface, and the GPU reader for files that carry a block index or are BGZF;
-* ``GzipNGFile`` is ``gzip.GzipFile`` with the deflate object swapped for this package's (everything else inherited);
+* ``GzipNGFile`` is ``gzip.GzipFile`` with the deflate object swapped for this package's (everything else, the
+  write path's checks and CRC included, inherited); ``open()`` builds one, wrapped for text modes;
 * ``compress()`` is ``zlib_ng.compress(wbits=31)`` with the header's mtime / OS bytes set (gzip_ng.py:182-195);
 * ``decompress()`` inflates indexed / BGZF data on the GPU and leaves anything else to CPython.
 
@@ -31,8 +30,8 @@ BadGzipFile = gzip.BadGzipFile
 
 
 def open(filename, mode="rb", compresslevel=_COMPRESS_LEVEL_TRADEOFF, encoding=None, errors=None, newline=None):
-    """gzip.open()'s contract; the work is done by gzip_ng_threaded with a single worker."""
-    from . import gzip_ng_threaded
+    """gzip.open()'s contract, returning GzipNGFile objects (what gzip_ng_threaded.open(threads=0) hands out too,
+    reference tests/test_gzip_ng_threaded.py:53-57)."""
     text = "t" in mode
     if text and "b" in mode:
         raise ValueError(f"Invalid mode: {mode!r}")
@@ -40,9 +39,13 @@ def open(filename, mode="rb", compresslevel=_COMPRESS_LEVEL_TRADEOFF, encoding=N
         for name, value in (("encoding", encoding), ("errors", errors), ("newline", newline)):
             if value is not None:
                 raise ValueError(f"Argument '{name}' not supported in binary mode")
-    if not (isinstance(filename, (str, bytes, os.PathLike)) or hasattr(filename, "read") or hasattr(filename, "write")):
+    if isinstance(filename, (str, bytes, os.PathLike)):
+        gz = GzipNGFile(filename, mode.replace("t", ""), compresslevel)
+    elif hasattr(filename, "read") or hasattr(filename, "write"):
+        gz = GzipNGFile(None, mode.replace("t", ""), compresslevel, filename)
+    else:
         raise TypeError("filename must be a str or bytes object, or a file")
-    return gzip_ng_threaded.open(filename, mode, compresslevel, encoding, errors, newline, threads=1)
+    return io.TextIOWrapper(gz, encoding, errors, newline) if text else gz
 
 
 class GzipNGFile(gzip.GzipFile):

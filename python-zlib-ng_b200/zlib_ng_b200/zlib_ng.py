@@ -148,6 +148,14 @@ _api.Py_DecRef.restype = None
 _api.Py_DecRef.argtypes = [ctypes.c_void_p]
 
 
+try:
+    _libc = ctypes.CDLL(None, use_errno=True)
+    _libc.madvise.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+    _libc.madvise.restype = ctypes.c_int
+except Exception:          # pragma: no cover
+    _libc = None
+
+
 class _OutBytes:
     """An uninitialised bytes object the library writes into, trimmed in place afterwards: what
     arrange_output_buffer does in the reference (zlib_ngmodule.c:149-197) — no zero fill of the
@@ -159,6 +167,16 @@ class _OutBytes:
             raise MemoryError
         self.addr = _api.PyBytes_AsString(self._p)
         self.cap = cap
+        if cap >= (8 << 20) and _libc is not None:
+            # a fresh multi-MiB bytes object is untouched memory: ask for huge pages, so that filling it costs a page
+            # fault per 2 MiB instead of per 4 KiB (the faults, not the copy, bound compress() of a GiB)
+            lo = (self.addr + 0x1FFFFF) & ~0x1FFFFF
+            hi = (self.addr + cap) & ~0x1FFFFF
+            if hi > lo:
+                try:
+                    _libc.madvise(ctypes.c_void_p(lo), ctypes.c_size_t(hi - lo), 14)      # MADV_HUGEPAGE
+                except Exception:
+                    pass
 
     def finish(self, size: int) -> bytes:
         pp = ctypes.c_void_p(self._p)
@@ -257,6 +275,33 @@ def compress(data, /, level=Z_DEFAULT_COMPRESSION, wbits=MAX_WBITS):
     return body
 
 
+_PIN_BYTES = 64 << 20             # gather buffer of a long compressobj stream = one GPU call (a multiple of _BLOCK)
+_pin_free, _pin_lock = [], threading.Lock()
+
+
+def _pin_take():
+    while True:
+        with _pin_lock:
+            pin = _pin_free.pop() if _pin_free else None
+        if pin is None:
+            break
+        if len(pin[1]) == _PIN_BYTES:
+            return pin
+        pin[1].release()                   # another size (tests change _PIN_BYTES)
+        _native.pinned_free(pin[0])
+    ptr = _native.pinned_alloc(_PIN_BYTES)
+    return ptr, memoryview((ctypes.c_char * _PIN_BYTES).from_address(ptr)).cast("B")
+
+
+def _pin_give(pin):
+    with _pin_lock:
+        if len(_pin_free) < 4:
+            _pin_free.append(pin)
+            return
+    pin[1].release()
+    _native.pinned_free(pin[0])
+
+
 class _Compress:
     """Streaming compressor (compobject, zlib_ngmodule.c:56-66).  Input is gathered
     until a flush or until _STREAM_THRESHOLD bytes are pending, then whole device
@@ -271,6 +316,8 @@ class _Compress:
         self._zdict = bytes(zdict) if zdict is not None else b""
         self._tail = self._zdict[-(1 << self._wb):][-_WINDOW:]
         self._pending = bytearray()
+        self._pin = None                   # (ptr, view) of a page-locked gather buffer: streams that reach the threshold get one
+        self._pin_fill = 0
         self._started = False
         self._finished = False
         self._crc = 0
@@ -306,6 +353,10 @@ class _Compress:
 
     def _submit(self, nbytes: int, final: bool) -> bytes:
         """the first nbytes of the pending buffer, in place (no copy of the input on the Python side)"""
+        if self._pin is not None:
+            nbytes, self._pin_fill = self._pin_fill, 0          # everything gathered so far (flush / finish)
+            if nbytes:
+                return self._run(self._pin[0], nbytes, final)
         if nbytes == 0:
             if not final and not self._flush_empty:
                 return b""
@@ -327,17 +378,45 @@ class _Compress:
             mv = memoryview(data)
             mv = mv.cast("B") if mv.ndim == 1 and mv.c_contiguous else memoryview(bytes(mv))
             out = b""
-            if not self._pending and mv.nbytes >= _STREAM_THRESHOLD:
+            if not self._pending and self._pin_fill == 0 and mv.nbytes >= _STREAM_THRESHOLD:
                 # a large write on an empty buffer: its whole blocks go straight from the caller's memory
                 k = mv.nbytes // _BLOCK * _BLOCK
                 addr, _, keep = _native._addr(mv)
                 out = self._header() + self._run(addr, k, False)
                 del keep
                 mv = mv[k:]
+            if self._pin is not None:
+                return out + self._gather_pinned(mv)
             self._pending += mv
             if len(self._pending) >= _STREAM_THRESHOLD:
                 out += self._header() + self._submit(len(self._pending) // _BLOCK * _BLOCK, False)
+                # a long stream: from now on the input is gathered in page-locked memory (one copy, like the bytearray's,
+                # but the GPU then reads it by DMA without the library staging it again) in calls of _PIN_BYTES
+                self._pin = _pin_take()
+                rest = len(self._pending)
+                self._pin[1][:rest] = self._pending
+                self._pin_fill = rest
+                self._pending = bytearray()
             return out
+
+    def _gather_pinned(self, mv) -> bytes:
+        out, pos, n = b"", 0, mv.nbytes
+        ptr, view = self._pin
+        cap = len(view)
+        while pos < n:
+            k = min(n - pos, cap - self._pin_fill)
+            if k >= (4 << 20):
+                saddr, _, keep = _native._addr(mv[pos:pos + k])
+                _native.check(_native.lib().b2d_host_copy(ptr + self._pin_fill, saddr, k, 8))
+                del keep
+            else:
+                view[self._pin_fill:self._pin_fill + k] = mv[pos:pos + k]
+            self._pin_fill += k
+            pos += k
+            if self._pin_fill == cap:
+                out += self._header() + self._run(ptr, cap, False)
+                self._pin_fill = 0
+        return out
 
     def flush(self, mode=Z_FINISH, /):
         with self._lock:
@@ -371,9 +450,15 @@ class _Compress:
                 raise ValueError("Inconsistent stream state")
             c = _Compress.__new__(_Compress)
             c.__dict__.update({k: v for k, v in self.__dict__.items() if k != "_lock"})
-            c._pending = bytearray(self._pending)
+            c._pending = bytearray(self._pending) if self._pin is None else bytearray(self._pin[1][:self._pin_fill])
+            c._pin, c._pin_fill = None, 0
             c._lock = threading.Lock()
             return c
+
+    def __del__(self):
+        pin, self._pin = getattr(self, "_pin", None), None
+        if pin is not None:
+            _pin_give(pin)
 
     __copy__ = copy
 

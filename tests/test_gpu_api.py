@@ -158,6 +158,7 @@ def test_pair_compress_equals_compressobj(zng, fastq):
 
 def test_compressobj_streams_large_input_incrementally(zng, monkeypatch):
     monkeypatch.setattr(zng, "_STREAM_THRESHOLD", 4 << 20)
+    monkeypatch.setattr(zng, "_PIN_BYTES", 2 << 20)      # the page-locked gather buffer long streams switch to
     data = synthdata.make("mixed", 12_000_000, 4).tobytes()
     co = zng.compressobj(6)
     pieces = [co.compress(data[i:i + 1_000_000]) for i in range(0, len(data), 1_000_000)]
