@@ -42,13 +42,13 @@ _MIN_BATCH = 128 * 1024
 # What one native call covers, per GPU.  The reference keeps threads * block_size bytes in flight; a GPU wants more
 # per launch, so batches grow to this size (times the number of GPUs) unless the caller asked for less than one
 # 128 KiB device block in total (then the reference's sizes, and its OverflowError on oversized blocks, are kept).
-_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "256")) << 20
+_STREAM_BATCH = int(os.environ.get("B2D_STREAM_BATCH_MIB", "128")) << 20
 # what one GPU context works on at a time (its batch): a call's bytes are dealt to the devices in pieces of this size,
 # four of which are in flight per device
 _CTX_BATCH = int(os.environ.get("B2D_MAX_BATCH_MIB", "64")) << 20
 # native calls in flight (each on its own multi-device context): call j+1's first H2D and call j-1's last D2H
 # overlap call j's kernels.  Inside a call the library already pipelines 3 slots x 2 lanes per device.
-_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "2")), 1)
+_STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "3")), 1)
 _COPY_CHUNK = 4 << 20
 # Block index (for the GPU reader): one data member, then the empty member the reference's close() leaves
 # (gzip_ng_threaded.py:340-355), then empty members whose FEXTRA field ("B2" subfields, RFC 1952 2.3.1.1) lists
@@ -775,9 +775,8 @@ class _ThreadedGzipWriter(io.RawIOBase):
         nw = len(self._contexts)
         # one batch = what the reference would have in flight across its threads, grown to a GPU-sized piece per device
         nominal = max(block_size * threads // nw, 1)
-        # (several devices: half as much per device and call — two calls are in flight, and the pinned batches of a
-        # writer over 8 GPUs would otherwise add up to 16 GiB)
-        per_dev = _STREAM_BATCH if len(devices) == 1 else max(_STREAM_BATCH // 2, 2 * _CTX_BATCH)
+        # (128 MiB per device and call with three calls in flight: profiles/writer_sweep_r2.log)
+        per_dev = _STREAM_BATCH
         self.batch = nominal if block_size * threads < _MIN_BATCH else max(nominal, per_dev * len(devices))
         self._out_cap = self.batch + max(self.batch // 10, 500)
         # the first batches of a file go out early (a quarter, then half of the full size), so that the GPUs start

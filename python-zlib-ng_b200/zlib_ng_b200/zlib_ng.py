@@ -275,7 +275,7 @@ def compress(data, /, level=Z_DEFAULT_COMPRESSION, wbits=MAX_WBITS):
     return body
 
 
-_PIN_BYTES = 64 << 20             # gather buffer of a long compressobj stream = one GPU call (a multiple of _BLOCK)
+_PIN_BYTES = 256 << 20            # gather buffer of a long compressobj stream = one GPU call of four pipelined batches (a multiple of _BLOCK)
 _pin_free, _pin_lock = [], threading.Lock()
 
 
