@@ -423,9 +423,10 @@ def main():
             hv = np.frombuffer((ctypes.c_uint8 * total).from_address(h_in), dtype=np.uint8)
             for r in range(world):
                 hv[r * n:(r + 1) * n] = shard if r == rank else shard_bytes(base, r, n)
-            # 64 MiB batches for the host path: four lanes of them fill a device like two of 256 MiB do, with a quarter of
-            # the pipeline's fill and drain time (profiles/r2_i_multi_e2e.log: 100.7 against 95.9 GB/s on 8 GPUs)
-            m = nat.MultiContext(list(range(world)), min(a.batch_mib, 64) * MIB)
+            # several GPUs: 64 MiB batches — four lanes of them fill a device like two of 256 MiB do, with a quarter of the
+            # pipeline's fill and drain time (profiles/r2_i_multi_e2e.log: 100.7 against 95.9 GB/s on 8 GPUs; one GPU:
+            # 39.1 against 40.4)
+            m = nat.MultiContext(list(range(world)), (a.batch_mib if world == 1 else min(a.batch_mib, 64)) * MIB)
 
             def host_pass():
                 return m.compress_and_crc(a.level, h_in, total, None, 0, h_out, cap_all, want_sizes=True)
@@ -512,18 +513,23 @@ def main():
             nat.check(L.b2d_block_index(ctx.handle, None, 0, ctypes.byref(cnt)))
             offs = (ctypes.c_uint64 * cnt.value)()
             nat.check(L.b2d_block_index(ctx.handle, offs, cnt.value, ctypes.byref(cnt)))
+            nbk = cnt.value - 1
+            bits = (ctypes.c_uint32 * (4 * nbk))()
+            nat.check(L.b2d_subblock_bits(ctx.handle, bits, 4 * nbk, ctypes.byref(cnt)))
             d_back = ctx.device_alloc(n + 64)
-            best = 1e9
-            for _ in range(3):
-                ims = ctypes.c_float(0)
-                nat.check(L.b2d_inflate_device(ctx.handle, ctypes.c_void_p(d_out), o_full, offs, cnt.value - 1, None, 0,
-                                               ctypes.c_void_p(d_back), n, ctypes.byref(ims)))
-                best = min(best, ims.value)
-            v = ctypes.c_uint32(0)
-            nat.check(L.b2d_crc32_device(ctx.handle, 0, ctypes.c_void_p(d_back), n, ctypes.byref(v), None))
+            for tag, sub in (("inflate", None), ("inflate_sub_blocks", bits)):      # one warp per block / per 32 KiB sub-block
+                best = 1e9
+                for _ in range(3):
+                    ims = ctypes.c_float(0)
+                    nat.check(L.b2d_inflate_device_sub(ctx.handle, ctypes.c_void_p(d_out), o_full, offs, sub, nbk, None, 0,
+                                                       ctypes.c_void_p(d_back), n, ctypes.byref(ims)))
+                    best = min(best, ims.value)
+                v = ctypes.c_uint32(0)
+                nat.check(L.b2d_crc32_device(ctx.handle, 0, ctypes.c_void_p(d_back), n, ctypes.byref(v), None))
+                extra[f"{tag}_GBps"] = n / best / 1e6
+                extra[f"{tag}_crc_ok"] = v.value == c_full
             ctx.device_free(d_back)
-            extra["inflate_GBps"] = n / best / 1e6
-            extra["inflate_crc_ok"] = v.value == c_full
+            cnt.value = nbk + 1
             nblk = min(2048, cnt.value - 1)
             comp = np.empty(offs[nblk], dtype=np.uint8)
             ctx.d2h(comp.ctypes.data_as(ctypes.c_void_p), d_out, int(offs[nblk]))

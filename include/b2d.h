@@ -139,6 +139,12 @@ int b2d_compress_and_crc_multi(b2d_mctx *m, int level, const uint8_t *data, uint
                                uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
                                uint64_t *block_sizes, uint64_t cap, uint64_t *count);
 
+/* ... and, with sub_bits (4 entries per block, `cap` counts blocks), the bit offset of every 32 KiB sub-block inside its
+ * block (see b2d_subblock_bits): what the writer stores so that readers can decode one warp per sub-block */
+int b2d_compress_and_crc_multi_sub(b2d_mctx *m, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                   uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                   uint64_t *block_sizes, uint32_t *sub_bits, uint64_t cap, uint64_t *count);
+
 /* ---- the other side of the wire: block-parallel inflate of streams written by this library ----
  * (first version.  The reference decompresses with zng_inflate on one thread:
  * zlib_ng.decompress, zlib_ngmodule.c:275-370; _GzipReader.read, :2426-2637; gzip_ng_threaded.py:90-167.)
@@ -163,6 +169,16 @@ int b2d_compress_and_crc_indexed(b2d_ctx *ctx, int level, const uint8_t *data, u
 int b2d_inflate_device(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
                        uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
                        float *ms);
+/* Four times the parallelism: the writer also knows at which BIT every 32 KiB sub-block (= one DEFLATE block) starts inside
+ * its 128 KiB block.  b2d_subblock_bits returns them for the last deflate call on the context (4 entries per block, 0 for
+ * the first sub-block and for sub-blocks a short last block does not have); the _sub forms of the inflate calls take them
+ * (sub_bits may be NULL: one warp per block as before) and decode one warp per sub-block. */
+int b2d_subblock_bits(b2d_ctx *ctx, uint32_t *bits, uint64_t cap, uint64_t *count);
+int b2d_inflate_device_sub(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
+                           const uint32_t *sub_bits, uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n,
+                           uint8_t *d_out, uint64_t raw_n, float *ms);
+int b2d_inflate_host_sub(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
+                         uint64_t nblocks, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc);
 /* the same with host buffers: chunks of 512 blocks flow through H2D / decode / resolve / D2H side by side.  `crc`
  * (optional) is continued over the output: *crc = crc32(out[0, raw_n), *crc), computed on the device. */
 int b2d_inflate_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,

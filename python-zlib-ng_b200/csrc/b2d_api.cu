@@ -15,6 +15,7 @@
 #include <thread>
 #include <vector>
 #include <chrono>
+#include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -161,6 +162,8 @@ struct b2d_ctx {
     uint64_t launches;
     /* compressed start offset of every device block of the last b2d_deflate_device call (b2d_block_index) */
     uint64_t *d_index; uint64_t index_cap, index_n;
+    uint32_t *d_subidx;                      /* bit offset of every sub-block inside its block, B2D_NSUB entries per block (same capacity) */
+    uint32_t *d_inf_sub; uint64_t inf_sub_cap;     /* inflate: the caller's sub-block bit offsets on the device */
     /* host-buffer calls keep offsets relative to each batch's output: index_base[j] is where batch j's output starts */
     std::vector<uint64_t> index_base; uint64_t index_total;
     uint64_t index_bpb, index_local;        /* blocks per batch of that call; entries this context holds in d_index */
@@ -189,7 +192,7 @@ static void ctx_free(b2d_ctx *c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int i = 1; i < B2D_NLANE; ++i) if (c->stl[i]) cudaStreamDestroy(c->stl[i]);
     cudaFree(c->d_total);
-    cudaFree(c->d_index); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out); cudaFree(c->d_inf_flags);
+    cudaFree(c->d_index); cudaFree(c->d_subidx); cudaFree(c->d_inf_sub); cudaFree(c->d_inf16); cudaFree(c->d_inf_index); cudaFree(c->d_inf_err); cudaFree(c->d_inf_in); cudaFree(c->d_inf_out); cudaFree(c->d_inf_flags);
     if (c->st_inf) cudaStreamDestroy(c->st_inf);
     if (c->st_inf_in) cudaStreamDestroy(c->st_inf_in);
     if (c->st_inf_out) cudaStreamDestroy(c->st_inf_out);
@@ -504,13 +507,25 @@ static int ensure_index(b2d_ctx *c, uint64_t n) {
     const uint64_t need = (n + B2D_BLOCK - 1) / B2D_BLOCK + 2;
     if (need > c->index_cap) {
         cudaFree(c->d_index); c->d_index = nullptr; c->index_cap = 0;
+        cudaFree(c->d_subidx); c->d_subidx = nullptr;
         CU(cudaMalloc(&c->d_index, need * sizeof(uint64_t)));
+        CU(cudaMalloc(&c->d_subidx, need * B2D_NSUB * sizeof(uint32_t)));
         c->index_cap = need;
     }
+    CU(cudaMemsetAsync(c->d_subidx, 0, need * B2D_NSUB * sizeof(uint32_t), c->st));     /* sub-blocks a short last block does not have */
+    CU(cudaStreamSynchronize(c->st));                                                   /* (the lanes write it from other streams) */
     c->index_n = 0;
     c->index_base.clear();
     c->index_total = 0;
     return B2D_OK;
+}
+
+/* keep the bit offset of every sub-block of a batch (b2d_subinfo.bit_off, written by k_scan) next to the block index */
+static cudaError_t save_sub_bits(b2d_ctx *c, uint64_t first_block, const b2d_job &J, uint64_t m, cudaStream_t st) {
+    const uint64_t nsub = (m + B2D_SUB - 1) / B2D_SUB;
+    return cudaMemcpy2DAsync(c->d_subidx + first_block * B2D_NSUB, sizeof(uint32_t),
+                             reinterpret_cast<const uint8_t *>(J.info) + offsetof(b2d_subinfo, bit_off), sizeof(b2d_subinfo),
+                             sizeof(uint32_t), nsub, cudaMemcpyDeviceToDevice, st);
 }
 
 extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, uint64_t dict_n, uint64_t n, uint8_t *d_out,
@@ -558,6 +573,7 @@ extern "C" int b2d_deflate_device(b2d_ctx *c, int level, const uint8_t *d_buf, u
         const uint64_t nb = (m + B2D_BLOCK - 1) / B2D_BLOCK;
         CU(cudaMemcpyAsync(c->d_index + off / B2D_BLOCK, J.block_off, (nb + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice,
                            lane ? c->stl[lane] : c->st));
+        CU(save_sub_bits(c, off / B2D_BLOCK, J, m, lane ? c->stl[lane] : c->st));
     }
     if (two) for (int i = 1; i < NL; ++i) { CU(cudaEventRecord(c->ev_join[i], c->stl[i])); CU(cudaStreamWaitEvent(c->st, c->ev_join[i], 0)); }
     if (crc && n) { CU(b2d_crc32_dev_launch(c->ck, d_buf + dict_n, n, c->st)); c->launches += crc_launches(d_buf + dict_n, n); }
@@ -760,6 +776,7 @@ static int deflate_host_pipelined(b2d_ctx *c, int level, uint32_t max_dist, cons
         CU(cudaMemcpyAsync(&c->h_total[s], d_total[s], sizeof(uint64_t), cudaMemcpyDeviceToHost, cs[ln]));
         CU(cudaMemcpyAsync(c->d_index + i * bpb, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK) * sizeof(uint64_t),
                            cudaMemcpyDeviceToDevice, cs[ln]));
+        CU(save_sub_bits(c, i * bpb, J, m, cs[ln]));
         if (want_crc) { CU(b2d_crc32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += crc_launches(d_in[s] + D, m); }
         if (want_adler) { CU(b2d_adler32_dev_launch(ck[s], d_in[s] + D, m, cs[ln])); c->launches += 2; }
         CU(cudaEventRecord(c->ev_comp[s], cs[ln]));
@@ -903,6 +920,7 @@ extern "C" int b2d_deflate_host(b2d_ctx *c, int level, int window_bits, const ui
         c->launches += pipeline_launches(level);
         CU(cudaMemcpyAsync(c->h_total, c->d_total, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
         CU(cudaMemcpyAsync(c->d_index, J.block_off, ((m + B2D_BLOCK - 1) / B2D_BLOCK + 1) * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c->st));
+        CU(save_sub_bits(c, 0, J, m, c->st));
         c->index_n = (m + B2D_BLOCK - 1) / B2D_BLOCK + 1;
         if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_in + D, m, c->st)); c->launches += crc_launches(c->d_in + D, m); }
         CU(cudaStreamSynchronize(c->st));
@@ -1021,9 +1039,28 @@ static uint64_t multi_batch(const b2d_mctx *m, uint64_t n) {
     return b;
 }
 
+static int deflate_host_multi_impl(b2d_mctx *m, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                   uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                   uint32_t *adler, uint64_t *block_sizes, uint32_t *sub_bits, uint64_t cap, uint64_t *count);
+
 extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
                                       uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
                                       uint32_t *adler, uint64_t *block_sizes, uint64_t cap, uint64_t *count) {
+    return deflate_host_multi_impl(m, level, window_bits, data, n, dict, dict_n, final, out, out_cap, out_n, crc, adler, block_sizes, nullptr, cap, count);
+}
+
+extern "C" int b2d_compress_and_crc_multi_sub(b2d_mctx *m, int level, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                              uint64_t dict_n, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                              uint64_t *block_sizes, uint32_t *sub_bits, uint64_t cap, uint64_t *count) {
+    if (!crc) return fail(B2D_STREAM_ERROR, "null argument");
+    if (sub_bits && !block_sizes) return fail(B2D_STREAM_ERROR, "sub_bits needs block_sizes");
+    *crc = 0;
+    return deflate_host_multi_impl(m, level, 15, data, n, dict, dict_n, 0, out, out_cap, out_n, crc, nullptr, block_sizes, sub_bits, cap, count);
+}
+
+static int deflate_host_multi_impl(b2d_mctx *m, int level, int window_bits, const uint8_t *data, uint64_t n, const uint8_t *dict,
+                                   uint64_t dict_n, int final, uint8_t *out, uint64_t out_cap, uint64_t *out_n, uint32_t *crc,
+                                   uint32_t *adler, uint64_t *block_sizes, uint32_t *sub_bits, uint64_t cap, uint64_t *count) {
     if (!m || !out_n || (!data && n) || (!out && out_cap) || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
     if (!b2d_level_valid(level)) return fail(B2D_STREAM_ERROR, "Bad compression level");
     if (window_bits < 9 || window_bits > 15) return fail(B2D_STREAM_ERROR, "window_bits outside 9..15");
@@ -1044,6 +1081,7 @@ extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, c
         if ((rc = b2d_block_index(c, offs.data(), nblocks + 1, &cnt))) return rc;
         if (cnt != nblocks + 1) return fail(B2D_STREAM_ERROR, "block index does not match the input size");
         for (uint64_t i = 0; i < nblocks; ++i) block_sizes[i] = offs[i + 1] - offs[i];
+        if (sub_bits && (rc = b2d_subblock_bits(c, sub_bits, nblocks * B2D_NSUB, &cnt))) return rc;
         return B2D_OK;
     }
     const uint32_t max_dist = 1u << window_bits;
@@ -1053,6 +1091,7 @@ extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, c
     b2d_ledger G(nb);
     std::thread th[B2D_MAX_DEVICES];
     std::vector<uint64_t> rel[B2D_MAX_DEVICES];               /* per context: its blocks' offsets relative to their batch */
+    std::vector<uint32_t> rsub[B2D_MAX_DEVICES];              /* ... and the bit offsets of their sub-blocks */
     for (int d = 0; d < k; ++d)
         th[d] = std::thread([&, d] {
             b2d_ctx *c = m->ctx[d];
@@ -1073,6 +1112,10 @@ extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, c
             if (!rc && block_sizes && c->index_local) {
                 rel[d].resize(c->index_local);
                 e = cudaMemcpyAsync(rel[d].data(), c->d_index, c->index_local * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st);
+                if (e == cudaSuccess && sub_bits) {
+                    rsub[d].resize(c->index_local * B2D_NSUB);
+                    e = cudaMemcpyAsync(rsub[d].data(), c->d_subidx, c->index_local * B2D_NSUB * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st);
+                }
                 if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
                 if (e != cudaSuccess) rc = fail_cuda(e, "block index copy");
             }
@@ -1090,6 +1133,7 @@ extern "C" int b2d_deflate_host_multi(b2d_mctx *m, int level, int window_bits, c
             const uint64_t start = G.off[j] + rel[d][i * bpb + b % bpb];
             if (b) block_sizes[b - 1] = start - prev;
             prev = start;
+            if (sub_bits) memcpy(sub_bits + b * B2D_NSUB, &rsub[d][(i * bpb + b % bpb) * B2D_NSUB], B2D_NSUB * sizeof(uint32_t));
         }
         block_sizes[nblocks - 1] = produced - prev;
     }
@@ -1180,9 +1224,45 @@ static int inflate_mode(b2d_ctx *c) {
     return conc ? B2D_INF_CONCURRENT : B2D_INF_SERIAL;
 }
 
+/* the caller's sub-block bit offsets (B2D_NSUB per block, host array) on the device, or null */
+static int upload_sub_bits(b2d_ctx *c, const uint32_t *sub_bits, uint64_t nblocks, const uint32_t **d_out) {
+    *d_out = nullptr;
+    if (!sub_bits) return B2D_OK;
+    for (uint64_t i = 0; i < nblocks * B2D_NSUB; ++i)
+        if (sub_bits[i] >= 8u * (B2D_BLOCK + 1024u) || ((i % B2D_NSUB) && sub_bits[i] && sub_bits[i] <= sub_bits[i - 1]))
+            return fail(B2D_STREAM_ERROR, "bad sub-block index");
+    if (nblocks * B2D_NSUB > c->inf_sub_cap) {
+        cudaFree(c->d_inf_sub); c->d_inf_sub = nullptr; c->inf_sub_cap = 0;
+        CU(cudaMalloc(&c->d_inf_sub, nblocks * B2D_NSUB * sizeof(uint32_t)));
+        c->inf_sub_cap = nblocks * B2D_NSUB;
+    }
+    CU(cudaMemcpyAsync(c->d_inf_sub, sub_bits, nblocks * B2D_NSUB * sizeof(uint32_t), cudaMemcpyHostToDevice, c->st));
+    *d_out = c->d_inf_sub;
+    return B2D_OK;
+}
+
+extern "C" int b2d_subblock_bits(b2d_ctx *c, uint32_t *bits, uint64_t cap, uint64_t *count) {
+    if (!c || !count) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::recursive_mutex> g(c->mu);
+    const uint64_t nblocks = c->index_n ? c->index_n - 1 : 0;
+    *count = nblocks * B2D_NSUB;
+    if (!bits || !nblocks) return B2D_OK;
+    if (cap < *count) return fail(B2D_BUF_ERROR, "b2d_subblock_bits: capacity below the number of entries");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(bits, c->d_subidx, *count * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return B2D_OK;
+}
+
 extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
                                   uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n, uint8_t *d_out, uint64_t raw_n,
                                   float *ms) {
+    return b2d_inflate_device_sub(c, d_in, in_n, block_offsets, nullptr, nblocks, d_dict, dict_n, d_out, raw_n, ms);
+}
+
+extern "C" int b2d_inflate_device_sub(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n, const uint64_t *block_offsets,
+                                      const uint32_t *sub_bits, uint64_t nblocks, const uint8_t *d_dict, uint64_t dict_n,
+                                      uint8_t *d_out, uint64_t raw_n, float *ms) {
     if (!c || (!d_in && in_n) || (!d_out && raw_n) || (!block_offsets && nblocks) || (!d_dict && dict_n))
         return fail(B2D_STREAM_ERROR, "null argument");
     if (nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
@@ -1198,6 +1278,8 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
     CU(cudaSetDevice(c->device));
     { int rc = inflate_prepare(c, nblocks, raw_n, true); if (rc) return rc; }
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
+    const uint32_t *d_sub = nullptr;
+    { int rc = upload_sub_bits(c, sub_bits, nblocks, &d_sub); if (rc) return rc; }
     CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
     if (ms) CU(cudaEventRecord(c->ev0, c->st));
     CU(cudaMemsetAsync(c->d_inf_flags, 0, nblocks * sizeof(uint32_t), c->st));
@@ -1206,7 +1288,7 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* flags and error words are cleared */
         CU(cudaStreamWaitEvent(c->st_inf, c->ev_inf_fork, 0));
     }
-    CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+    CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, d_sub, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
                           c->d_inf_flags, c->d_inf_err, c->st, mode == B2D_INF_CONCURRENT ? c->st_inf : c->st, mode));
     if (mode == B2D_INF_CONCURRENT) {
         CU(cudaEventRecord(c->ev_inf_join, c->st_inf));
@@ -1221,7 +1303,7 @@ extern "C" int b2d_inflate_device(b2d_ctx *c, const uint8_t *d_in, uint64_t in_n
         /* the pass over the tails gave up waiting for the decode (it could not run beside it and the wait ran out).
          * That says nothing about the data: every block is decoded by now, so resolve again on one stream. */
         CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
-        CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
+        CU(b2d_launch_inflate(d_in, in_n, c->d_inf_index, d_sub, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16, d_out, raw_n,
                               c->d_inf_flags, c->d_inf_err, c->st, c->st, B2D_INF_RESOLVE_ONLY));
         c->launches += 2;
         if (ms) CU(cudaEventRecord(c->ev1, c->st));
@@ -1256,6 +1338,11 @@ static int inflate_host_buffers(b2d_ctx *c, uint64_t in_n, uint64_t out_n) {
 
 extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,
                                 const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
+    return b2d_inflate_host_sub(c, in, in_n, block_offsets, nullptr, nblocks, dict, dict_n, out, raw_n, crc);
+}
+
+extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
+                                    uint64_t nblocks, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
     if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n) || (!block_offsets && nblocks)) return fail(B2D_STREAM_ERROR, "null argument");
     if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
     if (nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
@@ -1289,6 +1376,8 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
      * side by side to fill the device) and resolved (st_inf, which follows the decodes block by block) and the bytes of
      * chunk k - 1 come back (st_inf_out).  The chain over the block tails runs through all chunks on st_inf. */
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
+    const uint32_t *d_sub = nullptr;
+    { int rc = upload_sub_bits(c, sub_bits, nblocks, &d_sub); if (rc) return rc; }
     CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
     CU(cudaMemsetAsync(c->d_inf_flags, 0, nblocks * sizeof(uint32_t), c->st));
     if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, c->st));
@@ -1305,7 +1394,7 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
         CU(cudaMemcpyAsync(d_stream + lo, in + lo, hi - lo, cudaMemcpyHostToDevice, c->st_inf_in));
         CU(cudaEventRecord(c->ev_inf_h2d[k], c->st_inf_in));
         CU(cudaStreamWaitEvent(st_dec, c->ev_inf_h2d[k], 0));
-        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, d_dict, (uint32_t)dict_n,
+        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, d_dict, (uint32_t)dict_n,
                               c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_dec, st_res, mode));
         c->launches += B2D_INF_LAUNCHES;
         CU(cudaEventRecord(c->ev_inf_done[k], st_res));
@@ -1325,7 +1414,7 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
         /* the pass over the tails gave up waiting for a decode (never a statement about the data): every block is decoded
          * by now, so resolve everything again on one stream and fetch the bytes once more */
         CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
-        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16,
+        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16,
                               c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, c->st, c->st, B2D_INF_RESOLVE_ONLY));
         c->launches += 2;
         if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, c->st)); c->launches += crc_launches(c->d_inf_out, raw_n); }

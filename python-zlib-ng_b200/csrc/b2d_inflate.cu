@@ -124,28 +124,49 @@ __device__ __forceinline__ void inf_fill(uint16_t *tab, int tbits, const uint16_
     }
 }
 
-/* INDEP = false: the stream of this library — block b covers output bytes [b * 128 KiB, ...), may look 32 KiB behind
- * its own start (markers), writes 16-bit symbols.  INDEP = true: independent members (BGZF: every member is its own
- * DEFLATE stream without a dictionary) — block b covers [out_index[b], out_index[b + 1]), nothing may reach behind
- * it, bytes are written as bytes and no resolving pass is needed.  A launch covers blocks [b0, b0 + nb). */
-template <bool INDEP>
+/* What one warp decodes (MODE):
+ *   INF_BLOCKS   a 128 KiB device block of this library's stream: output bytes [b * 128 KiB, ...), may look 32 KiB behind
+ *                its own start (markers), writes 16-bit symbols;
+ *   INF_MEMBERS  an independent member (BGZF: its own DEFLATE stream, no dictionary): output [out_index[b],
+ *                out_index[b + 1]), nothing may reach behind it, bytes are written as bytes, no resolving pass;
+ *   INF_SUBS     one 32 KiB sub-block (= one DEFLATE block) of a device block, found through its bit offset inside the
+ *                block (sub_bits[4 b + s]): four times the parallelism and a quarter of the latency of INF_BLOCKS.
+ *                Markers then mean "byte k of the 32 KiB before this SUB-block"; the warp that finishes a block's last
+ *                sub-block rewrites those of sub-blocks 1.. against their predecessors, after which the block looks
+ *                exactly as INF_BLOCKS leaves it.
+ * A launch covers blocks [b0, b0 + nb). */
+#define INF_BLOCKS 0
+#define INF_MEMBERS 1
+#define INF_SUBS 2
+#define INF_READY 0x80000000u        /* flags[b]: the block's symbols are final (low bits: sub-blocks decoded so far) */
+template <int MODE>
 __global__ void __launch_bounds__(INF_WARPS * 32)
 k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__restrict__ index,
-             const uint64_t *__restrict__ out_index, uint32_t b0, uint32_t nb, uint64_t raw_n, uint32_t dict_n, void *outp,
-             uint32_t *flags, uint32_t *err) {
+             const uint64_t *__restrict__ out_index, const uint32_t *__restrict__ sub_bits, uint32_t b0, uint32_t nb, uint64_t raw_n,
+             uint32_t dict_n, void *outp, uint32_t *flags, uint32_t *err) {
+    constexpr bool INDEP = MODE == INF_MEMBERS, SUBS = MODE == INF_SUBS;
     typedef typename std::conditional<INDEP, uint8_t, uint16_t>::type sym_t;
     __shared__ inf_warp s_w[INF_WARPS];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t b = b0 + blockIdx.x * INF_WARPS + warp;
+    const uint32_t unit = blockIdx.x * INF_WARPS + warp;
+    const uint32_t b = b0 + (SUBS ? unit / B2D_NSUB : unit), sub = SUBS ? unit % B2D_NSUB : 0u;
     if (b >= b0 + nb) return;
     inf_warp *T = &s_w[warp];
-    const uint64_t bs = INDEP ? out_index[b] : (uint64_t)b * B2D_BLOCK;
-    const uint32_t expect = INDEP ? (uint32_t)(out_index[b + 1] - bs) : (uint32_t)(raw_n - bs < B2D_BLOCK ? raw_n - bs : B2D_BLOCK);
-    /* how far behind its own start this block may reach: 32 KiB, or the caller's dictionary for block 0 */
-    const uint32_t reach = INDEP ? 0u : (b == 0 ? dict_n : B2D_WINDOW);
+    const uint64_t blk_start = INDEP ? out_index[b] : (uint64_t)b * B2D_BLOCK;
+    const uint32_t blk_len = INDEP ? (uint32_t)(out_index[b + 1] - blk_start) : (uint32_t)(raw_n - blk_start < B2D_BLOCK ? raw_n - blk_start : B2D_BLOCK);
+    const uint32_t nsub_b = (blk_len + B2D_SUB - 1) / B2D_SUB;            /* sub-blocks this block has (SUBS) */
+    if (SUBS && sub >= nsub_b) return;
+    const uint64_t bs = blk_start + (uint64_t)sub * B2D_SUB;
+    const uint32_t expect = SUBS ? (blk_len - sub * B2D_SUB < B2D_SUB ? blk_len - sub * B2D_SUB : B2D_SUB) : blk_len;
+    /* how far behind its own start this unit may reach: 32 KiB, or the caller's dictionary at the start of the stream */
+    const uint32_t reach = INDEP ? 0u : ((b == 0 && sub == 0) ? dict_n : B2D_WINDOW);
     sym_t *o16 = reinterpret_cast<sym_t *>(outp) + bs;
     bitrd R;
-    br_init(R, in, index[b], in_n);
+    {
+        const uint32_t bit0 = SUBS ? sub_bits[(uint64_t)b * B2D_NSUB + sub] : 0u;
+        br_init(R, in, index[b] + (bit0 >> 3), in_n);
+        if (SUBS && (bit0 & 7u)) { br_refill(R); br_take(R, bit0 & 7u); }
+    }
     uint32_t produced = 0, fail = 0;
 
     while (produced < expect && !fail) {
@@ -288,9 +309,31 @@ k_inf_decode(const uint8_t *__restrict__ in, uint64_t in_n, const uint64_t *__re
         for (uint32_t i = produced + lane; i < expect; i += 32) o16[i] = 0;
         if (lane == 0) atomicCAS(err, 0u, (fail << 28) | (b & 0x0fffffffu));
     }
-    /* the block's symbols are in memory: k_inf_tails (running beside this kernel) may pick its tail up */
     __syncwarp();
-    if (!INDEP && lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = 1u; }
+    if (INDEP) return;
+    if (SUBS) {
+        /* the warp that completes the block rewrites the markers of its sub-blocks 1.. in order: "byte k of the 32 KiB
+         * before sub-block s" is symbol k of sub-block s - 1, which by then holds bytes or block-level markers only */
+        uint32_t done = 0;
+        if (lane == 0) { __threadfence(); done = atomicAdd(flags + b, 1u) + 1u; }
+        done = __shfl_sync(FULL, done, 0);
+        if (done != nsub_b) return;
+        __threadfence();
+        uint16_t *blk = reinterpret_cast<uint16_t *>(outp) + blk_start;
+        for (uint32_t s2 = 1; s2 < nsub_b; ++s2) {
+            const uint32_t len2 = blk_len - s2 * B2D_SUB < B2D_SUB ? blk_len - s2 * B2D_SUB : B2D_SUB;
+            uint16_t *cur = blk + s2 * B2D_SUB;
+            const uint16_t *prev = cur - B2D_SUB;
+            for (uint32_t i = lane; i < len2; i += 32) {
+                const uint32_t v = __ldcg(cur + i);
+                if (v >= 256u) cur[i] = __ldcg(prev + (v - 256u));
+            }
+            __syncwarp();
+            __threadfence();
+        }
+    }
+    /* the block's symbols are in memory: k_inf_tails (running beside this kernel) may pick its tail up */
+    if (lane == 0) { __threadfence(); *reinterpret_cast<volatile uint32_t *>(flags + b) = INF_READY; }
 }
 
 /* the byte a marker stands for: `k` indexes the 32 KiB that precede the block starting at output byte bs */
@@ -341,7 +384,7 @@ k_inf_tails(const uint16_t *out16, uint8_t *out8, const uint8_t *__restrict__ di
         if (threadIdx.x < last - first && *reinterpret_cast<volatile uint32_t *>(err + 1) == 0u) {
             const volatile uint32_t *f = flags + first + threadIdx.x;
             uint32_t spins = 0;
-            while (*f == 0u) {
+            while ((*f & INF_READY) == 0u) {
                 __nanosleep(1000);
                 if (++spins > 4000000u) { ok = false; break; }
             }
@@ -409,15 +452,19 @@ static cudaError_t launch_tails(const uint16_t *d_out16, uint8_t *d_out, const u
 
 /* One chunk: blocks [b0, b0 + nb) of a stream of nblocks; chunks are issued in order (the tails of chunk c build on
  * those of chunk c - 1).  The caller has cleared d_flags / d_err for the whole stream and made both streams wait for that. */
-cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t b0, uint32_t nb, uint32_t nblocks,
-                               const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
+cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, const uint32_t *d_sub_bits, uint32_t b0, uint32_t nb,
+                               uint32_t nblocks, const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
                                uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st_dec, cudaStream_t st_res, int mode) {
     if (nb == 0) return cudaSuccess;
     cudaError_t e;
     if (mode != B2D_INF_RESOLVE_ONLY) {
         /* The decode goes first (in host order) and waits for nobody. */
-        k_inf_decode<false><<<(nb + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st_dec>>>(d_in, in_n, d_index, nullptr, b0, nb,
-                                                                                                         raw_n, dict_n, d_out16, d_flags, d_err);
+        if (d_sub_bits)
+            k_inf_decode<INF_SUBS><<<(nb * B2D_NSUB + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st_dec>>>(
+                d_in, in_n, d_index, nullptr, d_sub_bits, b0, nb, raw_n, dict_n, d_out16, d_flags, d_err);
+        else
+            k_inf_decode<INF_BLOCKS><<<(nb + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st_dec>>>(
+                d_in, in_n, d_index, nullptr, nullptr, b0, nb, raw_n, dict_n, d_out16, d_flags, d_err);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     /* The serial pass over the tails is launched right behind it — on its own (high-priority) stream when the device
@@ -432,7 +479,7 @@ cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_
 cudaError_t b2d_launch_inflate_members(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, const uint64_t *d_out_index,
                                        uint32_t nblocks, uint8_t *d_out, uint64_t raw_n, uint32_t *d_err, cudaStream_t st) {
     if (nblocks == 0) return cudaSuccess;
-    k_inf_decode<true><<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, d_out_index, 0, nblocks, raw_n,
-                                                                                       0, d_out, nullptr, d_err);
+    k_inf_decode<INF_MEMBERS><<<(nblocks + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, 0, st>>>(d_in, in_n, d_index, d_out_index, nullptr, 0, nblocks,
+                                                                                              raw_n, 0, d_out, nullptr, d_err);
     return cudaGetLastError();
 }

@@ -17,8 +17,10 @@
 /* One chunk: blocks [b0, b0 + nb) of a stream of nblocks, chunks in order.  The decode is issued on st_dec, the pass over
  * the tails and the rest of the resolving on st_res.  The caller makes both streams wait until d_flags and d_err are
  * cleared; st_res == st_dec for B2D_INF_SERIAL and B2D_INF_RESOLVE_ONLY. */
-cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, uint32_t b0, uint32_t nb, uint32_t nblocks,
-                               const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
+/* d_sub_bits (optional): bit offset of every 32 KiB sub-block inside its block, 4 entries per block — one warp per
+ * sub-block instead of one per block */
+cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_t *d_index, const uint32_t *d_sub_bits, uint32_t b0, uint32_t nb,
+                               uint32_t nblocks, const uint8_t *d_dict, uint32_t dict_n, uint16_t *d_out16, uint8_t *d_out,
                                uint64_t raw_n, uint32_t *d_flags, uint32_t *d_err, cudaStream_t st_dec, cudaStream_t st_res, int mode);
 /* independent members (BGZF): d_index[b] = where member b's DEFLATE data starts, d_out_index[b] .. d_out_index[b + 1] = its
  * place in the output; bytes are written directly, *d_err as above */

@@ -76,6 +76,12 @@ SIGNATURES = {
     "b2d_bgzf_scan": (ctypes.c_int, [_u8p, _u64, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u32), _P(_u64), _P(_u64)]),
     "b2d_inflate_members_host": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _P(_u32), _P(_u32), _u64, _u8p, _u64,
                                                 _P(_u64)]),
+    "b2d_subblock_bits": (ctypes.c_int, [ctypes.c_void_p, _P(_u32), _u64, _P(_u64)]),
+    "b2d_inflate_device_sub": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _u64, _u8p, _u64, _u8p, _u64,
+                                              _P(ctypes.c_float)]),
+    "b2d_inflate_host_sub": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _u64, _u8p, _u64, _u8p, _u64, _P(_u32)]),
+    "b2d_compress_and_crc_multi_sub": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
+                                                      _P(_u64), _P(_u32), _P(_u64), _P(_u32), _u64, _P(_u64)]),
     "b2d_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "b2d_profile_read": (ctypes.c_int, [ctypes.c_void_p, _P(ctypes.c_double), _P(_u64), ctypes.c_int]),
 }
@@ -214,14 +220,17 @@ class MultiContext:
     def launch_count(self) -> int:
         return int(lib().b2d_mctx_launch_count(self.handle))
 
-    def compress_and_crc(self, level, daddr, n, zaddr, zn, out_addr, out_cap, want_sizes=False):
-        """-> (out_n, crc, [compressed size of every 128 KiB block] or None); raises NativeError"""
+    def compress_and_crc(self, level, daddr, n, zaddr, zn, out_addr, out_cap, want_sizes=False, want_subs=False):
+        """-> (out_n, crc, [compressed size of every 128 KiB block] or None[, bit offsets of the sub-blocks]); raises NativeError"""
         out_n, crc, cnt = _u64(0), _u32(0), _u64(0)
         nb = (n + 131071) // 131072
         sizes = (_u64 * max(nb, 1))() if want_sizes else None
-        check(lib().b2d_compress_and_crc_multi(self.handle, level, daddr, n, zaddr if zn else None, zn, out_addr, out_cap,
-                                               ctypes.byref(out_n), ctypes.byref(crc), sizes, nb if want_sizes else 0,
-                                               ctypes.byref(cnt)))
+        subs = (_u32 * max(4 * nb, 1))() if (want_sizes and want_subs) else None
+        check(lib().b2d_compress_and_crc_multi_sub(self.handle, level, daddr, n, zaddr if zn else None, zn, out_addr, out_cap,
+                                                   ctypes.byref(out_n), ctypes.byref(crc), sizes, subs, nb if want_sizes else 0,
+                                                   ctypes.byref(cnt)))
+        if want_subs:
+            return out_n.value, crc.value, (list(sizes[:nb]) if want_sizes else None), (list(subs[:4 * nb]) if subs is not None else None)
         return out_n.value, crc.value, (list(sizes[:nb]) if want_sizes else None)
 
 

@@ -52,9 +52,11 @@ _STREAM_DEPTH = max(int(os.environ.get("B2D_STREAM_DEPTH", "3")), 1)
 _COPY_CHUNK = 4 << 20
 # Block index (for the GPU reader): one data member, then the empty member the reference's close() leaves
 # (gzip_ng_threaded.py:340-355), then empty members whose FEXTRA field ("B2" subfields, RFC 1952 2.3.1.1) lists
-# the compressed size of every 128 KiB device block, then a fixed-size locator member.  Other gzip readers skip
+# the compressed size of every 128 KiB device block (and the bit offsets of its 32 KiB sub-blocks, so that a reader can
+# decode four warps per block), then a fixed-size locator member.  Other gzip readers skip
 # extra fields and empty members, so the file stays an ordinary multi-member gzip file.
 _WRITE_INDEX = os.environ.get("B2D_WRITE_INDEX", "1") != "0"
+_WRITE_SUBS = os.environ.get("B2D_WRITE_SUBS", "1") != "0"        # the index also holds the bit offset of every 32 KiB sub-block
 _GPU_READ = os.environ.get("B2D_GPU_READ", "1") != "0"
 _DEVICE_BLOCK = 128 * 1024
 _INDEX_CHUNK = 16000                      # block sizes per index member (XLEN is 16 bits)
@@ -269,17 +271,23 @@ class _ThreadedGzipReader(io.RawIOBase):
                 return None
             raw.seek(index_off)
             buf = raw.read(end - _LOCATOR_MEMBER - index_off)
-            sizes, off = [], 0
+            sizes, subs, off = [], [], 0
             while len(sizes) < nblocks:
                 got = _parse_extra_member(buf, off)
                 if not got:
                     return None
                 payload, off = got
                 kind, _, _, cnt = struct.unpack_from("<BBHI", payload, 0)
-                if kind != 1 or len(payload) != 8 + 4 * cnt:
+                if kind == 1 and len(payload) == 8 + 4 * cnt:          # compressed size of every block
+                    sizes.extend(struct.unpack_from(f"<{cnt}I", payload, 8))
+                elif kind == 2 and len(payload) == 8 + 16 * cnt:       # ... and the bit offsets of its sub-blocks 1..3
+                    rows = struct.unpack_from(f"<{4 * cnt}I", payload, 8)
+                    sizes.extend(rows[0::4])
+                    for i in range(cnt):
+                        subs.extend((0, rows[4 * i + 1], rows[4 * i + 2], rows[4 * i + 3]))
+                else:
                     return None
-                sizes.extend(struct.unpack_from(f"<{cnt}I", payload, 8))
-            if len(sizes) != nblocks or off != len(buf):
+            if len(sizes) != nblocks or off != len(buf) or (subs and len(subs) != 4 * nblocks):
                 return None
             raw.seek(here)
             head = raw.read(10)
@@ -297,7 +305,7 @@ class _ThreadedGzipReader(io.RawIOBase):
             if (len(empty) != 20 or empty[:8] != head[:8] or empty[8] != 0xFF or empty[10:] != b"\x03\x00" + b"\x00" * 8):
                 return None
             _native.default_context()      # no usable GPU: the CPU reader takes over (raises here)
-            return {"sizes": sizes, "raw_n": raw_n, "cpos": here + 10}
+            return {"sizes": sizes, "subs": subs or None, "raw_n": raw_n, "cpos": here + 10}
         finally:
             if self._gpu is None:
                 raw.seek(here)
@@ -411,8 +419,11 @@ class _ThreadedGzipReader(io.RawIOBase):
                         if g["stop"]:
                             return
                 out_ptr, out_view = out
-                rc = L.b2d_inflate_host(ctx.handle, comp[0], comp_n, offs, nb, tail if tail else None, len(tail),
-                                        out_ptr, raw_n, ctypes.byref(crc))
+                subs = None
+                if g.get("subs"):                     # one warp per 32 KiB sub-block instead of one per block
+                    subs = (ctypes.c_uint32 * (4 * nb))(*g["subs"][4 * first:4 * (first + nb)])
+                rc = L.b2d_inflate_host_sub(ctx.handle, comp[0], comp_n, offs, subs, nb, tail if tail else None, len(tail),
+                                            out_ptr, raw_n, ctypes.byref(crc))
                 g["comp_free"].put(comp)
                 if rc:
                     g["free"].put(out)
@@ -838,12 +849,22 @@ class _ThreadedGzipWriter(io.RawIOBase):
         if not self._indexing or len(self._members) != 1:
             return
         start, raw_n, sizes = self._members[0]
-        if len(sizes) != (raw_n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK or max(sizes) >= 1 << 32:
+        if len(sizes) != (raw_n + _DEVICE_BLOCK - 1) // _DEVICE_BLOCK:
+            return
+        with_subs = all(isinstance(x, tuple) for x in sizes)
+        if not with_subs:
+            sizes = [x[0] if isinstance(x, tuple) else x for x in sizes]
+        if max(x[0] if with_subs else x for x in sizes) >= 1 << 32:
             return
         index_off = self.raw.tell()
-        for i in range(0, len(sizes), _INDEX_CHUNK):
-            part = sizes[i:i + _INDEX_CHUNK]
-            self.raw.write(_extra_member(struct.pack("<BBHI", 1, 0, 0, len(part)) + struct.pack(f"<{len(part)}I", *part)))
+        chunk = _INDEX_CHUNK // 4 if with_subs else _INDEX_CHUNK
+        for i in range(0, len(sizes), chunk):
+            part = sizes[i:i + chunk]
+            if with_subs:       # kind 2: (compressed size, bit offsets of sub-blocks 1..3) per block
+                flat = [v for row in part for v in row]
+                self.raw.write(_extra_member(struct.pack("<BBHI", 2, 0, 0, len(part)) + struct.pack(f"<{len(flat)}I", *flat)))
+            else:               # kind 1: compressed sizes only
+                self.raw.write(_extra_member(struct.pack("<BBHI", 1, 0, 0, len(part)) + struct.pack(f"<{len(part)}I", *part)))
         self.raw.write(_extra_member(_LOCATOR.pack(_LOCATOR_MAGIC, 1, start, raw_n, index_off, len(sizes))))
         self.raw.flush()
 
@@ -1057,8 +1078,9 @@ class _ThreadedGzipWriter(io.RawIOBase):
         try:
             # one stream over the context's devices; the block sizes come back with the call (contexts are shared
             # by every writer of the process, so they cannot be asked for afterwards)
-            out_n, crc, sizes = self._contexts[index].compress_and_crc(self._zlevel, daddr, n, zaddr, zn, out_buf.ptr,
-                                                                       self._out_cap, want_sizes=self._indexing)
+            out_n, crc, sizes, subs = self._contexts[index].compress_and_crc(self._zlevel, daddr, n, zaddr, zn, out_buf.ptr,
+                                                                             self._out_cap, want_sizes=self._indexing,
+                                                                             want_subs=True)
         except _native.NativeError as e:
             if e.code == _native.B2D_BUF_ERROR:
                 raise OverflowError(f"Compressed output exceeds buffer size of {self._out_cap}") from None
@@ -1069,6 +1091,8 @@ class _ThreadedGzipWriter(io.RawIOBase):
             del k1, k2
         if sizes is not None and sum(sizes) != out_n:
             sizes = None
+        if sizes is not None and subs is not None and _WRITE_SUBS:
+            sizes = [(sizes[i], subs[4 * i + 1], subs[4 * i + 2], subs[4 * i + 3]) for i in range(len(sizes))]
         return out_buf.view[:out_n], crc, n, sizes
 
     def _release(self, job):

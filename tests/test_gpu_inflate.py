@@ -479,3 +479,101 @@ def test_host_inflate_over_many_chunks(nat):
             assert crc.value == zlib.crc32(data, zlib.crc32(b"before"))
     finally:
         c.close()
+
+
+# ---- one warp per 32 KiB sub-block: the writer's bit offsets of the sub-blocks (b2d_subblock_bits, index kind 2)
+def sub_bits_of_last_call(nat, ctx, nb):
+    L = nat.lib()
+    cnt = ctypes.c_uint64(0)
+    nat.check(L.b2d_subblock_bits(ctx.handle, None, 0, ctypes.byref(cnt)))
+    assert cnt.value == 4 * nb
+    bits = (ctypes.c_uint32 * max(cnt.value, 1))()
+    nat.check(L.b2d_subblock_bits(ctx.handle, bits, cnt.value, ctypes.byref(cnt)))
+    return bits
+
+
+@pytest.mark.parametrize("kind,n,seed", [("fastq", 1_000_000, 5), ("mixed", 3_000_000, 6), ("mixed", 131073, 8), ("fastq", 32769, 10),
+                                         ("mixed", 1023, 11), ("mixed", 20_000_000, 13), ("fastq", 98_304, 14), ("fastq", 98_305, 15)])
+@pytest.mark.parametrize("level", [0, 1, 6, 6 | (4 << 8)])
+def test_round_trip_one_warp_per_sub_block(nat, ctx, kind, n, seed, level):
+    if n > 4_000_000 and level != 6:
+        pytest.skip("large case at one level only")
+    L = nat.lib()
+    data = synthdata.make(kind, n, seed).tobytes()
+    zdict = synthdata.make("fastq", 20_000, seed + 100).tobytes() if seed % 2 else b""
+    stream, offs, d_buf, d_out, _ = deflate_indexed(nat, ctx, data, level, zdict)
+    nb = len(offs) - 1
+    bits = sub_bits_of_last_call(nat, ctx, nb)
+    try:
+        for b in range(nb):                                   # first sub-block at bit 0, the others strictly after
+            row = list(bits[4 * b:4 * b + 4])
+            have = -(-min(BLOCK, n - b * BLOCK) // 32768)
+            assert row[0] == 0 and all(row[i] > row[i - 1] for i in range(1, have)) and all(v == 0 for v in row[have:])
+        arr = (ctypes.c_uint64 * nb)(*offs[:nb])
+        d_raw = ctx.device_alloc(n + 64)
+        try:
+            nat.check(L.b2d_inflate_device_sub(ctx.handle, ctypes.c_void_p(d_out), len(stream), arr, bits, nb,
+                                               ctypes.c_void_p(d_buf) if zdict else None, len(zdict), ctypes.c_void_p(d_raw), n, None))
+            back = ctypes.create_string_buffer(n)
+            ctx.d2h(back, d_raw, n)
+        finally:
+            ctx.device_free(d_raw)
+        assert back.raw == data
+        # host form, CRC continued on the device
+        out = ctypes.create_string_buffer(n)
+        crc = ctypes.c_uint32(0)
+        nat.check(L.b2d_inflate_host_sub(ctx.handle, stream, len(stream), arr, bits, nb, zdict if zdict else None, len(zdict), out, n,
+                                         ctypes.byref(crc)))
+        assert out.raw == data and crc.value == zlib.crc32(data)
+        if nb >= 1 and n > 40_000 and (level & 0xff) != 0:      # (stored blocks begin with padding: three bits more still decode)
+            # a sub-block offset that points into the middle of a code: detected, or at worst different bytes
+            bad = (ctypes.c_uint32 * (4 * nb))(*bits)
+            bad[1] += 3
+            rc = L.b2d_inflate_host_sub(ctx.handle, stream, len(stream), arr, bad, nb, zdict if zdict else None, len(zdict), out, n, None)
+            assert rc == -3 or out.raw != data
+            bad[1] = 9 * (BLOCK + 1024)                       # out of range: refused before anything runs
+            assert L.b2d_inflate_host_sub(ctx.handle, stream, len(stream), arr, bad, nb, None, 0, out, n, None) == nat.B2D_STREAM_ERROR
+    finally:
+        ctx.device_free(d_buf)
+        ctx.device_free(d_out)
+
+
+def test_marker_chains_through_sub_blocks(nat, ctx):
+    """runs and a period just under the window: nearly every symbol of every sub-block refers to the sub-block before
+    it, through all four sub-blocks of a block and on into the next block"""
+    L = nat.lib()
+    rng = np.random.default_rng(4)
+    period = rng.integers(32, 127, 30_000, dtype=np.uint8).tobytes()
+    zdict = period[-20_000:]
+    data = period * 20 + b"\x00" * 700_000 + period[:5000] * 40 + b"ab" * 300_000
+    for level in (1, 6):
+        stream, offs, d_buf, d_out, _ = deflate_indexed(nat, ctx, data, level, zdict)
+        ctx.device_free(d_buf)
+        ctx.device_free(d_out)
+        nb = len(offs) - 1
+        bits = sub_bits_of_last_call(nat, ctx, nb)
+        arr = (ctypes.c_uint64 * nb)(*offs[:nb])
+        out = ctypes.create_string_buffer(len(data))
+        nat.check(L.b2d_inflate_host_sub(ctx.handle, stream, len(stream), arr, bits, nb, zdict, len(zdict), out, len(data), None))
+        assert out.raw == data
+
+
+def test_written_files_carry_sub_block_offsets(gzt, tmp_path, monkeypatch):
+    import gzip
+    data = synthdata.make("mixed", 9_000_000, 91).tobytes()
+    p = tmp_path / "v2.gz"
+    with gzt.open(p, "wb", threads=4) as f:
+        f.write(data)
+    assert gzip.decompress(p.read_bytes()) == data
+    monkeypatch.setattr(gzt, "_READ_WINDOW_BLOCKS", 16)
+    with gzt.open(p, "rb") as f:
+        assert f.raw._gpu is not None and f.raw._gpu["subs"] is not None and len(f.raw._gpu["subs"]) == 4 * len(f.raw._gpu["sizes"])
+        assert f.read() == data
+    # files with the older index (block sizes only) are still read on the GPU, one warp per block
+    monkeypatch.setattr(gzt, "_WRITE_SUBS", False)
+    q = tmp_path / "v1.gz"
+    with gzt.open(q, "wb", threads=4) as f:
+        f.write(data)
+    with gzt.open(q, "rb") as f:
+        assert f.raw._gpu is not None and f.raw._gpu["subs"] is None
+        assert f.read() == data
