@@ -165,9 +165,11 @@ __device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off
  *   DENSE = true   the kernel is issue-bound, and on compressible data some lane of a warp needs the compare in nine
  *                  steps of ten: every lane compares the candidate's first eight bytes straight-line, without the
  *                  reject branch and without a break (a match that ends the walk sets the step counter instead). */
-template <bool DENSE>
+template <bool DENSE, bool FULLWIN>
 __device__ __forceinline__ uint32_t k2_search(const uint32_t *s_in, const uint16_t *s_prev, uint32_t pr, uint32_t poff,
-                                              uint32_t maxl, int depth, uint32_t nice, uint32_t max_dist, int rle) {
+                                              uint32_t maxl, int depth, uint32_t nice, uint32_t max_dist_arg, int rle) {
+    /* FULLWIN: the 32 KiB window of every caller but the small-wbits forms — a constant in the loop's distance test */
+    const uint32_t max_dist = FULLWIN ? B2D_WINDOW : max_dist_arg;
     const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
     uint32_t best = 3, bd = 0;
     /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
@@ -217,14 +219,17 @@ __device__ __forceinline__ uint32_t k2_search(const uint32_t *s_in, const uint16
                         }
                     }
                 }
-                if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
+                /* x == 0 only when the long compare ran into maxl: 32 zero bits count as four more bytes, clamped next */
+                l += (uint32_t)__clz((int)__brev(x)) >> 3;
                 if (l > maxl) l = maxl;
                 if (l > best) {
                     best = l; bd = dist;
+                    /* nice_match is 258 at every level (b2d_level_policy; the launcher refuses anything else), and
+                     * l <= maxl <= 258: "l >= nice || l == maxl" is "l == maxl" — two instructions less per candidate */
                     if (DENSE) {
-                        if (l >= nice || l == maxl) step = 1;
+                        if (l == maxl) step = 1;
                     } else {
-                        if (l >= nice || l == maxl) break;
+                        if (l == maxl) break;
                         cbp = s_in8 + pr + best;
                         own_b = *cbp;
                     }
@@ -238,6 +243,7 @@ __device__ __forceinline__ uint32_t k2_search(const uint32_t *s_in, const uint16
 
 #define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
 
+template <bool FULLWIN>
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
         const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
@@ -284,7 +290,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
     /* the tile's first 1024 positions are searched with the quick-reject coding and tell which coding suits the rest */
     uint32_t t = tid, hit = 0;
     if (t < tile_len) {
-        const uint32_t m = k2_search<false>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+        const uint32_t m = k2_search<false, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
         mout[t] = m;
         hit = m != 0u;
     }
@@ -292,10 +298,10 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
     t += K2_THREADS;
     if (dense) {
         for (; t < tile_len; t += K2_THREADS)
-            mout[t] = k2_search<true>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+            mout[t] = k2_search<true, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
     } else {
         for (; t < tile_len; t += K2_THREADS)
-            mout[t] = k2_search<false>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+            mout[t] = k2_search<false, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
     }
 }
 
@@ -993,7 +999,9 @@ static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
 static size_t k2_smem() { return K2_IN_BYTES_T + 2u * (B2D_WINDOW + K2_TILE) + 32u; }
 
 cudaError_t b2d_kernels_init(void) {
-    cudaError_t e = cudaFuncSetAttribute(k_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
+    cudaError_t e = cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_match_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
     if (e != cudaSuccess) return e;
@@ -1023,11 +1031,15 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     }
     MARK(1);
     if (pol.search != B2D_SEARCH_NONE) {
+        if (pol.nice < (int)B2D_MAX_MATCH) return cudaErrorInvalidValue;      /* see k2_search */
         if (pol.depth == 1)
             k_match_d1<<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist,
                                                               pol.search == B2D_SEARCH_RLE);
+        else if (J->max_dist == B2D_WINDOW)
+            k_match<true><<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
+                                                        pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
         else
-            k_match<<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
+            k_match<false><<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
                                                         pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);

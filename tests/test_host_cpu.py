@@ -203,3 +203,47 @@ def test_reader_without_a_device_reads_indexed_files_through_cpython(tmp_path):
     with gzt.open(p, "rb") as f:
         assert f.raw._gpu is None
         assert f.read() == data
+
+
+def _bgzf(data, blk=65280):
+    import struct
+    out = []
+    for piece in [data[o:o + blk] for o in range(0, len(data), blk)] + [b""]:
+        c = zlib.compressobj(6, zlib.DEFLATED, -15)
+        body = c.compress(piece) + c.flush()
+        out.append(b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff\x06\x00BC\x02\x00" + struct.pack("<H", len(body) + 25) + body
+                   + struct.pack("<II", zlib.crc32(piece), len(piece)))
+    return b"".join(out)
+
+
+def test_bgzf_scan_is_plain_host_code(tmp_path):
+    """b2d_bgzf_scan finds the members of a BGZF file through their BC subfields (the layout of the reference's fixture
+    tests/data/test.fastq.bgzip.gz); without a device the reader hands BGZF files to CPython like any other gzip file."""
+    import ctypes
+    import gzip
+    import synthdata
+    from zlib_ng_b200 import _native, gzip_ng_threaded
+    L = _native.lib()
+    data = synthdata.make("fastq", 700_000, 3).tobytes()
+    blob = _bgzf(data)
+    n = len(blob)
+    m = n // 28 + 16
+    po, pl = (ctypes.c_uint64 * m)(), (ctypes.c_uint32 * m)()
+    rl, cr = (ctypes.c_uint32 * m)(), (ctypes.c_uint32 * m)()
+    cnt, used = ctypes.c_uint64(0), ctypes.c_uint64(0)
+    assert L.b2d_bgzf_scan(blob, n, m, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)) == 0
+    assert used.value == n and cnt.value == -(-len(data) // 65280) + 1 and sum(rl[:cnt.value]) == len(data)
+    off = 0
+    for i in range(cnt.value):
+        piece = zlib.decompressobj(-15).decompress(blob[po[i]:po[i] + pl[i]])
+        assert piece == data[off:off + rl[i]] and zlib.crc32(piece) == cr[i]
+        off += rl[i]
+    # a buffer cut inside a member stops at the last complete one; data that is not BGZF yields no members
+    assert L.b2d_bgzf_scan(blob, n - 40, m, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)) == 0 and used.value < n - 40
+    plain = gzip.compress(data[:1000])
+    assert L.b2d_bgzf_scan(plain, len(plain), m, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)) == 0 and cnt.value == 0
+    if L.b2d_device_count() == 0:
+        p = tmp_path / "x.bgzf.gz"
+        p.write_bytes(blob)
+        with gzip_ng_threaded.open(p, "rb") as f:
+            assert f.raw._gpu is None and f.read() == data
