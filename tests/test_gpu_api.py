@@ -553,3 +553,23 @@ def test_gzip_ng_module(fastq, tmp_path):
     with gzip_ng.open(p, "rb") as f:
         assert f.read(10) == fastq[:10]
     assert gzip_ng.decompress(p.read_bytes()) == fastq[:2_000_000]
+
+
+def test_compressobj_copy_of_a_long_stream(zng, monkeypatch):
+    """copy() while the stream gathers its input in page-locked memory (long streams switch to it): both objects go on
+    independently and produce what one compress() call produces"""
+    monkeypatch.setattr(zng, "_STREAM_THRESHOLD", 1 << 20)
+    monkeypatch.setattr(zng, "_PIN_BYTES", 1 << 20)
+    data = synthdata.make("mixed", 6_000_000, 23).tobytes()
+    co = zng.compressobj(6, zng.DEFLATED, 31)
+    head = b"".join(co.compress(data[i:i + 300_000]) for i in range(0, 3_300_000, 300_000))
+    assert co._pin is not None and co._pin_fill > 0          # part of the input sits in the gather buffer
+    twin = co.copy()
+    a = head + co.compress(data[3_300_000:]) + co.flush()
+    b = head + twin.compress(data[3_300_000:5_000_000]) + twin.compress(data[5_000_000:]) + twin.flush()
+    assert a == b == zng.compress(data, 6, 31)
+    assert zlib.decompress(a, 31) == data
+    # flush modes in the middle of a long stream
+    co = zng.compressobj(1)
+    parts = [co.compress(data[:2_500_000]), co.flush(zng.Z_SYNC_FLUSH), co.compress(data[2_500_000:]), co.flush(zng.Z_FULL_FLUSH), co.flush()]
+    assert zlib.decompress(b"".join(parts)) == data
