@@ -153,97 +153,114 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
 #define K2_IN_BYTES (B2D_WINDOW + B2D_SUB + 16u + 288u)   /* +16 align slack, +258+pad look-ahead (k_match_d1: whole sub-blocks) */
 #define K2_IN_BYTES_T (B2D_WINDOW + K2_TILE + 16u + 288u)  /* k_match */
 
-__device__ __forceinline__ uint32_t ldu32(const uint32_t *s32, uint32_t byte_off) {
-    const uint32_t wi = byte_off >> 2;
-    return __funnelshift_r(s32[wi], s32[wi + 1], (byte_off & 3u) << 3);
+/* shared-memory loads by 32-bit shared address: candidate addresses are `own address - distance`, one subtract and one
+ * mask, without the index arithmetic a C++ array expression costs per candidate */
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32_4(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+4];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32_8(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+8];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32_12(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+12];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32_16(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+16];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds16(uint32_t a) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds8(uint32_t a) { uint32_t v; asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+/* whole equal bytes at the low end of a xor of two little-endian words (4 for x == 0): bit-reverse + count-leading-zeros */
+__device__ __forceinline__ uint32_t eq_bytes(uint32_t x) {
+    uint32_t r;
+    asm("{\n\t.reg .b32 t;\n\tbrev.b32 t, %1;\n\tclz.b32 %0, t;\n\t}" : "=r"(r) : "r"(x));
+    return r >> 3;
 }
 
-/* Best match of the position at shared byte index `pr` (at most `maxl` bytes, `depth` candidates).  Two codings of
- * the same search, same result:
+/* Best match of the position at shared byte address `pa` (= address of s_in + its byte index; `la` = address of its
+ * link), at most `maxl` bytes, `depth` candidates (DEPTH > 0: that many, as straight-line code without a step counter).
+ * Two codings of the same search, same result:
  *   DENSE = false  quick reject on the byte at index `best` before a candidate is compared; cheapest where hardly any
  *                  candidate is a match (incompressible data: the whole warp skips the compare code);
  *   DENSE = true   the kernel is issue-bound, and on compressible data some lane of a warp needs the compare in nine
  *                  steps of ten: every lane compares the candidate's first eight bytes straight-line, without the
- *                  reject branch and without a break (a match that ends the walk sets the step counter instead). */
-template <bool DENSE, bool FULLWIN>
-__device__ __forceinline__ uint32_t k2_search(const uint32_t *s_in, const uint16_t *s_prev, uint32_t pr, uint32_t poff,
-                                              uint32_t maxl, int depth, uint32_t nice, uint32_t max_dist_arg, int rle) {
+ *                  reject branch.
+ * The shared window starts 4-byte aligned, so a byte address shifted left by 3 is, in its low five bits, the funnel
+ * shift that lines the bytes at that address up (shf wraps the amount). */
+template <bool DENSE, bool FULLWIN, int DEPTH>
+__device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t dist, uint32_t maxl, int depth, uint32_t max_dist_arg) {
     /* FULLWIN: the 32 KiB window of every caller but the small-wbits forms — a constant in the loop's distance test */
     const uint32_t max_dist = FULLWIN ? B2D_WINDOW : max_dist_arg;
-    const uint8_t *s_in8 = reinterpret_cast<const uint8_t *>(s_in);
     uint32_t best = 3, bd = 0;
     /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
      * pushes the running distance past max_dist, so one compare ends the walk either way */
-    /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links exist */
-    uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : s_prev[pr - poff];
     if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
         /* the position's first 16 bytes stay in registers: most compares end inside them */
+        const uint32_t pw = pa & ~3u, osh = pa << 3;
         uint32_t own[4];
         {
-            const uint32_t wi = pr >> 2, sh = (pr & 3u) << 3;
-            const uint32_t a0 = s_in[wi], a1 = s_in[wi + 1], a2 = s_in[wi + 2], a3 = s_in[wi + 3], a4 = s_in[wi + 4];
-            own[0] = __funnelshift_r(a0, a1, sh); own[1] = __funnelshift_r(a1, a2, sh);
-            own[2] = __funnelshift_r(a2, a3, sh); own[3] = __funnelshift_r(a3, a4, sh);
+            const uint32_t a0 = lds32(pw), a1 = lds32_4(pw), a2 = lds32_8(pw), a3 = lds32_12(pw), a4 = lds32_16(pw);
+            own[0] = __funnelshift_r(a0, a1, osh); own[1] = __funnelshift_r(a1, a2, osh);
+            own[2] = __funnelshift_r(a2, a3, osh); own[3] = __funnelshift_r(a3, a4, osh);
         }
         uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
-        int step = depth;
-        const uint32_t osh = (pr & 3u) << 3;
-        /* byte addresses inside the shared window, so that a step's loads are one subtract each */
-        const uint8_t *lpb = reinterpret_cast<const uint8_t *>(s_prev + (pr - poff));
-        const uint8_t *cbp = s_in8 + pr + best;         /* own_b's address; the candidate's is cbp - dist */
-        do {
-            const uint32_t nd = *reinterpret_cast<const uint16_t *>(lpb - 2u * dist);   /* next link: independent of the test below */
-            if (DENSE || *(cbp - dist) == own_b) {
-                const uint32_t cand = pr - dist;
-                uint32_t cw = cand >> 2;
-                const uint32_t csh = (cand & 3u) << 3;
-                const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
+        uint32_t cba = pa + best;                       /* own_b's address; the candidate's is cba - dist */
+        /* one candidate; true = the walk is over (nothing can beat a match of maxl bytes) */
+        auto visit = [&](uint32_t &nd) -> bool {
+            nd = lds16(la - 2u * dist);                 /* next link: independent of the compare below */
+            if (DENSE || lds8(cba - dist) == own_b) {
+                const uint32_t ca = pa - dist, cw = ca & ~3u, csh = ca << 3;
+                const uint32_t a0 = lds32(cw), a1 = lds32_4(cw), a2 = lds32_8(cw);
                 const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own[0];
                 const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own[1];
                 uint32_t x = x0 ? x0 : x1, l = x0 ? 0u : 4u;      /* most compares end in the first 8 bytes */
                 if ((x0 | x1) == 0u) {
-                    const uint32_t a3 = s_in[cw + 3], a4 = s_in[cw + 4];
+                    const uint32_t a3 = lds32_12(cw), a4 = lds32_16(cw);
                     if ((x = __funnelshift_r(a2, a3, csh) ^ own[2]) != 0) l = 8;
                     else if ((x = __funnelshift_r(a3, a4, csh) ^ own[3]) != 0) l = 12;
                     else {
                         /* long match: 8 bytes per trip, each aligned word of either side loaded once */
                         l = 16;
-                        cw += 4;
-                        uint32_t ow = (pr >> 2) + 4u, cp = a4, op = s_in[ow];
+                        uint32_t cq = cw + 16u, oq = pw + 16u, cp = a4, op = lds32(oq);
                         while (l < maxl) {
-                            const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], o1 = s_in[ow + 1], o2 = s_in[ow + 2];
+                            const uint32_t c1 = lds32_4(cq), c2 = lds32_8(cq), o1 = lds32_4(oq), o2 = lds32_8(oq);
                             if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, o1, osh)) != 0) break;
                             l += 4;
                             if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(o1, o2, osh)) != 0) break;
-                            l += 4; cw += 2; ow += 2; cp = c2; op = o2;
+                            l += 4; cq += 8u; oq += 8u; cp = c2; op = o2;
                         }
                     }
                 }
-                /* x == 0 only when the long compare ran into maxl: 32 zero bits count as four more bytes, clamped next */
-                l += (uint32_t)__clz((int)__brev(x)) >> 3;
+                /* x == 0 only when the long compare ran into maxl: that counts as four more bytes, clamped next */
+                l += eq_bytes(x);
                 if (l > maxl) l = maxl;
                 if (l > best) {
                     best = l; bd = dist;
                     /* nice_match is 258 at every level (b2d_level_policy; the launcher refuses anything else), and
-                     * l <= maxl <= 258: "l >= nice || l == maxl" is "l == maxl" — two instructions less per candidate */
-                    if (DENSE) {
-                        if (l == maxl) step = 1;
-                    } else {
-                        if (l == maxl) break;
-                        cbp = s_in8 + pr + best;
-                        own_b = *cbp;
-                    }
+                     * l <= maxl <= 258: "l >= nice || l == maxl" is "l == maxl" */
+                    if (l == maxl) return true;
+                    if (!DENSE) { cba = pa + best; own_b = lds8(cba); }
                 }
             }
-            dist += nd;
-        } while (--step > 0 && dist <= max_dist);
+            return false;
+        };
+        if (DEPTH > 0) {
+#pragma unroll
+            for (int i = 0; i < DEPTH; ++i) {
+                uint32_t nd;
+                const bool over = visit(nd);
+                dist += nd;
+                if (i + 1 < DEPTH && (over | (dist > max_dist))) break;
+            }
+        } else {
+            int step = depth;
+            for (;;) {
+                uint32_t nd;
+                const bool over = visit(nd);
+                dist += nd;
+                if (over | (--step <= 0) | (dist > max_dist)) break;
+            }
+        }
     }
     return best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
 }
 
 #define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
 
-template <bool FULLWIN>
+/* DEPTH > 0: the policy's chain depth as a compile-time constant (levels 4-6); 0: the `depth` argument */
+template <bool FULLWIN, int DEPTH>
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
         const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
@@ -280,28 +297,31 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
     __syncthreads();
     const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
     const uint32_t tile_off = (uint32_t)(tile_start - ws_al);
-    uint32_t *mout = match + (tile_start - D);
-    /* no match crosses a parse unit (tile starts are unit-aligned relative to the data) */
-    auto max_len = [&](uint32_t t) -> uint32_t {
-        const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
-        const uint32_t m = to_unit < to_end ? to_unit : to_end;
-        return m > B2D_MAX_MATCH ? B2D_MAX_MATCH : m;
-    };
+    /* this thread's positions are tid, tid + 1024, ...: K2_THREADS == B2D_UNIT, so all of them sit at the same offset
+     * of their parse units and no match crosses a unit (tile starts are unit-aligned relative to the data) */
+    static_assert(K2_THREADS == B2D_UNIT, "one thread per offset of a parse unit");
+    const uint32_t to_unit = B2D_UNIT - tid < B2D_MAX_MATCH ? B2D_UNIT - tid : B2D_MAX_MATCH;
+    uint32_t *mp = match + (tile_start - D) + tid;
+    uint32_t pa = (uint32_t)__cvta_generic_to_shared(s_in) + tile_off + tid;                    /* byte address of the position */
+    uint32_t la = (uint32_t)__cvta_generic_to_shared(s_prev) + 2u * (tile_off + tid - poff);    /* address of its link */
+    /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links are staged */
+    auto first_dist = [&](uint32_t t) -> uint32_t { return rle ? (tile_off + t >= 1u ? 1u : K_NOLINK) : lds16(la); };
+    auto max_len = [&](uint32_t t) -> uint32_t { const uint32_t to_end = tile_len - t; return to_unit < to_end ? to_unit : to_end; };
     /* the tile's first 1024 positions are searched with the quick-reject coding and tell which coding suits the rest */
     uint32_t t = tid, hit = 0;
     if (t < tile_len) {
-        const uint32_t m = k2_search<false, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
-        mout[t] = m;
+        const uint32_t m = k2_search<false, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
+        *mp = m;
         hit = m != 0u;
     }
     const bool dense = __syncthreads_count((int)hit) >= (int)K2_DENSE_HITS;
-    t += K2_THREADS;
+    t += K2_THREADS; mp += K2_THREADS; pa += K2_THREADS; la += 2u * K2_THREADS;
     if (dense) {
-        for (; t < tile_len; t += K2_THREADS)
-            mout[t] = k2_search<true, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+        for (; t < tile_len; t += K2_THREADS, mp += K2_THREADS, pa += K2_THREADS, la += 2u * K2_THREADS)
+            *mp = k2_search<true, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
     } else {
-        for (; t < tile_len; t += K2_THREADS)
-            mout[t] = k2_search<false, FULLWIN>(s_in, s_prev, tile_off + t, poff, max_len(t), depth, nice, max_dist, rle);
+        for (; t < tile_len; t += K2_THREADS, mp += K2_THREADS, pa += K2_THREADS, la += 2u * K2_THREADS)
+            *mp = k2_search<false, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
     }
 }
 
@@ -999,10 +1019,11 @@ static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
 static size_t k2_smem() { return K2_IN_BYTES_T + 2u * (B2D_WINDOW + K2_TILE) + 32u; }
 
 cudaError_t b2d_kernels_init(void) {
-    cudaError_t e = cudaFuncSetAttribute(k_match<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_match<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem());
-    if (e != cudaSuccess) return e;
+    cudaError_t e = cudaSuccess;
+#define K2_ATTR(F, DP) do { e = cudaFuncSetAttribute(k_match<F, DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem()); \
+                            if (e != cudaSuccess) return e; } while (0)
+    K2_ATTR(true, 0); K2_ATTR(true, 4); K2_ATTR(true, 5); K2_ATTR(true, 6); K2_ATTR(false, 0);
+#undef K2_ATTR
     e = cudaFuncSetAttribute(k_match_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k4_smem());
@@ -1035,12 +1056,19 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
         if (pol.depth == 1)
             k_match_d1<<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist,
                                                               pol.search == B2D_SEARCH_RLE);
-        else if (J->max_dist == B2D_WINDOW)
-            k_match<true><<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
-                                                        pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
-        else
-            k_match<false><<<(uint32_t)((n + K2_TILE - 1) / K2_TILE), K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match,
-                                                        pol.depth, (uint32_t)pol.nice, J->max_dist, pol.search == B2D_SEARCH_RLE);
+        else {
+            const uint32_t grid = (uint32_t)((n + K2_TILE - 1) / K2_TILE);
+            const int rle = pol.search == B2D_SEARCH_RLE;
+#define K2_GO(F, DP) k_match<F, DP><<<grid, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, pol.depth, \
+                                                                        (uint32_t)pol.nice, J->max_dist, rle)
+            /* the default window and the depths of levels 4-6 get their own instances (constants instead of loop state) */
+            if (J->max_dist != B2D_WINDOW) K2_GO(false, 0);
+            else if (pol.depth == 6) K2_GO(true, 6);
+            else if (pol.depth == 5) K2_GO(true, 5);
+            else if (pol.depth == 4) K2_GO(true, 4);
+            else K2_GO(true, 0);
+#undef K2_GO
+        }
     } else {
         cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
         if (e != cudaSuccess) return e;
