@@ -177,16 +177,21 @@ __device__ __forceinline__ uint32_t eq_bytes(uint32_t x) {
  *   DENSE = true   the kernel is issue-bound, and on compressible data some lane of a warp needs the compare in nine
  *                  steps of ten: every lane compares the candidate's first eight bytes straight-line, without the
  *                  reject branch.
- * The shared window starts 4-byte aligned, so a byte address shifted left by 3 is, in its low five bits, the funnel
- * shift that lines the bytes at that address up (shf wraps the amount). */
+ * The walk's state is the candidate's byte address `ca` and its link's address `lc` (each link moves both down), and
+ * the best match so far is one key, length << 18 | candidate address: a maximum over keys keeps the longest match and,
+ * among equals, the nearest one — the one found first, as distances grow along a chain.  Shared addresses are below
+ * 2^18.  The shared window starts 4-byte aligned, so a byte address shifted left by 3 is, in its low five bits, the
+ * funnel shift that lines the bytes at that address up (shf wraps the amount). */
+#define K2_KEY_SHIFT 18
 template <bool DENSE, bool FULLWIN, int DEPTH>
-__device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t dist, uint32_t maxl, int depth, uint32_t max_dist_arg) {
+__device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t maxl, int depth, uint32_t max_dist_arg) {
     /* FULLWIN: the 32 KiB window of every caller but the small-wbits forms — a constant in the loop's distance test */
     const uint32_t max_dist = FULLWIN ? B2D_WINDOW : max_dist_arg;
-    uint32_t best = 3, bd = 0;
     /* links are distances to the previous position of the same bucket; K_NOLINK (no predecessor)
      * pushes the running distance past max_dist, so one compare ends the walk either way */
-    if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
+    const uint32_t d0 = lds16(la);
+    uint32_t key = (3u << K2_KEY_SHIFT) | ((1u << K2_KEY_SHIFT) - 1u);     /* beats every match of three bytes */
+    if (maxl >= B2D_MIN_MATCH && d0 <= max_dist) {
         /* the position's first 16 bytes stay in registers: most compares end inside them */
         const uint32_t pw = pa & ~3u, osh = pa << 3;
         uint32_t own[4];
@@ -196,12 +201,14 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
             own[2] = __funnelshift_r(a2, a3, osh); own[3] = __funnelshift_r(a3, a4, osh);
         }
         uint32_t own_b = own[0] >> 24;                  /* byte at index `best`: a longer match must repeat it */
-        uint32_t cba = pa + best;                       /* own_b's address; the candidate's is cba - dist */
+        uint32_t boff = 3;                              /* that index (DENSE = false only) */
+        uint32_t ca = pa - d0, lc = la - 2u * d0;
+        const uint32_t ca_min = pa - max_dist;          /* the window's far end: a shared address, or "negative" (huge) */
         /* one candidate; true = the walk is over (nothing can beat a match of maxl bytes) */
         auto visit = [&](uint32_t &nd) -> bool {
-            nd = lds16(la - 2u * dist);                 /* next link: independent of the compare below */
-            if (DENSE || lds8(cba - dist) == own_b) {
-                const uint32_t ca = pa - dist, cw = ca & ~3u, csh = ca << 3;
+            nd = lds16(lc);                             /* next link: independent of the compare below */
+            if (DENSE || lds8(ca + boff) == own_b) {
+                const uint32_t cw = ca & ~3u, csh = ca << 3;
                 const uint32_t a0 = lds32(cw), a1 = lds32_4(cw), a2 = lds32_8(cw);
                 const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own[0];
                 const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own[1];
@@ -223,16 +230,20 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
                         }
                     }
                 }
-                /* x == 0 only when the long compare ran into maxl: that counts as four more bytes, clamped next */
+                /* x == 0 only when the long compare ran into maxl: that counts as four more bytes.  l may overshoot maxl
+                 * (by less than 12); such a candidate ends the walk, and the length is clamped once, at the end */
                 l += eq_bytes(x);
-                if (l > maxl) l = maxl;
-                if (l > best) {
-                    best = l; bd = dist;
-                    /* nice_match is 258 at every level (b2d_level_policy; the launcher refuses anything else), and
-                     * l <= maxl <= 258: "l >= nice || l == maxl" is "l == maxl" */
-                    if (l == maxl) return true;
-                    if (!DENSE) { cba = pa + best; own_b = lds8(cba); }
+                const uint32_t k = (l << K2_KEY_SHIFT) + ca;
+                if (DENSE) {
+                    key = k > key ? k : key;
+                } else if (k > key) {
+                    key = k;
+                    boff = l;
+                    own_b = lds8(pa + l);       /* l >= maxl: a byte past the match, never compared (the walk ends) */
                 }
+                /* nice_match is 258 at every level (b2d_level_policy; the launcher refuses anything else) and
+                 * maxl <= 258: "l >= nice || l >= maxl" is "l >= maxl".  (A second candidate that long is never reached.) */
+                return l >= maxl;
             }
             return false;
         };
@@ -241,30 +252,32 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
             for (int i = 0; i < DEPTH; ++i) {
                 uint32_t nd;
                 const bool over = visit(nd);
-                dist += nd;
-                if (i + 1 < DEPTH && (over | (dist > max_dist))) break;
+                ca -= nd; lc -= 2u * nd;
+                /* signed: near the start of the buffer both may be below zero (addresses are < 2^18, distances < 2^17) */
+                if (i + 1 < DEPTH && (over | ((int32_t)ca < (int32_t)ca_min))) break;
             }
         } else {
             int step = depth;
             for (;;) {
                 uint32_t nd;
                 const bool over = visit(nd);
-                dist += nd;
-                if (over | (--step <= 0) | (dist > max_dist)) break;
+                ca -= nd; lc -= 2u * nd;
+                if (over | (--step <= 0) | ((int32_t)ca < (int32_t)ca_min)) break;
             }
         }
     }
-    return best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+    const uint32_t best = key >> K2_KEY_SHIFT;
+    return best > 3u ? b2d_pack_match(best < maxl ? best : maxl, pa - (key & ((1u << K2_KEY_SHIFT) - 1u))) : 0u;
 }
 
 #define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
 
-/* DEPTH > 0: the policy's chain depth as a compile-time constant (levels 4-6); 0: the `depth` argument */
+/* DEPTH > 0: the policy's chain depth as a compile-time constant (levels 4-6); 0: the `depth` argument.  Depth 1
+ * (level 1, Z_RLE) goes to k_match_d1. */
 template <bool FULLWIN, int DEPTH>
 __global__ void __launch_bounds__(K2_THREADS, 1)
 k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
-        const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t nice,
-        uint32_t max_dist, int rle) {
+        const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, int depth, uint32_t max_dist) {
     extern __shared__ __align__(16) uint8_t smem2[];
     uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(smem2 + K2_IN_BYTES_T);       /* 2*(W+SUB)+16 */
@@ -292,7 +305,7 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
         const uint64_t bstart = D + blk * (uint64_t)B2D_BLOCK;
         const uint64_t span_al = (bstart - (bstart < B2D_WINDOW ? bstart : B2D_WINDOW)) & ~(uint64_t)7;
         const uint4 *src = reinterpret_cast<const uint4 *>(prevd + blk * (uint64_t)B2D_LINKS + (wp_al - span_al));
-        if (!rle) for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
+        for (uint32_t i = tid; i < np; i += K2_THREADS) p4[i] = __ldg(src + i);
     }
     __syncthreads();
     const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
@@ -301,27 +314,31 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
      * of their parse units and no match crosses a unit (tile starts are unit-aligned relative to the data) */
     static_assert(K2_THREADS == B2D_UNIT, "one thread per offset of a parse unit");
     const uint32_t to_unit = B2D_UNIT - tid < B2D_MAX_MATCH ? B2D_UNIT - tid : B2D_MAX_MATCH;
-    uint32_t *mp = match + (tile_start - D) + tid;
-    uint32_t pa = (uint32_t)__cvta_generic_to_shared(s_in) + tile_off + tid;                    /* byte address of the position */
-    uint32_t la = (uint32_t)__cvta_generic_to_shared(s_prev) + 2u * (tile_off + tid - poff);    /* address of its link */
-    /* Z_RLE: the only candidate is the previous byte (deflate_rle.c); depth is 1 then and no links are staged */
-    auto first_dist = [&](uint32_t t) -> uint32_t { return rle ? (tile_off + t >= 1u ? 1u : K_NOLINK) : lds16(la); };
-    auto max_len = [&](uint32_t t) -> uint32_t { const uint32_t to_end = tile_len - t; return to_unit < to_end ? to_unit : to_end; };
+    /* the loop runs on the position's shared byte address; its link's address and its slot in `match` follow from it */
+    const uint32_t pa0 = (uint32_t)__cvta_generic_to_shared(s_in) + tile_off;                     /* the tile's first position */
+    const uint32_t la_off = (uint32_t)__cvta_generic_to_shared(s_prev) - 2u * poff
+                            - 2u * (uint32_t)__cvta_generic_to_shared(s_in);                      /* link address = 2 * pa + this */
+    const uint32_t pa_end = pa0 + tile_len;
+    /* the position's slot in `match` is at mb + 4 * pa (one multiply-add per position) */
+    const uint64_t mb = (uint64_t)(uintptr_t)(match + (tile_start - D)) - 4ull * pa0;
+    auto put = [&](uint32_t p, uint32_t m) { asm volatile("st.global.u32 [%0], %1;" :: "l"(mb + 4ull * p), "r"(m) : "memory"); };
+    uint32_t pa = pa0 + tid;
+    auto max_len = [&](uint32_t p) -> uint32_t { const uint32_t to_end = pa_end - p; return to_unit < to_end ? to_unit : to_end; };
     /* the tile's first 1024 positions are searched with the quick-reject coding and tell which coding suits the rest */
-    uint32_t t = tid, hit = 0;
-    if (t < tile_len) {
-        const uint32_t m = k2_search<false, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
-        *mp = m;
+    uint32_t hit = 0;
+    if (pa < pa_end) {
+        const uint32_t m = k2_search<false, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist);
+        put(pa, m);
         hit = m != 0u;
     }
     const bool dense = __syncthreads_count((int)hit) >= (int)K2_DENSE_HITS;
-    t += K2_THREADS; mp += K2_THREADS; pa += K2_THREADS; la += 2u * K2_THREADS;
+    pa += K2_THREADS;
     if (dense) {
-        for (; t < tile_len; t += K2_THREADS, mp += K2_THREADS, pa += K2_THREADS, la += 2u * K2_THREADS)
-            *mp = k2_search<true, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
+        for (; pa < pa_end; pa += K2_THREADS)
+            put(pa, k2_search<true, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist));
     } else {
-        for (; t < tile_len; t += K2_THREADS, mp += K2_THREADS, pa += K2_THREADS, la += 2u * K2_THREADS)
-            *mp = k2_search<false, FULLWIN, DEPTH>(pa, la, first_dist(t), max_len(t), depth, max_dist);
+        for (; pa < pa_end; pa += K2_THREADS)
+            put(pa, k2_search<false, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist));
     }
 }
 
@@ -1058,9 +1075,7 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
                                                               pol.search == B2D_SEARCH_RLE);
         else {
             const uint32_t grid = (uint32_t)((n + K2_TILE - 1) / K2_TILE);
-            const int rle = pol.search == B2D_SEARCH_RLE;
-#define K2_GO(F, DP) k_match<F, DP><<<grid, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, pol.depth, \
-                                                                        (uint32_t)pol.nice, J->max_dist, rle)
+#define K2_GO(F, DP) k_match<F, DP><<<grid, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, pol.depth, J->max_dist)
             /* the default window and the depths of levels 4-6 get their own instances (constants instead of loop state) */
             if (J->max_dist != B2D_WINDOW) K2_GO(false, 0);
             else if (pol.depth == 6) K2_GO(true, 6);
