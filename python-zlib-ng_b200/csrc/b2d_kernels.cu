@@ -49,8 +49,9 @@ template <int HB>
 __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n,
                                                uint64_t buf_readable, uint16_t *__restrict__ prevd) {
     extern __shared__ __align__(16) uint8_t smem1[];
-    uint16_t *head = reinterpret_cast<uint16_t *>(smem1);                         /* 32 KiB */
-    uint32_t *stage = reinterpret_cast<uint32_t *>(smem1 + (2u << HB));            /* 2 x 512 B ring */
+    uint16_t *head = reinterpret_cast<uint16_t *>(smem1);                         /* 2^HB entries */
+    /* 2 x 512 B ring + 16 B guard: a copy of the ring's first bytes, so that "the word after" never wraps */
+    uint32_t *stage = reinterpret_cast<uint32_t *>(smem1 + (2u << HB));
     const uint32_t lane = threadIdx.x;
     const uint64_t b = blockIdx.x;
     const uint64_t job_end = D + n;
@@ -72,6 +73,11 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
         return make_uint4(0, 0, 0, 0);
     };
     uint4 *stage4 = reinterpret_cast<uint4 *>(stage);
+    /* the batch at byte offset c lives in ring slot (c / 512) & 1 */
+    auto put_batch = [&](uint32_t slot, const uint4 &v) {
+        stage4[slot * 32u + lane] = v;
+        if (slot == 0 && lane == 0) stage4[2 * K1_BATCH / 16] = v;           /* the guard */
+    };
     /* positions are handled as 32-bit offsets r from span_start; a batch that starts before the span
      * (c0 is rounded down) gives wrapped-around offsets that fail every range test */
     const uint32_t span_len = (uint32_t)(end - span_start);
@@ -82,63 +88,74 @@ __global__ void __launch_bounds__(32) k_chains(const uint8_t *__restrict__ buf, 
      * output then depends on nothing but its 32 KiB of history and its data, wherever batches are cut */
     uint16_t *pd = prevd + b * (uint64_t)B2D_LINKS + (span_start & 7u);
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint32_t rel = (uint32_t)(c0 - span_start) + lane;          /* offset of this lane's position in step 0 */
-    uint32_t ring = (uint32_t)(c0 & (2 * K1_BATCH - 1)) + lane;
-    /* the batch at byte offset c lives in ring slot (c / 512) & 1 */
-    stage4[(uint32_t)((c0 >> 9) & 1) * 32 + lane] = load16(c0);
+    /* a lane's positions sit at the same byte of their words in every step (steps are 32 positions apart) */
+    const uint32_t sh = (lane & 3u) << 3, b4sel = 0x4440u | (lane & 3u);
+    auto hash_of = [&](const uint32_t *w) -> uint32_t {     /* w: the word holding the position's first byte */
+        const uint32_t w0 = w[0], w1 = w[1];
+        return b2d_hash5(__funnelshift_r(w0, w1, sh), __byte_perm(w1, 0u, b4sel), HB);
+    };
+    uint32_t slot = (uint32_t)(c0 >> 9) & 1u;
+    put_batch(slot, load16(c0));
     uint4 nxt = load16(c0 + K1_BATCH);
     __syncwarp();
-    /* hash of the lane's position in the step that starts at ring offset `ro` */
-    auto hash_at = [&](uint32_t ro) -> uint32_t {
-        const uint32_t qo = ro & (2 * K1_BATCH - 1);
-        const uint32_t w0 = stage[qo >> 2], w1 = stage[((qo >> 2) + 1) & (2 * K1_BATCH / 4 - 1)];
-        const uint32_t sh = (qo & 3u) << 3;
-        return b2d_hash5(__funnelshift_r(w0, w1, sh), (w1 >> sh) & 0xffu, HB);
-    };
-    uint32_t h_next = hash_at(ring);
-    for (uint64_t c = c0; c < end; c += K1_BATCH) {
-        stage4[(uint32_t)(((c >> 9) + 1) & 1) * 32 + lane] = nxt;
+    uint32_t h_next = hash_of(stage + slot * (K1_BATCH / 4) + (lane >> 2));
+    for (uint64_t c = c0; c < end; c += K1_BATCH, slot ^= 1u) {
+        put_batch(slot ^ 1u, nxt);
         nxt = load16(c + 2 * K1_BATCH);
         __syncwarp();
-#pragma unroll 4
-        for (uint32_t k = 0; k < K1_BATCH / 32; ++k) {
-            /* the next step's hash does not depend on the table: computed here so that its shared loads and
-             * multiplies overlap this step's read / write / read-back chain */
-            const uint32_t h = h_next;
-            h_next = hash_at(ring + 32u);
-            const uint32_t r = rel;
-            const bool active = r < act_len;
-            /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
-             * writes its own position, read back — if every lane still sees its own value no two
-             * lanes share a bucket and `old` is each lane's predecessor. */
-            const uint32_t r16 = r & 0xffffu;
-            const uint32_t old = active ? head[h] : 0u;
-            __syncwarp();
-            if (active) head[h] = (uint16_t)r16;
-            __syncwarp();
-            const bool lost = active && head[h] != r16;
-            const uint32_t dd = (r - old) & 0xffffu;
-            uint32_t d = (active && dd != 0 && dd <= r && dd <= B2D_WINDOW) ? dd : K_NOLINK;
-            if (__any_sync(FULL, lost)) {
-                /* Some bucket was hit twice (runs, short periods, small alphabets).  The losers write
-                 * again, so the first winner of such a bucket sees a foreign value too: now every lane
-                 * of a shared bucket knows it.  match.any costs ~12 cycles per distinct key, so only
-                 * those lanes bring their bucket; everyone else shares one dummy key. */
-                if (lost) head[h] = (uint16_t)r16;
+        const uint32_t rb = (uint32_t)(c - span_start) + lane;             /* this lane's offset in the batch's step 0 */
+        uint16_t *pb = pd + (int64_t)(int32_t)rb;
+        const uint32_t *sw = stage + slot * (K1_BATCH / 4) + (lane >> 2);  /* its word in step 0 */
+        const uint32_t *so = stage + (slot ^ 1u) * (K1_BATCH / 4) + (lane >> 2);   /* and in the next batch's step 0 */
+#pragma unroll 1
+        for (uint32_t half = 0; half < 2; ++half) {
+            const uint32_t *sn = half ? so : sw + 64;        /* the step after this half's last one */
+            const uint32_t rh = rb + half * (K1_BATCH / 2);
+            uint16_t *ph = pb + half * (K1_BATCH / 2);
+            const uint32_t *swh = sw + half * 64;
+#pragma unroll
+            for (uint32_t k = 0; k < K1_BATCH / 64; ++k) {
+                /* the next step's hash does not depend on the table: computed here so that its shared loads and
+                 * multiplies overlap this step's read / write / read-back chain */
+                const uint32_t h = h_next;
+                h_next = hash_of(k + 1 < K1_BATCH / 64 ? swh + 8 * (k + 1) : sn);
+                const uint32_t r = rh + 32u * k;
+                const bool active = r < act_len;
+                /* Ordered insert of the step's 32 positions.  Fast path: read the old head, every lane
+                 * writes its own position, read back — if every lane still sees its own value no two
+                 * lanes share a bucket and `old` is each lane's predecessor.  (Inactive lanes: old = back = r,
+                 * i.e. distance 0 = no link, and not lost.) */
+                uint32_t old = r, back = r;
+                if (active) old = head[h];
                 __syncwarp();
-                const bool shared = active && (lost || head[h] != r16);
-                const uint32_t m = __match_any_sync(FULL, shared ? h : 0x10000u);
-                if (shared) {
-                    const uint32_t lower = m & lt_mask;
-                    if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
+                if (active) head[h] = (uint16_t)r;
+                __syncwarp();
+                if (active) back = head[h];
+                const bool lost = ((back ^ r) & 0xffffu) != 0u;
+                const uint32_t dd = (r - old) & 0xffffu;
+                /* a distance beyond the window is stored as it is: every reader stops at the first link that takes
+                 * it past its max_dist (K_NOLINK itself is just the largest such value) */
+                uint32_t d = (dd != 0u) & (dd <= r) ? dd : K_NOLINK;
+                if (__any_sync(FULL, lost)) {
+                    /* Some bucket was hit twice (runs, short periods, small alphabets).  The losers write
+                     * again, so the first winner of such a bucket sees a foreign value too: now every lane
+                     * of a shared bucket knows it.  match.any costs ~12 cycles per distinct key, so only
+                     * those lanes bring their bucket; everyone else shares one dummy key. */
+                    const uint32_t r16 = r & 0xffffu;
+                    if (lost) head[h] = (uint16_t)r16;
+                    __syncwarp();
+                    const bool shared = active && (lost || head[h] != r16);
+                    const uint32_t m = __match_any_sync(FULL, shared ? h : 0x10000u);
+                    if (shared) {
+                        const uint32_t lower = m & lt_mask;
+                        if (lower) d = lane - (31u - (uint32_t)__clz((int)lower));
+                    }
+                    __syncwarp();
+                    if (shared && (m >> lane) == 1u) head[h] = (uint16_t)r16;   /* highest lane of the bucket is the head */
+                    __syncwarp();
                 }
-                __syncwarp();
-                if (shared && (m >> lane) == 1u) head[h] = (uint16_t)r16;   /* highest lane of the bucket is the head */
-                __syncwarp();
+                if (r < span_len) ph[32u * k] = (uint16_t)d;
             }
-            if (r < span_len) pd[r] = (uint16_t)d;
-            rel += 32u;
-            ring += 32u;
         }
     }
 }
@@ -1031,7 +1048,7 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 /* ------------------------------------------------------------------------- */
 /* host-side launchers (called from b2d_api.cu)                               */
 /* ------------------------------------------------------------------------- */
-static size_t k1_smem(int hb) { return (2u << hb) + 2u * K1_BATCH; }
+static size_t k1_smem(int hb) { return (2u << hb) + 2u * K1_BATCH + 16u; }
 static size_t k4_smem() { return K4_WARPS * sizeof(k4_warp_smem); }
 static size_t k2_smem() { return K2_IN_BYTES_T + 2u * (B2D_WINDOW + K2_TILE) + 32u; }
 
