@@ -360,13 +360,15 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
 }
 
 /* K2 at depth 1 (level 1, Z_RLE): a position has one candidate, so nothing walks the links and they need not be staged —
- * each thread reads its own link from global memory (coalesced).  Only the input window sits in shared memory
- * (65 KiB instead of 197), three CTAs share an SM and one tile's loads overlap the other's compares.  Same results as
- * k_match with depth == 1. */
+ * each thread reads its own links from global memory.  Only the input window sits in shared memory (65 KiB instead of
+ * 197), three CTAs share an SM and one tile's loads overlap the other's compares.  A thread takes the four positions of
+ * one aligned shared-memory word at a time: their own bytes are three word loads for all four, lined up with constant
+ * shifts.  Same results as k_match with depth == 1. */
 #define K2D1_THREADS 512
+template <bool RLE>
 __global__ void __launch_bounds__(K2D1_THREADS, 3)
 k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_readable,
-           const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, uint32_t max_dist, int rle) {
+           const uint16_t *__restrict__ prevd, uint32_t *__restrict__ match, uint32_t max_dist) {
     extern __shared__ __align__(16) uint8_t smem2[];
     uint32_t *s_in = reinterpret_cast<uint32_t *>(smem2);                       /* K2_IN_BYTES */
     const uint32_t tid = threadIdx.x;
@@ -394,41 +396,72 @@ k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf
     const uint32_t tile_len = (uint32_t)(tile_end - tile_start);
     const uint32_t tile_off = (uint32_t)(tile_start - ws_al);
     uint32_t *mout = match + (tile_start - D);
-    for (uint32_t t = tid; t < tile_len; t += K2D1_THREADS) {
-        const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
-        uint32_t maxl = to_unit < to_end ? to_unit : to_end;
-        if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
-        const uint32_t pr = tile_off + t;
-        const uint32_t dist = rle ? (pr >= 1u ? 1u : K_NOLINK) : (uint32_t)__ldg(links + t);
-        uint32_t l = 0;
-        if (maxl >= B2D_MIN_MATCH && dist <= max_dist) {
-            const uint32_t wi = pr >> 2, osh = (pr & 3u) << 3;
-            const uint32_t cand = pr - dist;
-            uint32_t cw = cand >> 2;
-            const uint32_t csh = (cand & 3u) << 3;
-            const uint32_t o0 = s_in[wi], o1 = s_in[wi + 1], o2 = s_in[wi + 2];
-            const uint32_t a0 = s_in[cw], a1 = s_in[cw + 1], a2 = s_in[cw + 2];
-            const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ __funnelshift_r(o0, o1, osh);
-            const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ __funnelshift_r(o1, o2, osh);
-            uint32_t x = x0 ? x0 : x1;
-            l = x0 ? 0u : 4u;
-            if ((x0 | x1) == 0u) {
-                /* longer than 8: 8 bytes per trip, each aligned word of either side loaded once */
-                l = 8;
-                cw += 2;
-                uint32_t ow = wi + 2u, cp = a2, op = o2;
-                while (l < maxl) {
-                    const uint32_t c1 = s_in[cw + 1], c2 = s_in[cw + 2], p1 = s_in[ow + 1], p2 = s_in[ow + 2];
-                    if ((x = __funnelshift_r(cp, c1, csh) ^ __funnelshift_r(op, p1, osh)) != 0) break;
-                    l += 4;
-                    if ((x = __funnelshift_r(c1, c2, csh) ^ __funnelshift_r(p1, p2, osh)) != 0) break;
-                    l += 4; cw += 2; ow += 2; cp = c2; op = p2;
-                }
-            }
-            if (x) l += (uint32_t)(__ffs((int)x) - 1) >> 3;
-            if (l > maxl) l = maxl;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(s_in);
+    /* groups = aligned words of the shared window; the first and the last one may reach outside the tile */
+    const uint32_t g_end = (tile_off + tile_len + 3u) >> 2;
+    /* match slots of a group are 16-byte aligned when the data starts a multiple of 4 bytes after the window's word 0
+     * (always, unless a dictionary of odd length comes first) */
+    const bool vec_out = (((tile_start - D) - tile_off) & 3u) == 0u;
+    for (uint32_t G = (tile_off >> 2) + tid; G < g_end; G += K2D1_THREADS) {
+        const uint32_t wa = sbase + 4u * G;
+        const uint32_t t0 = 4u * G - tile_off;              /* tile position of the word's byte 0 ("negative" before the tile) */
+        const uint16_t *lk = links + (int64_t)(int32_t)t0;
+        uint32_t *mo = mout + (int64_t)(int32_t)t0;
+        /* all four positions inside the tile (t0 wraps to a huge value before it): their links are one aligned 8-byte
+         * load (the window and the link array start at multiples of 4 positions of each other), their results one store */
+        const bool inner = t0 + 3u < tile_len && t0 < tile_len;
+        uint32_t dist[4], mres[4];
+        if (RLE) {
+            /* Z_RLE: the only candidate is the previous byte (deflate_rle.c) */
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) dist[j] = 4u * G + j >= 1u ? 1u : K_NOLINK;
+        } else if (inner) {
+            const uint2 lv = __ldg(reinterpret_cast<const uint2 *>(lk));
+            dist[0] = lv.x & 0xffffu; dist[1] = lv.x >> 16; dist[2] = lv.y & 0xffffu; dist[3] = lv.y >> 16;
+        } else {
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) dist[j] = t0 + j < tile_len ? (uint32_t)__ldg(lk + j) : K_NOLINK;
         }
-        mout[t] = l >= B2D_MIN_MATCH ? b2d_pack_match(l, dist) : 0u;
+        const uint32_t w0 = lds32(wa), w1 = lds32_4(wa), w2 = lds32_8(wa);
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+            const uint32_t t = t0 + j;
+            mres[j] = 0;
+            if (t >= tile_len) continue;
+            const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
+            uint32_t maxl = to_unit < to_end ? to_unit : to_end;
+            if (maxl > B2D_MAX_MATCH) maxl = B2D_MAX_MATCH;
+            uint32_t l = 0;
+            if (maxl >= B2D_MIN_MATCH && dist[j] <= max_dist) {
+                const uint32_t own0 = j ? __funnelshift_r(w0, w1, 8u * j) : w0, own1 = j ? __funnelshift_r(w1, w2, 8u * j) : w1;
+                const uint32_t ca = wa + j - dist[j], cw = ca & ~3u, csh = ca << 3;
+                const uint32_t a0 = lds32(cw), a1 = lds32_4(cw), a2 = lds32_8(cw);
+                const uint32_t x0 = __funnelshift_r(a0, a1, csh) ^ own0;
+                const uint32_t x1 = __funnelshift_r(a1, a2, csh) ^ own1;
+                uint32_t x = x0 ? x0 : x1;
+                l = x0 ? 0u : 4u;
+                if ((x0 | x1) == 0u) {
+                    /* longer than 8: 8 bytes per trip, each aligned word of either side loaded once */
+                    l = 8;
+                    uint32_t cq = cw + 8u, oq = wa + 8u, cp = a2, op = w2;
+                    while (l < maxl) {
+                        const uint32_t c1 = lds32_4(cq), c2 = lds32_8(cq), p1 = lds32_4(oq), p2 = lds32_8(oq);
+                        if ((x = __funnelshift_r(cp, c1, csh) ^ (j ? __funnelshift_r(op, p1, 8u * j) : op)) != 0) break;
+                        l += 4;
+                        if ((x = __funnelshift_r(c1, c2, csh) ^ (j ? __funnelshift_r(p1, p2, 8u * j) : p1)) != 0) break;
+                        l += 4; cq += 8u; oq += 8u; cp = c2; op = p2;
+                    }
+                }
+                l += eq_bytes(x);           /* x == 0: the long compare ran into maxl; four more bytes, clamped next */
+                if (l > maxl) l = maxl;
+            }
+            if (l >= B2D_MIN_MATCH) mres[j] = b2d_pack_match(l, dist[j]);
+        }
+        if (inner && vec_out) *reinterpret_cast<uint4 *>(mo) = make_uint4(mres[0], mres[1], mres[2], mres[3]);
+        else {
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) if (t0 + j < tile_len) mo[j] = mres[j];
+        }
     }
 }
 
@@ -1058,7 +1091,9 @@ cudaError_t b2d_kernels_init(void) {
                             if (e != cudaSuccess) return e; } while (0)
     K2_ATTR(true, 0); K2_ATTR(true, 4); K2_ATTR(true, 5); K2_ATTR(true, 6); K2_ATTR(false, 0);
 #undef K2_ATTR
-    e = cudaFuncSetAttribute(k_match_d1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
+    e = cudaFuncSetAttribute(k_match_d1<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_match_d1<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K2_IN_BYTES);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k4_smem());
     if (e != cudaSuccess) return e;
@@ -1087,9 +1122,12 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
     MARK(1);
     if (pol.search != B2D_SEARCH_NONE) {
         if (pol.nice < (int)B2D_MAX_MATCH) return cudaErrorInvalidValue;      /* see k2_search */
-        if (pol.depth == 1)
-            k_match_d1<<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist,
-                                                              pol.search == B2D_SEARCH_RLE);
+        if (pol.depth == 1) {
+            if (pol.search == B2D_SEARCH_RLE)
+                k_match_d1<true><<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist);
+            else
+                k_match_d1<false><<<nsub, K2D1_THREADS, K2_IN_BYTES, st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, J->max_dist);
+        }
         else {
             const uint32_t grid = (uint32_t)((n + K2_TILE - 1) / K2_TILE);
 #define K2_GO(F, DP) k_match<F, DP><<<grid, K2_THREADS, k2_smem(), st>>>(J->buf, J->D, n, J->buf_readable, J->prevd, J->match, pol.depth, J->max_dist)
