@@ -186,6 +186,18 @@ __device__ __forceinline__ uint32_t eq_bytes(uint32_t x) {
     return r >> 3;
 }
 
+/* 31 - (index of the lowest set bit), as bfind of the reversed word gives it; 0xffffffff for 0 */
+__device__ __forceinline__ uint32_t low_bit_from_top(uint32_t x) {
+    uint32_t r;
+    asm("{\n\t.reg .b32 t;\n\tbrev.b32 t, %1;\n\tbfind.u32 %0, t;\n\t}" : "=r"(r) : "r"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+
 /* Best match of the position at shared byte address `pa` (= address of s_in + its byte index; `la` = address of its
  * link), at most `maxl` bytes, `depth` candidates (DEPTH > 0: that many, as straight-line code without a step counter).
  * Two codings of the same search, same result:
@@ -221,6 +233,7 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
         uint32_t boff = 3;                              /* that index (DENSE = false only) */
         uint32_t ca = pa - d0, lc = la - 2u * d0;
         const uint32_t ca_min = pa - max_dist;          /* the window's far end: a shared address, or "negative" (huge) */
+        const uint32_t maxl_key = maxl << K2_KEY_SHIFT;
         /* one candidate; true = the walk is over (nothing can beat a match of maxl bytes) */
         auto visit = [&](uint32_t &nd) -> bool {
             nd = lds16(lc);                             /* next link: independent of the compare below */
@@ -247,20 +260,21 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
                         }
                     }
                 }
-                /* x == 0 only when the long compare ran into maxl: that counts as four more bytes.  l may overshoot maxl
-                 * (by less than 12); such a candidate ends the walk, and the length is clamped once, at the end */
-                l += eq_bytes(x);
-                const uint32_t k = (l << K2_KEY_SHIFT) + ca;
+                /* the key, put together with multiply-adds (the kernel is bound by the ALU pipe, the FMA pipe idles):
+                 * 8 * (equal low bytes of x) = ~(index of its lowest set bit, from the top) & 0x18.  x == 0 only when the
+                 * long compare ran into maxl, where the extra bytes do not matter.  The length may overshoot maxl (by less
+                 * than 12); such a candidate ends the walk, and the length is clamped once, at the end. */
+                const uint32_t k = mad_u32(~low_bit_from_top(x) & 0x18u, 1u << (K2_KEY_SHIFT - 3), mad_u32(l, 1u << K2_KEY_SHIFT, ca));
                 if (DENSE) {
                     key = k > key ? k : key;
                 } else if (k > key) {
                     key = k;
-                    boff = l;
-                    own_b = lds8(pa + l);       /* l >= maxl: a byte past the match, never compared (the walk ends) */
+                    boff = k >> K2_KEY_SHIFT;
+                    own_b = lds8(pa + boff);    /* >= maxl: a byte past the match, never compared (the walk ends) */
                 }
                 /* nice_match is 258 at every level (b2d_level_policy; the launcher refuses anything else) and
                  * maxl <= 258: "l >= nice || l >= maxl" is "l >= maxl".  (A second candidate that long is never reached.) */
-                return l >= maxl;
+                return k >= maxl_key;
             }
             return false;
         };
@@ -269,7 +283,7 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
             for (int i = 0; i < DEPTH; ++i) {
                 uint32_t nd;
                 const bool over = visit(nd);
-                ca -= nd; lc -= 2u * nd;
+                ca -= nd; lc = mad_u32(nd, 0xfffffffeu, lc);      /* lc - 2 * nd, on the FMA pipe */
                 /* signed: near the start of the buffer both may be below zero (addresses are < 2^18, distances < 2^17) */
                 if (i + 1 < DEPTH && (over | ((int32_t)ca < (int32_t)ca_min))) break;
             }
@@ -278,7 +292,7 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
             for (;;) {
                 uint32_t nd;
                 const bool over = visit(nd);
-                ca -= nd; lc -= 2u * nd;
+                ca -= nd; lc = mad_u32(nd, 0xfffffffeu, lc);      /* lc - 2 * nd, on the FMA pipe */
                 if (over | (--step <= 0) | ((int32_t)ca < (int32_t)ca_min)) break;
             }
         }
