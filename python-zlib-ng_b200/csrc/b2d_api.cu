@@ -105,6 +105,10 @@ static cudaError_t pinned_free(void *p) {
 }
 
 #define PROF_BATCHES 64
+/* decode streams of a host inflate call: neighbouring chunks decode side by side.  (Eight streams — every chunk of a 512 MiB
+ * call on its own — measured slower than four: 29 ms against 25 ms per call; a sub-block takes a warp 7-10 ms whatever
+ * shares the SM with it, so what matters is how early the first chunks' warps start, tools/reader_trace.py.) */
+#define B2D_INF_DEC_STREAMS 4
 #ifndef B2D_NLANE
 #define B2D_NLANE 4     /* batches of one call in flight on the device, each on its own stream with its own intermediates.  The
                          * chain stage runs one warp per 128 KiB block, so a batch of 64 MiB fills a quarter of the device's warp
@@ -175,7 +179,7 @@ struct b2d_ctx {
     uint32_t *d_inf_flags; uint64_t inf_flags_cap;                       /* one ready flag per block */
     cudaStream_t st_inf; cudaEvent_t ev_inf_fork, ev_inf_join;           /* the serial pass runs beside the decode */
     cudaStream_t st_inf_in, st_inf_out;                                  /* host calls: copies of chunk c+1 / c-1 beside chunk c's kernels */
-    cudaStream_t st_inf_dec[4];                                          /* ... and the decodes of neighbouring chunks beside each other */
+    cudaStream_t st_inf_dec[B2D_INF_DEC_STREAMS];                                          /* ... and the decodes of neighbouring chunks beside each other */
     std::vector<cudaEvent_t> ev_inf_h2d, ev_inf_done;                    /* per chunk */
     /* optional per-stage timing of device-resident calls */
     int profiling;
@@ -196,7 +200,7 @@ static void ctx_free(b2d_ctx *c) {
     if (c->st_inf) cudaStreamDestroy(c->st_inf);
     if (c->st_inf_in) cudaStreamDestroy(c->st_inf_in);
     if (c->st_inf_out) cudaStreamDestroy(c->st_inf_out);
-    for (int i = 0; i < 4; ++i) if (c->st_inf_dec[i]) cudaStreamDestroy(c->st_inf_dec[i]);
+    for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) if (c->st_inf_dec[i]) cudaStreamDestroy(c->st_inf_dec[i]);
     for (cudaEvent_t e : c->ev_inf_h2d) cudaEventDestroy(e);
     for (cudaEvent_t e : c->ev_inf_done) cudaEventDestroy(e);
     if (c->ev_inf_fork) cudaEventDestroy(c->ev_inf_fork);
@@ -459,7 +463,11 @@ static int ensure_lanes(b2d_ctx *c, int want) {
 static int ensure_second_lane(b2d_ctx *c) { return ensure_lanes(c, B2D_NLANE); }
 /* lanes a device-resident call uses: two batches of 128 MiB or more fill the device (k_chains: one warp per 128 KiB
  * block, 1776 warp slots), so more lanes would only hold memory (2.7 GiB each at 256 MiB); smaller batches use all four */
-static int device_lanes(const b2d_ctx *c) { return c->max_batch >= (128ull << 20) ? 2 : B2D_NLANE; }
+static int device_lanes(const b2d_ctx *c) {
+    static const int forced = [] { const char *e = getenv("B2D_DEVICE_LANES"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= B2D_NLANE ? v : 0; }();
+    if (forced) return forced;          /* measurements only */
+    return c->max_batch >= (128ull << 20) ? 2 : B2D_NLANE;
+}
 
 /* kernels one batch launches at this level / strategy */
 static uint32_t pipeline_launches(int level) {
@@ -1357,7 +1365,7 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     if (!c->st_inf_in) {
         CU(cudaStreamCreateWithFlags(&c->st_inf_in, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&c->st_inf_out, cudaStreamNonBlocking));
-        for (int i = 0; i < 4; ++i) CU(cudaStreamCreateWithFlags(&c->st_inf_dec[i], cudaStreamNonBlocking));
+        for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) CU(cudaStreamCreateWithFlags(&c->st_inf_dec[i], cudaStreamNonBlocking));
     }
     const uint64_t nchunks = (nblocks + B2D_INF_CHUNK_BLOCKS - 1) / B2D_INF_CHUNK_BLOCKS;
     while (c->ev_inf_h2d.size() < nchunks) {
@@ -1372,7 +1380,7 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     uint8_t *d_stream = c->d_inf_in + B2D_WINDOW;
     const uint8_t *d_dict = dict_n ? c->d_inf_in : nullptr;
     /* Chunks of 512 blocks flow through three stages: the compressed bytes of chunk k + 1 go up (st_inf_in) while chunk
-     * k is decoded (one of four decode streams: a block takes a warp milliseconds, so neighbouring chunks must decode
+     * k is decoded (one of B2D_INF_DEC_STREAMS decode streams: a block takes a warp milliseconds, so neighbouring chunks must decode
      * side by side to fill the device) and resolved (st_inf, which follows the decodes block by block) and the bytes of
      * chunk k - 1 come back (st_inf_out).  The chain over the block tails runs through all chunks on st_inf. */
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
@@ -1384,23 +1392,35 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     if (conc) {
         CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* index, flags, error words, dictionary are in place */
         CU(cudaStreamWaitEvent(c->st_inf, c->ev_inf_fork, 0));
-        for (int i = 0; i < 4; ++i) CU(cudaStreamWaitEvent(c->st_inf_dec[i], c->ev_inf_fork, 0));
+        for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) CU(cudaStreamWaitEvent(c->st_inf_dec[i], c->ev_inf_fork, 0));
     }
     cudaStream_t st_res = conc ? c->st_inf : c->st;                    /* where a chunk's bytes become final */
+    /* B2D_TRACE=1: when each chunk's upload, resolve and download ended (device time, ms from the start of the call) */
+    static const bool trace = getenv("B2D_TRACE") && getenv("B2D_TRACE")[0] == '1';
+    std::vector<cudaEvent_t> tev;
+    const auto t_host = std::chrono::steady_clock::now();
+    if (trace) {
+        tev.resize(3 * nchunks + 1);
+        for (auto &e : tev) CU(cudaEventCreate(&e));
+        CU(cudaEventRecord(tev[3 * nchunks], c->st));
+    }
     for (uint64_t k = 0; k < nchunks; ++k) {
         const uint64_t b0 = k * B2D_INF_CHUNK_BLOCKS, b1 = b0 + B2D_INF_CHUNK_BLOCKS < nblocks ? b0 + B2D_INF_CHUNK_BLOCKS : nblocks;
         const uint64_t lo = block_offsets[b0], hi = b1 < nblocks ? block_offsets[b1] : in_n;
-        cudaStream_t st_dec = conc ? c->st_inf_dec[k & 3] : c->st;
+        cudaStream_t st_dec = conc ? c->st_inf_dec[k % B2D_INF_DEC_STREAMS] : c->st;
         CU(cudaMemcpyAsync(d_stream + lo, in + lo, hi - lo, cudaMemcpyHostToDevice, c->st_inf_in));
         CU(cudaEventRecord(c->ev_inf_h2d[k], c->st_inf_in));
+        if (trace) CU(cudaEventRecord(tev[3 * k], c->st_inf_in));
         CU(cudaStreamWaitEvent(st_dec, c->ev_inf_h2d[k], 0));
         CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, d_dict, (uint32_t)dict_n,
                               c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_dec, st_res, mode));
         c->launches += B2D_INF_LAUNCHES;
         CU(cudaEventRecord(c->ev_inf_done[k], st_res));
+        if (trace) CU(cudaEventRecord(tev[3 * k + 1], st_res));
         CU(cudaStreamWaitEvent(c->st_inf_out, c->ev_inf_done[k], 0));
         const uint64_t o0 = b0 * (uint64_t)B2D_BLOCK, o1 = b1 * (uint64_t)B2D_BLOCK < raw_n ? b1 * (uint64_t)B2D_BLOCK : raw_n;
         CU(cudaMemcpyAsync(out + o0, c->d_inf_out + o0, o1 - o0, cudaMemcpyDeviceToHost, c->st_inf_out));
+        if (trace) CU(cudaEventRecord(tev[3 * k + 2], c->st_inf_out));
         if (k + 1 == nchunks) {
             if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, st_res)); c->launches += crc_launches(c->d_inf_out, raw_n); }
             if (st_res != c->st) { CU(cudaEventRecord(c->ev_inf_join, st_res)); CU(cudaStreamWaitEvent(c->st, c->ev_inf_join, 0)); }
@@ -1410,6 +1430,18 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     CU(cudaMemcpyAsync(err, c->d_inf_err, sizeof err, cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
     CU(cudaStreamSynchronize(c->st_inf_out));
+    if (trace) {
+        fprintf(stderr, "b2d_inflate_host_sub: %llu blocks, host %.2f ms; chunk: upload / resolved / downloaded (ms)\n", (unsigned long long)nblocks,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host).count());
+        for (uint64_t k = 0; k < nchunks; ++k) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, tev[3 * nchunks], tev[3 * k]);
+            cudaEventElapsedTime(&b, tev[3 * nchunks], tev[3 * k + 1]);
+            cudaEventElapsedTime(&d, tev[3 * nchunks], tev[3 * k + 2]);
+            fprintf(stderr, "   %2llu: %6.2f %6.2f %6.2f\n", (unsigned long long)k, a, b, d);
+        }
+        for (auto &e : tev) cudaEventDestroy(e);
+    }
     if (err[1] && !err[0]) {
         /* the pass over the tails gave up waiting for a decode (never a statement about the data): every block is decoded
          * by now, so resolve everything again on one stream and fetch the bytes once more */

@@ -32,7 +32,9 @@ import multiprocessing
 import os
 import queue
 import struct
+import sys
 import threading
+import time
 
 from . import _native, zlib_ng
 
@@ -63,6 +65,7 @@ _INDEX_CHUNK = 16000                      # block sizes per index member (XLEN i
 _LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size, index offset, blocks
 _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
+_READER_TRACE = os.environ.get("B2D_READER_TRACE", "") not in ("", "0")       # stage times on stderr when a reader closes
 _READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "512")), 1) * 8    # device blocks the reader decodes per GPU call
 _BGZF_WINDOW = max(int(os.environ.get("B2D_BGZF_WINDOW_MIB", "128")), 1) << 20      # compressed bytes of a BGZF file per GPU call
 
@@ -328,6 +331,7 @@ class _ThreadedGzipReader(io.RawIOBase):
                         if g["stop"]:
                             return
                 view = comp[1]
+                t0 = time.perf_counter()
                 if not self._pread_window(view, cpos, comp_n):
                     got = 0
                     while got < comp_n:                           # raw streams may return short reads
@@ -336,6 +340,7 @@ class _ThreadedGzipReader(io.RawIOBase):
                             raise EOFError("Compressed file ended before the end-of-stream marker was reached")
                         got += more
                 cpos += comp_n
+                g["t_file"] = g.get("t_file", 0.0) + time.perf_counter() - t0
                 g["comp_ready"].put((comp, comp_n, first, nb))
                 first += nb
             if not g["stop"]:
@@ -422,8 +427,10 @@ class _ThreadedGzipReader(io.RawIOBase):
                 subs = None
                 if g.get("subs"):                     # one warp per 32 KiB sub-block instead of one per block
                     subs = (ctypes.c_uint32 * (4 * nb))(*g["subs"][4 * first:4 * (first + nb)])
+                t0 = time.perf_counter()
                 rc = L.b2d_inflate_host_sub(ctx.handle, comp[0], comp_n, offs, subs, nb, tail if tail else None, len(tail),
                                             out_ptr, raw_n, ctypes.byref(crc))
+                g["t_gpu"] = g.get("t_gpu", 0.0) + time.perf_counter() - t0
                 g["comp_free"].put(comp)
                 if rc:
                     g["free"].put(out)
@@ -558,6 +565,7 @@ class _ThreadedGzipReader(io.RawIOBase):
         if g.get("kind") == "bgzf":
             return self._bgzf_start()
         sizes = g["sizes"]
+        t_setup = time.perf_counter()
 
         def bucket(n):       # few distinct sizes, so that the pinned pool can hand buffers to the next reader
             if n <= 32 << 20:
@@ -576,6 +584,7 @@ class _ThreadedGzipReader(io.RawIOBase):
             g["pinned"].append(ent)
             g["free"].put(ent[1:])
         g["cur"], g["cur_n"], g["off"], g["eof"] = None, 0, 0, False
+        g["t_setup"] = time.perf_counter() - t_setup
         g["threads"] = [threading.Thread(target=self._gpu_file_reader, daemon=True),
                         threading.Thread(target=self._gpu_worker, daemon=True)]
         for t in g["threads"]:
@@ -588,6 +597,9 @@ class _ThreadedGzipReader(io.RawIOBase):
         g["stop"] = True
         for t in g["threads"]:
             t.join()
+        if _READER_TRACE:
+            sys.stderr.write("reader: file %.1f ms, gpu calls %.1f ms, copies out %.1f ms, setup %.1f ms\n" % (
+                1e3 * g.get("t_file", 0.0), 1e3 * g.get("t_gpu", 0.0), 1e3 * g.get("t_copy", 0.0), 1e3 * g.get("t_setup", 0.0)))
         for size, ptr, view in g["pinned"]:
             _pinned_pool.put(size, ptr, view)
         g["pinned"] = []
@@ -632,7 +644,9 @@ class _ThreadedGzipReader(io.RawIOBase):
             # big reads (BufferedReader hands read(n) its own fresh bytes object): copy on native threads, which also
             # spreads the page faults of a destination nobody has touched yet
             daddr, _, keep = _native._addr(mv)
+            t0 = time.perf_counter()
             _native.check(_native.lib().b2d_host_copy(daddr, g["cur"][0] + g["off"], n, _COPY_THREADS))
+            g["t_copy"] = g.get("t_copy", 0.0) + time.perf_counter() - t0
             del keep
         else:
             mv[:n] = g["cur"][1][g["off"]:g["off"] + n]
