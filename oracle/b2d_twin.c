@@ -70,7 +70,7 @@ static void twin_matches(const uint8_t *buf, size_t D, size_t n, size_t b, const
                 d = pol.search == B2D_SEARCH_RLE ? 0u : prevd[cand];
             }
         }
-        match[p - D] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd) : 0u;
+        match[p - D] = best >= B2D_MIN_MATCH ? b2d_pack_match(best, bd, buf[p]) : (uint32_t)buf[p];
     }
 }
 

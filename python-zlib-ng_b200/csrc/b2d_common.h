@@ -116,10 +116,13 @@ B2D_HD uint32_t b2d_hash5(uint32_t w, uint32_t b4, int bits) {
 }
 
 /* ---- match / token packing ---------------------------------------------- */
-/* match record per input position: (len << 16) | dist, 0 = no match */
-B2D_HD uint32_t b2d_pack_match(uint32_t len, uint32_t dist) { return (len << 16) | dist; }
-B2D_HD uint32_t b2d_match_len(uint32_t m) { return m >> 16; }
-B2D_HD uint32_t b2d_match_dist(uint32_t m) { return m & 0xffffu; }
+/* match record per input position: (len - 3) << 23 | (dist - 1) << 8 | the position's own byte; bits 8.. are 0 where
+ * no match was found (len >= 4, so len - 3 is never 0 for a match).  Bits 8-30 are the low bits of the token a taken
+ * match becomes, bits 0-7 the token of a literal: the parse reads nothing but these records. */
+B2D_HD uint32_t b2d_pack_match(uint32_t len, uint32_t dist, uint32_t lit) { return ((len - 3u) << 23) | ((dist - 1u) << 8) | lit; }
+B2D_HD uint32_t b2d_match_len(uint32_t m) { return (m >> 23) ? (m >> 23) + 3u : 0u; }
+B2D_HD uint32_t b2d_match_dist(uint32_t m) { return ((m >> 8) & 0x7fffu) + 1u; }
+B2D_HD uint32_t b2d_match_lit(uint32_t m) { return m & 0xffu; }
 
 /* token: literal = byte value; match = 1<<31 | (len-3) << 15 | (dist-1) */
 B2D_HD uint32_t b2d_tok_match(uint32_t len, uint32_t dist) { return 0x80000000u | ((len - 3u) << 15) | (dist - 1u); }

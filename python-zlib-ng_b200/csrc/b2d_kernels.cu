@@ -298,7 +298,8 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
         }
     }
     const uint32_t best = key >> K2_KEY_SHIFT;
-    return best > 3u ? b2d_pack_match(best < maxl ? best : maxl, pa - (key & ((1u << K2_KEY_SHIFT) - 1u))) : 0u;
+    /* without the position's own byte (the caller ORs it in) */
+    return best > 3u ? b2d_pack_match(best < maxl ? best : maxl, pa - (key & ((1u << K2_KEY_SHIFT) - 1u)), 0u) : 0u;
 }
 
 #define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
@@ -359,17 +360,17 @@ k_match(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf_re
     uint32_t hit = 0;
     if (pa < pa_end) {
         const uint32_t m = k2_search<false, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist);
-        put(pa, m);
+        put(pa, m | lds8(pa));
         hit = m != 0u;
     }
     const bool dense = __syncthreads_count((int)hit) >= (int)K2_DENSE_HITS;
     pa += K2_THREADS;
     if (dense) {
         for (; pa < pa_end; pa += K2_THREADS)
-            put(pa, k2_search<true, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist));
+            put(pa, k2_search<true, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist) | lds8(pa));
     } else {
         for (; pa < pa_end; pa += K2_THREADS)
-            put(pa, k2_search<false, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist));
+            put(pa, k2_search<false, FULLWIN, DEPTH>(pa, 2u * pa + la_off, max_len(pa), depth, max_dist) | lds8(pa));
     }
 }
 
@@ -440,7 +441,7 @@ k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j) {
             const uint32_t t = t0 + j;
-            mres[j] = 0;
+            mres[j] = (w0 >> (8u * j)) & 0xffu;                /* the position's own byte: what it is as a literal */
             if (t >= tile_len) continue;
             const uint32_t to_unit = B2D_UNIT - (t & (B2D_UNIT - 1u)), to_end = tile_len - t;
             uint32_t maxl = to_unit < to_end ? to_unit : to_end;
@@ -469,7 +470,7 @@ k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf
                 l += eq_bytes(x);           /* x == 0: the long compare ran into maxl; four more bytes, clamped next */
                 if (l > maxl) l = maxl;
             }
-            if (l >= B2D_MIN_MATCH) mres[j] = b2d_pack_match(l, dist[j]);
+            if (l >= B2D_MIN_MATCH) mres[j] = b2d_pack_match(l, dist[j], mres[j]);
         }
         if (inner && vec_out) *reinterpret_cast<uint4 *>(mo) = make_uint4(mres[0], mres[1], mres[2], mres[3]);
         else {
@@ -477,6 +478,12 @@ k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf
             for (uint32_t j = 0; j < 4; ++j) if (t0 + j < tile_len) mo[j] = mres[j];
         }
     }
+}
+
+/* match records without a search: the position's byte, nothing else (four positions per thread) */
+__global__ void __launch_bounds__(256) k_literals(const uint8_t *__restrict__ data, uint64_t n, uint32_t *__restrict__ match) {
+    const uint64_t i0 = 4ull * (blockIdx.x * 256ull + threadIdx.x);
+    for (uint32_t j = 0; j < 4; ++j) if (i0 + j < n) match[i0 + j] = data[i0 + j];
 }
 
 /* ------------------------------------------------------------------------- */
@@ -488,7 +495,7 @@ k_match_d1(const uint8_t *__restrict__ buf, uint64_t D, uint64_t n, uint64_t buf
 #define K3_SEG (B2D_UNIT / K3_SEGS)
 
 __global__ void __launch_bounds__(K3_THREADS, 5)
-k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict__ match,
+k_parse(uint64_t n, const uint32_t *__restrict__ match,
         uint32_t *__restrict__ tok, b2d_subinfo *__restrict__ info, uint32_t *__restrict__ hist, int lazy,
         uint32_t min_take) {
     __shared__ __align__(16) uint8_t s_len[B2D_SUB + 16];
@@ -502,6 +509,7 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
     const uint64_t sub_start = k * (uint64_t)B2D_SUB;
     const uint32_t len = (uint32_t)(n - sub_start < B2D_SUB ? n - sub_start : B2D_SUB);
     const uint32_t *m = match + sub_start;
+    const uint32_t take3 = min_take - 3u;                 /* >= 1: "no match" (0) never passes */
     /* match lengths -> one byte each (len-3, 0 = no match); sub_start is a multiple of 4 positions.
      * Whole uint4 groups first, eight loads in flight per thread; then the ragged end and the padding. */
     {
@@ -518,10 +526,11 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 #pragma unroll
             for (uint32_t j = 0; j < 8; ++j) {
                 const uint32_t i = i0 + j * K3_THREADS + tid;
-                const uint32_t l0 = v[j].x >> 16, l1 = v[j].y >> 16, l2 = v[j].z >> 16, l3 = v[j].w >> 16;
+                /* the records carry len - 3 in their top bits (0 = none) */
+                const uint32_t l0 = v[j].x >> 23, l1 = v[j].y >> 23, l2 = v[j].z >> 23, l3 = v[j].w >> 23;
                 if (i < full)      /* matches below min_take (Z_FILTERED) count as none */
-                    W[i] = (l0 >= min_take ? l0 - 3u : 0u) | ((l1 >= min_take ? l1 - 3u : 0u) << 8) |
-                           ((l2 >= min_take ? l2 - 3u : 0u) << 16) | ((l3 >= min_take ? l3 - 3u : 0u) << 24);
+                    W[i] = (l0 >= take3 ? l0 : 0u) | ((l1 >= take3 ? l1 : 0u) << 8) |
+                           ((l2 >= take3 ? l2 : 0u) << 16) | ((l3 >= take3 ? l3 : 0u) << 24);
             }
         }
         for (uint32_t i = full + tid; i < (B2D_SUB + 16) / 4; i += K3_THREADS) {
@@ -529,8 +538,8 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
 #pragma unroll
             for (uint32_t j = 0; j < 4; ++j) {
                 const uint32_t pos = 4 * i + j;
-                const uint32_t l = pos < len ? b2d_match_len(__ldg(m + pos)) : 0u;
-                pk |= (l >= min_take ? l - 3u : 0u) << (8 * j);
+                const uint32_t l = pos < len ? __ldg(m + pos) >> 23 : 0u;
+                pk |= (l >= take3 ? l : 0u) << (8 * j);
             }
             W[i] = pk;
         }
@@ -643,7 +652,6 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
      * zlib-ng _length_code / _dist_code idea, trees_tbl.h:76-132); one store and one literal/length
      * count per token, whatever its kind. */
     const uint32_t tbase = (uint32_t)sub_start;           /* a batch is at most 2 GiB: token indices fit 32 bits */
-    const uint8_t *src = data + sub_start;
     const uint32_t lt_mask = (1u << lane) - 1u;
     for (uint32_t w0 = warp * 4u; w0 < K3_WORDS; w0 += (K3_THREADS / 32) * 4u) {
         uint32_t rw[4], val[4];
@@ -655,18 +663,18 @@ k_parse(const uint8_t *__restrict__ data, uint64_t n, const uint32_t *__restrict
             reached[j] = (rw[j] >> lane) & 1u;
             take[j] = s_len[pos] != 0;
             val[j] = 0;
-            if (reached[j]) val[j] = take[j] ? __ldg(m + pos) : (uint32_t)__ldg(src + pos);
+            if (reached[j]) val[j] = __ldg(m + pos);     /* the record holds the token either way: match fields and literal */
         }
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j) {
             if (!reached[j]) continue;
             const uint32_t idx = s_base[w0 + j] + __popc(rw[j] & lt_mask);
-            uint32_t tv = val[j], sym = val[j];
+            uint32_t tv = b2d_match_lit(val[j]), sym = tv;
             if (take[j]) {
-                const uint32_t ml = b2d_match_len(val[j]), d1 = b2d_match_dist(val[j]) - 1u;
-                sym = 257u + s_lsym[ml - 3u];
+                const uint32_t d1 = (val[j] >> 8) & 0x7fffu;
+                sym = 257u + s_lsym[val[j] >> 23];
                 atomicAdd(&s_hist[B2D_LL_CODES + s_dsym[d1 < 256u ? d1 : 256u + (d1 >> 7)]], 1u);
-                tv = 0x80000000u | ((ml - 3u) << 15) | d1;      /* b2d_tok_match */
+                tv = 0x80000000u | (val[j] >> 8);         /* b2d_tok_match: (len - 3) << 15 | (dist - 1) */
             }
             atomicAdd(&s_hist[sym], 1u);
             tok[tbase + idx] = tv;
@@ -1154,11 +1162,11 @@ cudaError_t b2d_launch_pipeline(const b2d_job *J, cudaStream_t st, cudaEvent_t *
 #undef K2_GO
         }
     } else {
-        cudaError_t e = cudaMemsetAsync(J->match, 0, n * sizeof(uint32_t), st);
-        if (e != cudaSuccess) return e;
+        /* no search (level 0, Z_HUFFMAN_ONLY): every record is its position's literal */
+        k_literals<<<(uint32_t)((n + 4u * 256u - 1) / (4u * 256u)), 256, 0, st>>>(data, n, J->match);
     }
     MARK(2);
-    k_parse<<<nsub, K3_THREADS, 0, st>>>(data, n, J->match, J->tok, J->info, J->hist, pol.lazy, (uint32_t)pol.min_take);
+    k_parse<<<nsub, K3_THREADS, 0, st>>>(n, J->match, J->tok, J->info, J->hist, pol.lazy, (uint32_t)pol.min_take);
     MARK(3);
     k_plan<<<(nsub + K4_WARPS - 1) / K4_WARPS, K4_WARPS * 32, k4_smem(), st>>>(J->hist, J->info, J->plan, nsub, pol.blocks);
     MARK(4);
