@@ -41,8 +41,8 @@ METRIC = "gzip_compress_input_GBps_L6"
 STAGES = ["k_chains", "k_match", "k_parse", "k_plan", "k_scan", "k_emit"]
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per INPUT byte of a launch, from the `ncu --set full`
 # capture of a 256 MiB level-6 batch of this workload (profiles/README.md names the capture the figures come from)
-NCU_DRAM_BYTES_PER_INPUT_BYTE = {"k_chains": 3.57, "k_match": 7.33, "k_parse": 9.32, "k_plan": 0.063,
-                                 "k_scan": 0.004, "k_emit": 2.01}
+NCU_DRAM_BYTES_PER_INPUT_BYTE = {"k_chains": 3.58, "k_match": 7.33, "k_parse": 8.97, "k_plan": 0.063,
+                                 "k_scan": 0.004, "k_emit": 2.11}
 NCU_SOURCE = "profiles/ncu_r2_summary.txt"
 
 
