@@ -67,6 +67,7 @@ _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
 _READER_TRACE = os.environ.get("B2D_READER_TRACE", "") not in ("", "0")       # stage times on stderr when a reader closes
 _READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "512")), 1) * 8    # device blocks the reader decodes per GPU call
+_BGZF_HEAD = 128 << 10        # room in front of a BGZF window for what the window before left over (a member is at most 64 KiB)
 _BGZF_WINDOW = max(int(os.environ.get("B2D_BGZF_WINDOW_MIB", "128")), 1) << 20      # compressed bytes of a BGZF file per GPU call
 
 
@@ -476,31 +477,50 @@ class _ThreadedGzipReader(io.RawIOBase):
         left over (a partial member) starts the next window."""
         g = self._gpu
         L, ctx = _native.lib(), _native.default_context()
-        win, cap = g["win"], g["out_cap"]
-        comp_ptr, comp_view = g["comp"]
+        win, cap, head = g["win"], g["out_cap"], _BGZF_HEAD
+        bufs = g["comp"]                              # two (ptr, view) of head + win bytes: data is read in behind `head`
+        eof = False
+
+        def fill(view, lo, hi, res):
+            """raw.readinto until view[lo:hi] is full or the file ends; res = [bytes read, at the end of the file]"""
+            got, end = 0, False
+            try:
+                while lo + got < hi:
+                    k = self.raw.readinto(view[lo + got:hi])
+                    if not k:
+                        end = True
+                        break
+                    got += k
+            except BaseException as e:
+                res.append(e)
+                return
+            res.extend((got, end))
+
         try:
-            keep = 0                                  # bytes at the start of comp_view carried over from the last window
-            maxm = win // 28 + 16
+            maxm = (win + head) // 28 + 16
             po, pl = (ctypes.c_uint64 * maxm)(), (ctypes.c_uint32 * maxm)()
             rl, cr = (ctypes.c_uint32 * maxm)(), (ctypes.c_uint32 * maxm)()
-            eof = False
+            cur, start, keep = 0, head, 0             # the window is bufs[cur][start : start + keep]
             while not g["stop"]:
-                while keep < win and not eof:
-                    k = self.raw.readinto(comp_view[keep:win])
-                    if not k:
-                        eof = True
-                        break
-                    keep += k
+                ptr, view = bufs[cur]
+                if keep < win and not eof:            # (not after a prefetch, which filled the window already)
+                    res = []
+                    fill(view, start + keep, start + win, res)
+                    if isinstance(res[0], BaseException):
+                        raise res[0]
+                    keep += res[0]
+                    eof = res[1]
                 if keep == 0 and eof:
                     g["ready"].put(None)
                     return
+                base = ptr + start
                 cnt, used = ctypes.c_uint64(0), ctypes.c_uint64(0)
-                _native.check(L.b2d_bgzf_scan(comp_ptr, keep, maxm, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)))
+                _native.check(L.b2d_bgzf_scan(base, keep, maxm, po, pl, rl, cr, ctypes.byref(cnt), ctypes.byref(used)))
                 n = cnt.value
                 if n == 0:
                     # not (or no longer) BGZF: a partial member at the end of the file, trailing zero padding, or an
                     # ordinary gzip member appended to the file — CPython's reader takes the rest, errors included
-                    rest = bytes(comp_view[:keep])
+                    rest = bytes(view[start:start + keep])
                     g["ready"].put(("cpu", _stdgzip.GzipFile(fileobj=_Prefixed(rest, self.raw), mode="rb")))
                     return
                 # as many members as fit the output buffer
@@ -509,15 +529,27 @@ class _ThreadedGzipReader(io.RawIOBase):
                     total += rl[take]
                     take += 1
                 consumed = used.value if take == n else po[take - 1] + pl[take - 1] + 8
+                rest = keep - consumed
+                # What is left over is at most a partial member (< 64 KiB) unless the output buffer cut the window short:
+                # then the next window's bytes can be read into the other buffer, behind room for the leftover, while the
+                # GPU works on this one (a 128 MiB read from the page cache takes about as long as its inflate call).
+                pre, pre_res = None, []
+                if take == n and not eof and rest <= head:
+                    pre = threading.Thread(target=fill, args=(bufs[cur ^ 1][1], head, head + win - rest, pre_res), daemon=True)
+                    pre.start()
                 out = None
                 while out is None:
                     try:
                         out = g["free"].get(timeout=0.05)
                     except queue.Empty:
                         if g["stop"]:
+                            if pre is not None:
+                                pre.join()
                             return
                 out_n = ctypes.c_uint64(0)
-                rc = L.b2d_inflate_members_host(ctx.handle, comp_ptr, keep, po, pl, rl, cr, take, out[0], cap, ctypes.byref(out_n))
+                rc = L.b2d_inflate_members_host(ctx.handle, base, keep, po, pl, rl, cr, take, out[0], cap, ctypes.byref(out_n))
+                if pre is not None:
+                    pre.join()
                 if rc:
                     g["free"].put(out)
                     msg = _native.last_error()
@@ -528,10 +560,18 @@ class _ThreadedGzipReader(io.RawIOBase):
                     g["ready"].put((out, out_n.value))
                 else:
                     g["free"].put(out)
-                rest = keep - consumed
-                if rest:
-                    ctypes.memmove(comp_ptr, comp_ptr + consumed, rest)
-                keep = rest
+                if pre is not None:
+                    if isinstance(pre_res[0], BaseException):
+                        raise pre_res[0]
+                    optr = bufs[cur ^ 1][0]
+                    if rest:
+                        ctypes.memmove(optr + head - rest, base + consumed, rest)
+                    cur ^= 1
+                    start, keep, eof = head - rest, rest + pre_res[0], pre_res[1]
+                else:
+                    if rest:
+                        ctypes.memmove(ptr + head, base + consumed, rest)
+                    start, keep = head, rest
         except BaseException as e:       # surfaces in the reading thread
             g["ready"].put(e)
 
@@ -549,9 +589,11 @@ class _ThreadedGzipReader(io.RawIOBase):
         g["out_cap"] = win * 4
         g["pinned"] = []
         g["free"], g["ready"], g["stop"] = queue.Queue(), queue.Queue(), False
-        ent = (g["win"] + 16,) + _pinned_pool.get(g["win"] + 16)
-        g["pinned"].append(ent)
-        g["comp"] = ent[1:]
+        g["comp"] = []
+        for _ in range(2):
+            ent = (_BGZF_HEAD + g["win"] + 16,) + _pinned_pool.get(_BGZF_HEAD + g["win"] + 16)
+            g["pinned"].append(ent)
+            g["comp"].append(ent[1:])
         for _ in range(2):
             ent = (g["out_cap"] + 16,) + _pinned_pool.get(g["out_cap"] + 16)
             g["pinned"].append(ent)
