@@ -179,6 +179,16 @@ int b2d_inflate_device_sub(b2d_ctx *ctx, const uint8_t *d_in, uint64_t in_n, con
                            uint8_t *d_out, uint64_t raw_n, float *ms);
 int b2d_inflate_host_sub(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
                          uint64_t nblocks, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc);
+/* b2d_inflate_host_sub in two halves, for readers that work through a file window by window (the reference's reader
+ * thread does the same job serially, src/zlib_ng/gzip_ng_threaded.py:98-190): _decode uploads the window's compressed
+ * bytes and queues its decode without waiting for anything and WITHOUT the dictionary (dict_n only says how long it will
+ * be); _resolve, given the dictionary — the 32 KiB the window before ended with — finishes the window into `out` and
+ * returns when the bytes are there.  A reader queues the decode of window w + 1 (on a second context) before it resolves
+ * window w, so the device never idles between windows.  One decode may be outstanding per context; out == NULL gives
+ * it up. */
+int b2d_inflate_host_decode(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
+                            uint64_t nblocks, uint64_t dict_n, uint64_t raw_n);
+int b2d_inflate_host_resolve(b2d_ctx *ctx, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc);
 /* the same with host buffers: chunks of 512 blocks flow through H2D / decode / resolve / D2H side by side.  `crc`
  * (optional) is continued over the output: *crc = crc32(out[0, raw_n), *crc), computed on the device. */
 int b2d_inflate_host(b2d_ctx *ctx, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, uint64_t nblocks,

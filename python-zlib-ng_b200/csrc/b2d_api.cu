@@ -181,6 +181,8 @@ struct b2d_ctx {
     cudaStream_t st_inf_in, st_inf_out;                                  /* host calls: copies of chunk c+1 / c-1 beside chunk c's kernels */
     cudaStream_t st_inf_dec[B2D_INF_DEC_STREAMS];                                          /* ... and the decodes of neighbouring chunks beside each other */
     std::vector<cudaEvent_t> ev_inf_h2d, ev_inf_done;                    /* per chunk */
+    /* b2d_inflate_host_decode has queued the decode of a call; b2d_inflate_host_resolve finishes it */
+    struct { bool active; uint64_t in_n, nblocks, raw_n, nchunks, dict_n; const uint32_t *d_sub; int mode; } inf_pend;
     /* optional per-stage timing of device-resident calls */
     int profiling;
     cudaEvent_t pev[PROF_BATCHES][B2D_NSTAGE + 1];
@@ -1349,16 +1351,23 @@ extern "C" int b2d_inflate_host(b2d_ctx *c, const uint8_t *in, uint64_t in_n, co
     return b2d_inflate_host_sub(c, in, in_n, block_offsets, nullptr, nblocks, dict, dict_n, out, raw_n, crc);
 }
 
-extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
-                                    uint64_t nblocks, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
-    if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n) || (!block_offsets && nblocks)) return fail(B2D_STREAM_ERROR, "null argument");
-    if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
-    if (nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
+/* One host call in two halves, so that a reader can queue the decode of its next window before it waits for the window
+ * before (a 32 KiB sub-block takes a warp 6-7 ms whatever shares the SM: a single 512 MiB call leaves the device half
+ * empty while its last warps finish and its bytes travel back).  The decode needs no dictionary — what it cannot know
+ * it leaves as markers — so b2d_inflate_host_decode uploads the compressed bytes and queues k_inf_decode for every chunk
+ * without waiting for anything; b2d_inflate_host_resolve, given the dictionary (the 32 KiB the window before ended
+ * with), queues the pass over the tails and the finishing pass per chunk, brings the bytes back and checks the
+ * verdict.  One decode may be outstanding per context. */
+extern "C" int b2d_inflate_host_decode(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
+                                       uint64_t nblocks, uint64_t dict_n, uint64_t raw_n) {
+    if (!c || (!in && in_n) || (!block_offsets && nblocks)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (raw_n == 0 || nblocks != (raw_n + B2D_BLOCK - 1) / B2D_BLOCK) return fail(B2D_STREAM_ERROR, "block index does not match the output size");
     if (nblocks > 0x0fffffffull) return fail(B2D_STREAM_ERROR, "too many blocks");
     for (uint64_t b = 0; b < nblocks; ++b)
         if (block_offsets[b] >= in_n || (b && block_offsets[b] <= block_offsets[b - 1])) return fail(B2D_STREAM_ERROR, "bad block index");
-    if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
-    std::lock_guard<std::recursive_mutex> whole(c->mu);      /* the device copies below belong to this call until it returns */
+    if (dict_n > B2D_WINDOW) dict_n = B2D_WINDOW;
+    std::lock_guard<std::recursive_mutex> whole(c->mu);
+    if (c->inf_pend.active) return fail(B2D_STREAM_ERROR, "a decode is outstanding on this context: b2d_inflate_host_resolve comes first");
     CU(cudaSetDevice(c->device));
     { int rc = inflate_host_buffers(c, in_n, raw_n); if (rc) return rc; }
     { int rc = inflate_prepare(c, nblocks, raw_n, true); if (rc) return rc; }
@@ -1378,31 +1387,19 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     const int mode = inflate_mode(c);
     const bool conc = mode == B2D_INF_CONCURRENT;
     uint8_t *d_stream = c->d_inf_in + B2D_WINDOW;
-    const uint8_t *d_dict = dict_n ? c->d_inf_in : nullptr;
     /* Chunks of 512 blocks flow through three stages: the compressed bytes of chunk k + 1 go up (st_inf_in) while chunk
      * k is decoded (one of B2D_INF_DEC_STREAMS decode streams: a block takes a warp milliseconds, so neighbouring chunks must decode
-     * side by side to fill the device) and resolved (st_inf, which follows the decodes block by block) and the bytes of
-     * chunk k - 1 come back (st_inf_out).  The chain over the block tails runs through all chunks on st_inf. */
+     * side by side to fill the device) and, in the second half of the call, resolved (st_inf, which follows the decodes
+     * block by block) while the bytes of chunk k - 1 come back (st_inf_out). */
     CU(cudaMemcpyAsync(c->d_inf_index, block_offsets, nblocks * sizeof(uint64_t), cudaMemcpyHostToDevice, c->st));
     const uint32_t *d_sub = nullptr;
     { int rc = upload_sub_bits(c, sub_bits, nblocks, &d_sub); if (rc) return rc; }
     CU(cudaMemsetAsync(c->d_inf_err, 0, 2 * sizeof(uint32_t), c->st));
     CU(cudaMemsetAsync(c->d_inf_flags, 0, nblocks * sizeof(uint32_t), c->st));
-    if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, c->st));
     if (conc) {
-        CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* index, flags, error words, dictionary are in place */
+        CU(cudaEventRecord(c->ev_inf_fork, c->st));                    /* index, flags, error words are in place */
         CU(cudaStreamWaitEvent(c->st_inf, c->ev_inf_fork, 0));
         for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) CU(cudaStreamWaitEvent(c->st_inf_dec[i], c->ev_inf_fork, 0));
-    }
-    cudaStream_t st_res = conc ? c->st_inf : c->st;                    /* where a chunk's bytes become final */
-    /* B2D_TRACE=1: when each chunk's upload, resolve and download ended (device time, ms from the start of the call) */
-    static const bool trace = getenv("B2D_TRACE") && getenv("B2D_TRACE")[0] == '1';
-    std::vector<cudaEvent_t> tev;
-    const auto t_host = std::chrono::steady_clock::now();
-    if (trace) {
-        tev.resize(3 * nchunks + 1);
-        for (auto &e : tev) CU(cudaEventCreate(&e));
-        CU(cudaEventRecord(tev[3 * nchunks], c->st));
     }
     for (uint64_t k = 0; k < nchunks; ++k) {
         const uint64_t b0 = k * B2D_INF_CHUNK_BLOCKS, b1 = b0 + B2D_INF_CHUNK_BLOCKS < nblocks ? b0 + B2D_INF_CHUNK_BLOCKS : nblocks;
@@ -1410,17 +1407,69 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
         cudaStream_t st_dec = conc ? c->st_inf_dec[k % B2D_INF_DEC_STREAMS] : c->st;
         CU(cudaMemcpyAsync(d_stream + lo, in + lo, hi - lo, cudaMemcpyHostToDevice, c->st_inf_in));
         CU(cudaEventRecord(c->ev_inf_h2d[k], c->st_inf_in));
-        if (trace) CU(cudaEventRecord(tev[3 * k], c->st_inf_in));
         CU(cudaStreamWaitEvent(st_dec, c->ev_inf_h2d[k], 0));
+        CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, nullptr, (uint32_t)dict_n,
+                              c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_dec, st_dec, B2D_INF_DECODE_ONLY));
+        c->launches += 1;
+    }
+    c->inf_pend.active = true; c->inf_pend.in_n = in_n; c->inf_pend.nblocks = nblocks; c->inf_pend.raw_n = raw_n;
+    c->inf_pend.nchunks = nchunks; c->inf_pend.dict_n = dict_n; c->inf_pend.d_sub = d_sub; c->inf_pend.mode = mode;
+    return B2D_OK;
+}
+
+/* wait for everything a decode has queued (the context's buffers may be reused afterwards) */
+static int inflate_settle(b2d_ctx *c) {
+    c->inf_pend.active = false;
+    CU(cudaStreamSynchronize(c->st_inf_in));
+    for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) CU(cudaStreamSynchronize(c->st_inf_dec[i]));
+    CU(cudaStreamSynchronize(c->st_inf));
+    CU(cudaStreamSynchronize(c->st_inf_out));
+    CU(cudaStreamSynchronize(c->st));
+    return B2D_OK;
+}
+
+/* out == NULL: give the outstanding decode up (waits for what it queued) */
+extern "C" int b2d_inflate_host_resolve(b2d_ctx *c, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
+    if (!c || (!dict && dict_n)) return fail(B2D_STREAM_ERROR, "null argument");
+    std::lock_guard<std::recursive_mutex> whole(c->mu);
+    if (!c->inf_pend.active) return fail(B2D_STREAM_ERROR, "b2d_inflate_host_resolve without b2d_inflate_host_decode");
+    CU(cudaSetDevice(c->device));
+    if (!out) return inflate_settle(c);
+    if (dict_n > B2D_WINDOW) { dict += dict_n - B2D_WINDOW; dict_n = B2D_WINDOW; }
+    if (raw_n != c->inf_pend.raw_n || dict_n != c->inf_pend.dict_n) {
+        inflate_settle(c);
+        return fail(B2D_STREAM_ERROR, "output size or dictionary length differ from what the decode was told");
+    }
+    const uint64_t in_n = c->inf_pend.in_n, nblocks = c->inf_pend.nblocks, nchunks = c->inf_pend.nchunks;
+    const uint32_t *d_sub = c->inf_pend.d_sub;
+    const bool conc = c->inf_pend.mode == B2D_INF_CONCURRENT;
+    c->inf_pend.active = false;
+    uint8_t *d_stream = c->d_inf_in + B2D_WINDOW;
+    const uint8_t *d_dict = dict_n ? c->d_inf_in : nullptr;
+    cudaStream_t st_res = conc ? c->st_inf : c->st;                    /* where a chunk's bytes become final */
+    if (dict_n) CU(cudaMemcpyAsync(c->d_inf_in, dict, dict_n, cudaMemcpyHostToDevice, st_res));
+    /* B2D_TRACE=1: when each chunk was resolved and downloaded (device time, ms from the start of this half) */
+    static const bool trace = getenv("B2D_TRACE") && getenv("B2D_TRACE")[0] == '1';
+    std::vector<cudaEvent_t> tev;
+    const auto t_host = std::chrono::steady_clock::now();
+    if (trace) {
+        tev.resize(2 * nchunks + 1);
+        for (auto &e : tev) CU(cudaEventCreate(&e));
+        CU(cudaEventRecord(tev[2 * nchunks], st_res));
+    }
+    for (uint64_t k = 0; k < nchunks; ++k) {
+        const uint64_t b0 = k * B2D_INF_CHUNK_BLOCKS, b1 = b0 + B2D_INF_CHUNK_BLOCKS < nblocks ? b0 + B2D_INF_CHUNK_BLOCKS : nblocks;
+        /* the pass over the tails follows the decode through the blocks' ready flags (chunk by chunk on one stream: the
+         * tails of chunk k build on those of chunk k - 1) */
         CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, (uint32_t)b0, (uint32_t)(b1 - b0), (uint32_t)nblocks, d_dict, (uint32_t)dict_n,
-                              c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_dec, st_res, mode));
-        c->launches += B2D_INF_LAUNCHES;
+                              c->d_inf16, c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, st_res, st_res, B2D_INF_RESOLVE_ONLY));
+        c->launches += 2;
         CU(cudaEventRecord(c->ev_inf_done[k], st_res));
-        if (trace) CU(cudaEventRecord(tev[3 * k + 1], st_res));
+        if (trace) CU(cudaEventRecord(tev[2 * k], st_res));
         CU(cudaStreamWaitEvent(c->st_inf_out, c->ev_inf_done[k], 0));
         const uint64_t o0 = b0 * (uint64_t)B2D_BLOCK, o1 = b1 * (uint64_t)B2D_BLOCK < raw_n ? b1 * (uint64_t)B2D_BLOCK : raw_n;
         CU(cudaMemcpyAsync(out + o0, c->d_inf_out + o0, o1 - o0, cudaMemcpyDeviceToHost, c->st_inf_out));
-        if (trace) CU(cudaEventRecord(tev[3 * k + 2], c->st_inf_out));
+        if (trace) CU(cudaEventRecord(tev[2 * k + 1], c->st_inf_out));
         if (k + 1 == nchunks) {
             if (crc) { CU(b2d_crc32_dev_launch(c->ck, c->d_inf_out, raw_n, st_res)); c->launches += crc_launches(c->d_inf_out, raw_n); }
             if (st_res != c->st) { CU(cudaEventRecord(c->ev_inf_join, st_res)); CU(cudaStreamWaitEvent(c->st, c->ev_inf_join, 0)); }
@@ -1431,20 +1480,20 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     CU(cudaStreamSynchronize(c->st));
     CU(cudaStreamSynchronize(c->st_inf_out));
     if (trace) {
-        fprintf(stderr, "b2d_inflate_host_sub: %llu blocks, host %.2f ms; chunk: upload / resolved / downloaded (ms)\n", (unsigned long long)nblocks,
+        fprintf(stderr, "b2d_inflate_host_resolve: %llu blocks, host %.2f ms; chunk: resolved / downloaded (ms)\n", (unsigned long long)nblocks,
                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host).count());
         for (uint64_t k = 0; k < nchunks; ++k) {
-            float a = 0, b = 0, d = 0;
-            cudaEventElapsedTime(&a, tev[3 * nchunks], tev[3 * k]);
-            cudaEventElapsedTime(&b, tev[3 * nchunks], tev[3 * k + 1]);
-            cudaEventElapsedTime(&d, tev[3 * nchunks], tev[3 * k + 2]);
-            fprintf(stderr, "   %2llu: %6.2f %6.2f %6.2f\n", (unsigned long long)k, a, b, d);
+            float b = 0, d = 0;
+            cudaEventElapsedTime(&b, tev[2 * nchunks], tev[2 * k]);
+            cudaEventElapsedTime(&d, tev[2 * nchunks], tev[2 * k + 1]);
+            fprintf(stderr, "   %2llu: %6.2f %6.2f\n", (unsigned long long)k, b, d);
         }
         for (auto &e : tev) cudaEventDestroy(e);
     }
     if (err[1] && !err[0]) {
-        /* the pass over the tails gave up waiting for a decode (never a statement about the data): every block is decoded
-         * by now, so resolve everything again on one stream and fetch the bytes once more */
+        /* the pass over the tails gave up waiting for a decode (never a statement about the data): once every block is
+         * decoded, resolve everything again on one stream and fetch the bytes once more */
+        for (int i = 0; i < B2D_INF_DEC_STREAMS; ++i) CU(cudaStreamSynchronize(c->st_inf_dec[i]));
         CU(cudaMemsetAsync(c->d_inf_err + 1, 0, sizeof(uint32_t), c->st));
         CU(b2d_launch_inflate(d_stream, in_n, c->d_inf_index, d_sub, 0, (uint32_t)nblocks, (uint32_t)nblocks, d_dict, (uint32_t)dict_n, c->d_inf16,
                               c->d_inf_out, raw_n, c->d_inf_flags, c->d_inf_err, c->st, c->st, B2D_INF_RESOLVE_ONLY));
@@ -1458,6 +1507,16 @@ extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n
     { int rc = inflate_verdict(err); if (rc) return rc; }
     if (crc) *crc = b2d_crc32_dev_finish(c->ck, raw_n, *crc);
     return B2D_OK;
+}
+
+extern "C" int b2d_inflate_host_sub(b2d_ctx *c, const uint8_t *in, uint64_t in_n, const uint64_t *block_offsets, const uint32_t *sub_bits,
+                                    uint64_t nblocks, const uint8_t *dict, uint64_t dict_n, uint8_t *out, uint64_t raw_n, uint32_t *crc) {
+    if (!c || (!in && in_n) || (!out && raw_n) || (!dict && dict_n) || (!block_offsets && nblocks)) return fail(B2D_STREAM_ERROR, "null argument");
+    if (raw_n == 0) return nblocks ? fail(B2D_STREAM_ERROR, "block index does not match the output size") : B2D_OK;
+    std::lock_guard<std::recursive_mutex> whole(c->mu);      /* the device copies belong to this call until it returns */
+    int rc = b2d_inflate_host_decode(c, in, in_n, block_offsets, sub_bits, nblocks, dict_n, raw_n);
+    if (rc) return rc;
+    return b2d_inflate_host_resolve(c, dict, dict_n, out, raw_n, crc);
 }
 
 /* ------------------------------------------------------------------------- */

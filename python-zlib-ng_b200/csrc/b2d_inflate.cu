@@ -474,6 +474,7 @@ cudaError_t b2d_launch_inflate(const uint8_t *d_in, uint64_t in_n, const uint64_
             k_inf_decode<INF_BLOCKS><<<(nb + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, INF_DECODE_PAD, st_dec>>>(
                 d_in, in_n, d_index, nullptr, nullptr, b0, nb, raw_n, dict_n, d_out16, d_flags, d_err);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (mode == B2D_INF_DECODE_ONLY) return cudaSuccess;
     }
     /* The serial pass over the tails is launched right behind it — on its own (high-priority) stream when the device
      * runs kernels side by side, where it follows the decode through d_flags — and the rest of each block is resolved

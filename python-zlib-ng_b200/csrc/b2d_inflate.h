@@ -14,6 +14,7 @@
 #define B2D_INF_CONCURRENT   0   /* decode first, the tails pass behind it on its own stream */
 #define B2D_INF_SERIAL       1   /* decode, tails, finish on one stream */
 #define B2D_INF_RESOLVE_ONLY 2   /* tails + finish again over symbols that are already decoded */
+#define B2D_INF_DECODE_ONLY  3   /* k_inf_decode alone: the caller resolves later (B2D_INF_RESOLVE_ONLY), e.g. once the dictionary is known */
 /* One chunk: blocks [b0, b0 + nb) of a stream of nblocks, chunks in order.  The decode is issued on st_dec, the pass over
  * the tails and the rest of the resolving on st_res.  The caller makes both streams wait until d_flags and d_err are
  * cleared; st_res == st_dec for B2D_INF_SERIAL and B2D_INF_RESOLVE_ONLY. */

@@ -80,6 +80,8 @@ SIGNATURES = {
     "b2d_inflate_device_sub": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _u64, _u8p, _u64, _u8p, _u64,
                                               _P(ctypes.c_float)]),
     "b2d_inflate_host_sub": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _u64, _u8p, _u64, _u8p, _u64, _P(_u32)]),
+    "b2d_inflate_host_decode": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _P(_u64), _P(_u32), _u64, _u64, _u64]),
+    "b2d_inflate_host_resolve": (ctypes.c_int, [ctypes.c_void_p, _u8p, _u64, _u8p, _u64, _P(_u32)]),
     "b2d_compress_and_crc_multi_sub": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _u8p, _u64, _u8p, _u64, _u8p, _u64,
                                                       _P(_u64), _P(_u32), _P(_u64), _P(_u32), _u64, _P(_u64)]),
     "b2d_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),

@@ -66,6 +66,7 @@ _LOCATOR = struct.Struct("<4sIQQQI")      # magic, version, data_start, raw size
 _LOCATOR_MAGIC = b"B2DX"
 _LOCATOR_MEMBER = 10 + 2 + 4 + _LOCATOR.size + 2 + 8
 _READER_TRACE = os.environ.get("B2D_READER_TRACE", "") not in ("", "0")       # stage times on stderr when a reader closes
+_READ_DEPTH = min(max(int(os.environ.get("B2D_READ_DEPTH", "2")), 1), 4)      # windows of a reader whose decode is queued on the GPU at once
 _READ_WINDOW_BLOCKS = max(int(os.environ.get("B2D_READ_WINDOW_MIB", "512")), 1) * 8    # device blocks the reader decodes per GPU call
 _BGZF_HEAD = 128 << 10        # room in front of a BGZF window for what the window before left over (a member is at most 64 KiB)
 _BGZF_WINDOW = max(int(os.environ.get("B2D_BGZF_WINDOW_MIB", "128")), 1) << 20      # compressed bytes of a BGZF file per GPU call
@@ -237,6 +238,32 @@ def open_as_binary_stream(filename, open_mode):
     raise TypeError("filename must be a str or bytes object, or a file")
 
 
+class _ReaderContexts:
+    """Pairs of contexts for readers (a reader keeps a decode queued on one while it resolves on the other, so the pair is
+    its own for as long as it reads); a finished reader's pair, device buffers included, serves the next one."""
+
+    def __init__(self):
+        self._lock = threading.Lock()
+        self._idle = []
+
+    def get(self):
+        with self._lock:
+            if self._idle:
+                return self._idle.pop()
+        return [_native.Context(0, 1 << 20) for _ in range(_READ_DEPTH)]      # they only inflate: no deflate batch to size for
+
+    def put(self, pair):
+        with self._lock:
+            if len(self._idle) < 2:
+                self._idle.append(pair)
+                return
+        for c in pair:
+            c.close()
+
+
+_reader_contexts = _ReaderContexts()
+
+
 class _ThreadedGzipReader(io.RawIOBase):
     """Streamed gzip reader.  Files written by this module's writer carry a block index (see _WRITE_INDEX): those
     are inflated on the GPU, a window of device blocks per call (b2d_inflate_host: one warp per 128 KiB block),
@@ -384,13 +411,42 @@ class _ThreadedGzipReader(io.RawIOBase):
         return True
 
     def _gpu_worker(self):
-        """Decodes window after window into pinned buffers, one window ahead of the consumer."""
+        """Decodes window after window into pinned buffers, ahead of the consumer.  Two contexts take turns: the decode of
+        window w + 1 is queued (b2d_inflate_host_decode: no dictionary needed, nothing waited for) before window w is
+        resolved against the 32 KiB before it and brought back (b2d_inflate_host_resolve), so the device always has the
+        next window's warps to run while the last ones of this window finish and its bytes travel."""
         g = self._gpu
         sizes = g["sizes"]
-        ctx = _native.default_context()
+        ctxs = _reader_contexts.get()
         L = _native.lib()
+        pending = []                   # (context, compressed buffer, raw bytes) of the windows whose decode is queued, oldest first
         try:
             tail, crc = b"", ctypes.c_uint32(0)
+
+            def finish(p):
+                """False: the reader was closed while waiting for an output buffer"""
+                nonlocal tail
+                ctx, comp, raw_n = p
+                out = None
+                while out is None:
+                    try:
+                        out = g["free"].get(timeout=0.05)
+                    except queue.Empty:
+                        if g["stop"]:
+                            return False
+                out_ptr, out_view = out
+                t0 = time.perf_counter()
+                rc = L.b2d_inflate_host_resolve(ctx.handle, tail if tail else None, len(tail), out_ptr, raw_n, ctypes.byref(crc))
+                g["t_gpu"] = g.get("t_gpu", 0.0) + time.perf_counter() - t0
+                g["comp_free"].put(comp)
+                if rc:
+                    g["free"].put(out)
+                    raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
+                tail = (tail + bytes(out_view[max(raw_n - DEFLATE_WINDOW_SIZE, 0):raw_n]))[-DEFLATE_WINDOW_SIZE:]
+                g["ready"].put((out, raw_n))
+                return True
+
+            k = 0
             while not g["stop"]:
                 try:
                     item = g["comp_ready"].get(timeout=0.05)
@@ -399,6 +455,10 @@ class _ThreadedGzipReader(io.RawIOBase):
                 if isinstance(item, BaseException):
                     raise item
                 if isinstance(item, bytes):                       # the member's end
+                    while pending:
+                        if not finish(pending[0]):
+                            return
+                        pending.pop(0)
                     if len(item) != 10:
                         raise EOFError("Compressed file ended before the end-of-stream marker was reached")
                     if item[:2] != b"\x03\x00":
@@ -417,29 +477,30 @@ class _ThreadedGzipReader(io.RawIOBase):
                 for i in range(nb):
                     offs[i] = acc
                     acc += sizes[first + i]
-                out = None
-                while out is None:
-                    try:
-                        out = g["free"].get(timeout=0.05)
-                    except queue.Empty:
-                        if g["stop"]:
-                            return
-                out_ptr, out_view = out
                 subs = None
                 if g.get("subs"):                     # one warp per 32 KiB sub-block instead of one per block
                     subs = (ctypes.c_uint32 * (4 * nb))(*g["subs"][4 * first:4 * (first + nb)])
+                ctx = ctxs[k % len(ctxs)]
+                k += 1
+                # every window but the first follows at least one whole block: its dictionary will be 32 KiB long
+                dict_n = DEFLATE_WINDOW_SIZE if first else 0
                 t0 = time.perf_counter()
-                rc = L.b2d_inflate_host_sub(ctx.handle, comp[0], comp_n, offs, subs, nb, tail if tail else None, len(tail),
-                                            out_ptr, raw_n, ctypes.byref(crc))
+                rc = L.b2d_inflate_host_decode(ctx.handle, comp[0], comp_n, offs, subs, nb, dict_n, raw_n)
                 g["t_gpu"] = g.get("t_gpu", 0.0) + time.perf_counter() - t0
-                g["comp_free"].put(comp)
                 if rc:
-                    g["free"].put(out)
+                    g["comp_free"].put(comp)
                     raise _stdgzip.BadGzipFile(f"Error {rc} while decompressing data: {_native.last_error()}")
-                tail = (tail + bytes(out_view[max(raw_n - DEFLATE_WINDOW_SIZE, 0):raw_n]))[-DEFLATE_WINDOW_SIZE:]
-                g["ready"].put((out, raw_n))
+                pending.append((ctx, comp, raw_n))
+                while len(pending) >= len(ctxs):      # every context has a decode queued: the oldest window is due
+                    if not finish(pending[0]):
+                        return
+                    pending.pop(0)
         except BaseException as e:       # surfaces in the reading thread
             g["ready"].put(e)
+        finally:
+            for p in pending:            # closed or failed with decodes still queued: give them up
+                L.b2d_inflate_host_resolve(p[0].handle, None, 0, None, 0, None)
+            _reader_contexts.put(ctxs)
 
     # ---- BGZF: blocked gzip as written by bgzip / htslib.  Every member carries its compressed size in a "BC" extra
     # subfield and is an independent DEFLATE stream of at most 64 KiB, so the members of a window decode side by side
@@ -618,10 +679,13 @@ class _ThreadedGzipReader(io.RawIOBase):
         several = len(sizes) > _READ_WINDOW_BLOCKS
         g["pinned"] = []
         g["free"], g["ready"], g["comp_free"], g["comp_ready"], g["stop"] = queue.Queue(), queue.Queue(), queue.Queue(), queue.Queue(), False
-        for _ in range(3 if several else 1):
+        # compressed windows: one per queued decode and one being read; output windows: one being filled, one being
+        # handed out, one spare
+        for _ in range(_READ_DEPTH + 1 if several else 1):
             ent = (win_comp + 16,) + _pinned_pool.get(win_comp + 16)
             g["pinned"].append(ent)
             g["comp_free"].put(ent[1:])
+        for _ in range(3 if several else 1):
             ent = (win_raw + 16,) + _pinned_pool.get(win_raw + 16)
             g["pinned"].append(ent)
             g["free"].put(ent[1:])
