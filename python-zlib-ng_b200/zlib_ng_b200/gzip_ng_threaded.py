@@ -344,12 +344,13 @@ class _ThreadedGzipReader(io.RawIOBase):
     def _gpu_file_reader(self):
         """Compressed bytes of window after window into pinned buffers (the file is only touched by this thread)."""
         g = self._gpu
-        sizes, nb_all = g["sizes"], len(g["sizes"])
+        sizes = g["sizes"]
         try:
-            first, cpos = 0, g["cpos"]
+            cpos = g["cpos"]
             self.raw.seek(cpos)
-            while first < nb_all and not g["stop"]:
-                nb = min(_READ_WINDOW_BLOCKS, nb_all - first)
+            for first, nb in g["windows"]:
+                if g["stop"]:
+                    break
                 comp_n = sum(sizes[first:first + nb])
                 comp = None
                 while comp is None:
@@ -370,7 +371,6 @@ class _ThreadedGzipReader(io.RawIOBase):
                 cpos += comp_n
                 g["t_file"] = g.get("t_file", 0.0) + time.perf_counter() - t0
                 g["comp_ready"].put((comp, comp_n, first, nb))
-                first += nb
             if not g["stop"]:
                 g["comp_ready"].put(self.raw.read(10))            # 03 00, CRC32, ISIZE
         except BaseException as e:
@@ -674,9 +674,17 @@ class _ThreadedGzipReader(io.RawIOBase):
             if n <= 32 << 20:
                 return max(1 << (n - 1).bit_length(), 1 << 20)
             return (n + (32 << 20) - 1) // (32 << 20) * (32 << 20)
-        win_raw = bucket(min(_READ_WINDOW_BLOCKS * _DEVICE_BLOCK, g["raw_n"]))
-        win_comp = bucket(max(sum(sizes[i:i + _READ_WINDOW_BLOCKS]) for i in range(0, len(sizes), _READ_WINDOW_BLOCKS)))
-        several = len(sizes) > _READ_WINDOW_BLOCKS
+        # the windows: the first ones smaller, so that the first bytes arrive sooner (a quarter, a half, then whole windows)
+        wins, first, ramp = [], 0, max(_READ_WINDOW_BLOCKS // 4, 1)
+        while first < len(sizes):
+            nb = min(ramp, _READ_WINDOW_BLOCKS, len(sizes) - first)
+            wins.append((first, nb))
+            first += nb
+            ramp *= 2
+        g["windows"] = wins
+        win_raw = bucket(min(max(nb for _, nb in wins) * _DEVICE_BLOCK, g["raw_n"]))
+        win_comp = bucket(max(sum(sizes[f:f + nb]) for f, nb in wins))
+        several = len(wins) > 1
         g["pinned"] = []
         g["free"], g["ready"], g["comp_free"], g["comp_ready"], g["stop"] = queue.Queue(), queue.Queue(), queue.Queue(), queue.Queue(), False
         # compressed windows: one per queued decode and one being read; output windows: one being filled, one being

@@ -577,3 +577,55 @@ def test_written_files_carry_sub_block_offsets(gzt, tmp_path, monkeypatch):
     with gzt.open(q, "rb") as f:
         assert f.raw._gpu is not None and f.raw._gpu["subs"] is None
         assert f.read() == data
+
+
+# ---- the host call in two halves: b2d_inflate_host_decode (no dictionary, no waiting) / b2d_inflate_host_resolve
+def test_two_windows_decoded_ahead_and_resolved_in_order(nat):
+    """What the reader does: the stream is cut into two windows at a block boundary; both decodes are queued (on two
+    contexts) before the first window is resolved, the second one against the last 32 KiB of the first.  The CRC runs on.
+    Then the error behaviour of the pair of calls."""
+    L = nat.lib()
+    a, b = nat.Context(0, 1 << 20), nat.Context(0, 1 << 20)
+    comp = nat.Context(0, 64 << 20)
+    try:
+        n = 700 * BLOCK + 12345
+        base = synthdata.make("mixed", 16_000_000, 91).tobytes()
+        data = (base * (n // len(base) + 1))[:n]
+        zdict = base[-20_000:]
+        stream, offs, d_buf, d_out, _ = deflate_indexed(nat, comp, data, 6, zdict)
+        bits = sub_bits_of_last_call(nat, comp, len(offs) - 1)
+        comp.device_free(d_buf)
+        comp.device_free(d_out)
+        nb = len(offs) - 1
+        cut = 300                                      # blocks in the first window
+        w1 = stream[:offs[cut]]
+        w2 = stream[offs[cut]:]
+        o1 = (ctypes.c_uint64 * cut)(*offs[:cut])
+        o2 = (ctypes.c_uint64 * (nb - cut))(*[o - offs[cut] for o in offs[cut:nb]])
+        s1 = (ctypes.c_uint32 * (4 * cut))(*bits[:4 * cut])
+        s2 = (ctypes.c_uint32 * (4 * (nb - cut)))(*bits[4 * cut:4 * nb])
+        n1, n2 = cut * BLOCK, n - cut * BLOCK
+        out1, out2 = ctypes.create_string_buffer(n1), ctypes.create_string_buffer(n2)
+        for subs1, subs2 in ((s1, s2), (None, None)):
+            nat.check(L.b2d_inflate_host_decode(a.handle, w1, len(w1), o1, subs1, cut, len(zdict), n1))
+            nat.check(L.b2d_inflate_host_decode(b.handle, w2, len(w2), o2, subs2, nb - cut, 32768, n2))
+            crc = ctypes.c_uint32(0)
+            nat.check(L.b2d_inflate_host_resolve(a.handle, zdict, len(zdict), out1, n1, ctypes.byref(crc)))
+            assert out1.raw == data[:n1]
+            nat.check(L.b2d_inflate_host_resolve(b.handle, out1.raw[-32768:], 32768, out2, n2, ctypes.byref(crc)))
+            assert out2.raw == data[n1:]
+            assert crc.value == zlib.crc32(data)
+        # a second decode before the resolve, a resolve without a decode, a dictionary of another length: refused
+        nat.check(L.b2d_inflate_host_decode(a.handle, w1, len(w1), o1, s1, cut, len(zdict), n1))
+        assert L.b2d_inflate_host_decode(a.handle, w1, len(w1), o1, s1, cut, len(zdict), n1) == nat.B2D_STREAM_ERROR
+        assert L.b2d_inflate_host_resolve(a.handle, zdict, len(zdict) - 1, out1, n1, None) == nat.B2D_STREAM_ERROR
+        assert L.b2d_inflate_host_resolve(a.handle, zdict, len(zdict), out1, n1, None) == nat.B2D_STREAM_ERROR   # given up by the mismatch
+        # giving a queued decode up leaves the context usable
+        nat.check(L.b2d_inflate_host_decode(a.handle, w1, len(w1), o1, s1, cut, len(zdict), n1))
+        nat.check(L.b2d_inflate_host_resolve(a.handle, None, 0, None, 0, None))
+        nat.check(L.b2d_inflate_host_sub(a.handle, w1, len(w1), o1, s1, cut, zdict, len(zdict), out1, n1, None))
+        assert out1.raw == data[:n1]
+    finally:
+        a.close()
+        b.close()
+        comp.close()
