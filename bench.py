@@ -619,6 +619,33 @@ def main():
                         f.write(pb.view)
                     best = max(best, n / (time.perf_counter() - t0) / 1e9)
             extra["gzip_ng_threaded_open_wb_pinned_buffer_GBps"] = best
+            # ... and the way back: the file (tmpfs) through open(..., "rb") on the GPU, readinto a reused 64 MiB buffer;
+            # the bytes are checked (CRC-32 by the reader itself, against the trailer; a wrong length raises too)
+            shm = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
+            path = os.path.join(shm, f"b2d_bench_{os.getpid()}.gz")
+            try:
+                with gzt.open(path, "wb", compresslevel=a.level, threads=ncores) as f:
+                    f.write(smv)
+                box = bytearray(64 * MIB)
+                best, on_gpu = 0.0, False
+                for _ in range(3):
+                    got = 0
+                    t0 = time.perf_counter()
+                    with gzt.open(path, "rb") as f:
+                        on_gpu = f.raw._gpu is not None
+                        while True:
+                            k = f.readinto(box)
+                            if not k:
+                                break
+                            got += k
+                    if got != n:
+                        raise RuntimeError(f"reader returned {got} of {n} bytes")
+                    best = max(best, n / (time.perf_counter() - t0) / 1e9)
+                extra["gzip_ng_threaded_open_rb_GBps"] = best
+                extra["gzip_ng_threaded_open_rb_on_gpu"] = on_gpu
+            finally:
+                if os.path.exists(path):
+                    os.unlink(path)
         except Exception as e:  # report, never fake
             extra["gzip_ng_threaded_error"] = f"{type(e).__name__}: {e}"
     if rank == 0:
