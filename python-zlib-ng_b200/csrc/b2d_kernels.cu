@@ -968,16 +968,18 @@ __device__ __forceinline__ void sink_close(bitsink &s) {
     if (s.fill) atomicOr(&s.out[s.word], (uint32_t)s.acc);
 }
 
-__device__ __forceinline__ void tok_bits(uint32_t x, const uint32_t *ll, const uint32_t *dc, uint64_t *val, uint32_t *cnt) {
+/* the bits of one token.  lc[len - 3] = the length's code with its extra bits behind it, bit count in the top byte (built
+ * once per sub-block); dsym = distance symbol of d-1 (d-1 < 256) or of 256 + ((d-1) >> 7), as in k_parse */
+__device__ __forceinline__ void tok_bits(uint32_t x, const uint32_t *ll, const uint32_t *dc, const uint32_t *lc, const uint8_t *dsym,
+                                         uint64_t *val, uint32_t *cnt) {
     if (!b2d_tok_is_match(x)) { const uint32_t c = ll[x]; *val = c & 0xffffu; *cnt = c >> 16; return; }
-    uint32_t ls, le, lv, ds, de, dv;
-    b2d_len_sym(b2d_tok_len3(x), &ls, &le, &lv);
-    b2d_dist_sym(b2d_tok_dist1(x), &ds, &de, &dv);
-    const uint32_t c1 = ll[257u + ls], c2 = dc[ds];
-    uint64_t v = c1 & 0xffffu; uint32_t nb = c1 >> 16;
-    v |= (uint64_t)lv << nb; nb += le;
+    const uint32_t d1 = b2d_tok_dist1(x);
+    const uint32_t c1 = lc[b2d_tok_len3(x)];
+    const uint32_t ds = dsym[d1 < 256u ? d1 : 256u + (d1 >> 7)];
+    const uint32_t c2 = dc[ds], de = b2d_dist_extra_bits(ds);
+    uint64_t v = c1 & 0xffffffu; uint32_t nb = c1 >> 24;
     v |= (uint64_t)(c2 & 0xffffu) << nb; nb += c2 >> 16;
-    v |= (uint64_t)dv << nb; nb += de;
+    v |= (uint64_t)(d1 & ((1u << de) - 1u)) << nb; nb += de;
     *val = v; *cnt = nb;                      /* <= 15+5+15+13 = 48 bits */
 }
 
@@ -986,6 +988,8 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
        const b2d_plan *__restrict__ plan, const uint64_t *__restrict__ block_off, uint32_t nsub,
        uint32_t *__restrict__ out) {
     __shared__ uint32_t s_ll[B2D_LL_CODES], s_d[B2D_D_CODES];
+    __shared__ uint32_t s_lc[256];
+    __shared__ uint8_t s_dsym[512];
     __shared__ uint32_t s_wsum[K6_THREADS / 32];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t k = blockIdx.x;
@@ -1034,6 +1038,16 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
             for (uint32_t i = tid; i < B2D_LL_CODES; i += K6_THREADS) s_ll[i] = P->ll_code[i];
             if (tid < B2D_D_CODES) s_d[tid] = P->d_code[tid];
             __syncthreads();
+            static_assert(K6_THREADS == 256, "one table row per thread");
+            {   /* per length: code | extra bits << code length, total bit count in the top byte (<= 20 bits) */
+                uint32_t sy, eb, ev;
+                b2d_len_sym(tid, &sy, &eb, &ev);
+                const uint32_t c1 = s_ll[257u + sy];
+                s_lc[tid] = (((c1 >> 16) + eb) << 24) | (c1 & 0xffffu) | (ev << (c1 >> 16));
+                b2d_dist_sym(tid, &sy, &eb, &ev); s_dsym[tid] = (uint8_t)sy;
+                b2d_dist_sym(tid << 7, &sy, &eb, &ev); s_dsym[256 + tid] = (uint8_t)sy;
+            }
+            __syncthreads();
             const uint32_t nt = I.tok_count;
             /* each thread owns a run of tokens whose length is a multiple of 4, read as uint4 with the
              * next group already in flight (the loop is otherwise bound by the load latency) */
@@ -1052,7 +1066,7 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 #pragma unroll
                     for (uint32_t j = 0; j < 4; ++j) {
                         if (4u * g + j >= t1) break;          /* slots past the last token hold stale words */
-                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, &v, &c);
+                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, s_lc, s_dsym, &v, &c);
                         mybits += c;
                     }
                 }
@@ -1076,7 +1090,7 @@ k_emit(const uint8_t *__restrict__ data, const uint32_t *__restrict__ tok, const
 #pragma unroll
                     for (uint32_t j = 0; j < 4; ++j) {
                         if (4u * g + j >= t1) break;
-                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, &v, &c);
+                        uint64_t v; uint32_t c; tok_bits(x[j], s_ll, s_d, s_lc, s_dsym, &v, &c);
                         if (c > 32u) { sink_put(s, v & 0xffffffffull, 32u); sink_put(s, v >> 32, c - 32u); }
                         else sink_put(s, v, c);
                     }
