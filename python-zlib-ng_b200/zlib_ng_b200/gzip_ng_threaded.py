@@ -238,6 +238,18 @@ def open_as_binary_stream(filename, open_mode):
     raise TypeError("filename must be a str or bytes object, or a file")
 
 
+def _reader_windows(nblocks: int, window: int):
+    """(first block, number of blocks) of the GPU calls a reader makes for a file of `nblocks` device blocks: whole windows
+    of `window` blocks, but the first two smaller (a quarter, a half), so that the first bytes arrive sooner."""
+    wins, first, ramp = [], 0, max(window // 4, 1)
+    while first < nblocks:
+        nb = min(ramp, window, nblocks - first)
+        wins.append((first, nb))
+        first += nb
+        ramp *= 2
+    return wins
+
+
 class _ReaderContexts:
     """Pairs of contexts for readers (a reader keeps a decode queued on one while it resolves on the other, so the pair is
     its own for as long as it reads); a finished reader's pair, device buffers included, serves the next one."""
@@ -674,14 +686,7 @@ class _ThreadedGzipReader(io.RawIOBase):
             if n <= 32 << 20:
                 return max(1 << (n - 1).bit_length(), 1 << 20)
             return (n + (32 << 20) - 1) // (32 << 20) * (32 << 20)
-        # the windows: the first ones smaller, so that the first bytes arrive sooner (a quarter, a half, then whole windows)
-        wins, first, ramp = [], 0, max(_READ_WINDOW_BLOCKS // 4, 1)
-        while first < len(sizes):
-            nb = min(ramp, _READ_WINDOW_BLOCKS, len(sizes) - first)
-            wins.append((first, nb))
-            first += nb
-            ramp *= 2
-        g["windows"] = wins
+        wins = g["windows"] = _reader_windows(len(sizes), _READ_WINDOW_BLOCKS)
         win_raw = bucket(min(max(nb for _, nb in wins) * _DEVICE_BLOCK, g["raw_n"]))
         win_comp = bucket(max(sum(sizes[f:f + nb]) for f, nb in wins))
         several = len(wins) > 1

@@ -247,3 +247,17 @@ def test_bgzf_scan_is_plain_host_code(tmp_path):
         p.write_bytes(blob)
         with gzip_ng_threaded.open(p, "rb") as f:
             assert f.raw._gpu is None and f.read() == data
+
+
+def test_reader_windows_cover_every_block_once_and_ramp_up():
+    """the reader's GPU calls: contiguous, nothing left out, at most `window` blocks each, the first ones smaller"""
+    from zlib_ng_b200.gzip_ng_threaded import _reader_windows
+    for nblocks, window in ((0, 4096), (1, 4096), (1023, 4096), (1024, 4096), (4096, 4096), (32768, 4096), (32769, 4096), (7, 1), (100, 3)):
+        wins = _reader_windows(nblocks, window)
+        assert sum(nb for _, nb in wins) == nblocks
+        pos = 0
+        for first, nb in wins:
+            assert first == pos and 1 <= nb <= window
+            pos += nb
+        if nblocks >= 4 * window and window >= 4:
+            assert [nb for _, nb in wins[:3]] == [window // 4, window // 2, window]
