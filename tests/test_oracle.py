@@ -106,3 +106,16 @@ def test_oracle_vs_live_reference():
         data = synthdata.make(kind, 300_000, seed).tobytes()
         for level in range(0, 10):
             assert orc_inflate(ref.compress(data, level, -15), len(data)) == data
+
+
+def test_fullsize_ratio_fixture_is_complete():
+    """the full-size GPU tests take the reference's sizes from this fixture (tools/make_golden_fullsize.py)"""
+    import json
+    import os
+    rows = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fullsize_ratios.json")))["rows"]
+    got = {(r["kind"], r["seed"], r["level"]): r for r in rows}
+    assert set(got) == {("fastq", 1, 1), ("mixed", 2, 6)}
+    for r in rows:
+        assert r["base_bytes"] == 256 << 20 and r["block_size"] == 1 << 20
+        assert abs(r["reference_ratio"] - r["reference_bytes"] / r["base_bytes"]) < 1e-12
+        assert 0.3 < r["reference_ratio"] < 0.8
