@@ -302,7 +302,9 @@ __device__ __forceinline__ uint32_t k2_search(uint32_t pa, uint32_t la, uint32_t
     return best > 3u ? b2d_pack_match(best < maxl ? best : maxl, pa - (key & ((1u << K2_KEY_SHIFT) - 1u)), 0u) : 0u;
 }
 
+#ifndef K2_DENSE_HITS
 #define K2_DENSE_HITS (K2_THREADS / 8)   /* matches among a tile's first 1024 positions that select the dense coding */
+#endif
 
 /* DEPTH > 0: the policy's chain depth as a compile-time constant (levels 4-6); 0: the `depth` argument.  Depth 1
  * (level 1, Z_RLE) goes to k_match_d1. */
