@@ -22,7 +22,7 @@
  * Reference code this stands in for: zng_inflate (zlib-ng/inflate.c:474-1150), inflate_table
  * (inftrees.c:30-290), inflate_fast (inffast_tpl.h), as driven by zlib_ng.decompress / _GzipReader
  * (zlib_ngmodule.c:275-370, 2426-2637).  Streams from other writers carry no block index and are not
- * accepted.
+ * accepted (DESIGN.md §0 "Out of scope", §10); BGZF members are (k_inf_decode<INF_MEMBERS>).
  */
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
